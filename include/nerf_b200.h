@@ -1,0 +1,191 @@
+/*
+ * nerf_b200 -- C ABI of the B200-native NeRF hot path (libnerf_b200.so).
+ *
+ * The reference (brandontrabucco/nerf) has no FFI: its boundary is the Python
+ * method surface of nerf.model.NeRF.  Each entry point below is what a binding
+ * for one of those methods calls; the comment above it cites the reference
+ * code it replaces (paths relative to the reference repository root).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - tensors are dense, row-major, fp32 unless stated otherwise;
+ *   - the library never allocates: callers pass outputs and workspaces
+ *     (sizes from the *_workspace_bytes queries);
+ *   - `stream` is a cudaStream_t passed as void*; calls are stream-ordered
+ *     and re-entrant;
+ *   - return value: 0 = ok, NERF_ERR_* < 0 = argument error, > 0 = cudaError_t.
+ *   - there is no CPU fallback anywhere.
+ */
+#ifndef NERF_B200_H_
+#define NERF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NERF_OK 0
+#define NERF_ERR_BAD_ARG (-1)
+#define NERF_ERR_UNSUPPORTED (-2)
+#define NERF_ERR_WORKSPACE (-3)
+
+#define NERF_HIDDEN 256
+#define NERF_PE_X_OCTAVES 10
+#define NERF_PE_D_OCTAVES 6
+#define NERF_G1_LAYERS 10
+
+/* precision of the MLP contraction */
+#define NERF_PREC_FP32 0 /* fp32 FFMA tiles: the <=1e-3 parity mode            */
+#define NERF_PREC_BF16 1 /* tcgen05 kind::f16 (bf16 in, fp32 accumulate in TMEM) */
+
+int nerf_abi_version(void);
+/* Human readable name of the last CUDA error seen by this library (thread local). */
+const char* nerf_last_error(void);
+
+/* ------------------------------------------------------------------ rays --- */
+
+/* NeRF.generate_rays + rays_to_world_coordinates + the flatten in
+ * render_image (nerf/model.py:242-278, 336-367, 727-753) for the flattened ray
+ * ids [ray_begin, ray_end): id = (cam*H + row)*W + col.  cam_o [n_cams,3],
+ * cam_r [n_cams,3,3]; outputs [ray_end-ray_begin, 3].  Either output may be NULL. */
+int nerf_generate_rays(const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                       float focal, int64_t ray_begin, int64_t ray_end,
+                       float* rays_o, float* rays_d, void* stream);
+
+/* PixelRayDataset.__getitem__ + default collate for a whole batch
+ * (nerf/dataset.py:283-316): idx -> (image, row, col), gather pixel, pose,
+ * states; rotate the camera ray to world.  images [N,H,W,C] fp32, poses
+ * [N,3|4,4] (pose_rows = 3 or 4), states_x [N,Sx] or NULL.  idx int64 [B].
+ * Outputs: rays_o/rays_d [B,3], pixels [B,C], states_out [B,Sx] (or NULL),
+ * bhw int64 [B,3] = (image_bi, image_hi, image_wi) (or NULL). */
+int nerf_gather_pixel_rays(const float* images, const float* poses, int pose_rows,
+                           const float* states_x, int Sx, int N, int H, int W, int C,
+                           float focal, const int64_t* idx, int64_t B,
+                           float* rays_o, float* rays_d, float* pixels, float* states_out,
+                           int64_t* bhw, void* stream);
+
+/* G1 sampler: linspace(near, far, S) with the stratified jitter of
+ * NeRF.sample_along_rays (nerf/model.py:422-433).  u [B,S] uniforms in [0,1)
+ * or NULL; if u is NULL and jitter != 0 the uniforms come from Philox4x32-10
+ * keyed by (seed, ray_id_base + ray, sample).  t_base [S] (device) optionally
+ * supplies the un-jittered ladder (the host binding passes torch.linspace's own
+ * output so the bins are bit-identical to the reference's); NULL = computed in
+ * the kernel.  t_out [B,S]. */
+int nerf_sample_linear(float near_plane, float far_plane, const float* t_base, int S,
+                       int64_t B, const float* u, int jitter, uint64_t seed,
+                       int64_t ray_id_base, float* t_out, void* stream);
+
+/* HEAD sampler: 2^linspace(-9.43633744014, 0, S) * box_diag with the same
+ * jitter (nerf/model.py:412-435). */
+int nerf_sample_geometric(float box_diag, const float* t_base, int S, int64_t B,
+                          const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                          float* t_out, void* stream);
+
+/* Hierarchical inverse-CDF sampler (promised at nerf/model.py:191-193, never
+ * implemented there; NeRF paper sec. 5.2): per ray, n_fine draws from the pdf of
+ * the interior coarse weights over the midpoint bins, merged and sorted with the
+ * coarse t.  t [B,S], weights [B,S] -> t_out [B,S+n_fine] ascending.
+ * u_fine [B,n_fine] or NULL (= linspace(0,1,n_fine)). */
+int nerf_sample_pdf_merge(const float* t, const float* weights, int S, int n_fine,
+                          const float* u_fine, int64_t B, float* t_out, void* stream);
+
+/* G1 encoder (layout of NeRF.positional_encoding, nerf/model.py:235-240; SURVEY
+ * A.3): ex [B,S,20*(3+Sx)] from cat[(o+d t)/normalize, states_x], ed
+ * [B,12*(3+Sd)] from cat[d/|d|, states_d].  points_out [B,S,3] optional. */
+int nerf_encode_g1(const float* rays_o, const float* rays_d, const float* t,
+                   const float* states_x, int Sx, const float* states_d, int Sd,
+                   int64_t B, int S, float normalize_position, int normalize_direction,
+                   float* ex, float* ed, float* points_out, void* stream);
+
+/* ------------------------------------------------------------ compositing --- */
+
+/* NeRF.alpha_compositing_coefficients + the colour composite
+ * (nerf/model.py:462-469, 660) plus depth = sum w t and acc = sum w.
+ * sigma [B,S] (pre-relu, noise already added), rgb [B,S,3] (pre-sigmoid).
+ * Sample positions: either points [B,S,3] (exactly the reference's argument) or,
+ * when points == NULL, rays_o/rays_d [B,3] + t [B,S] (p = o + d t is rebuilt in
+ * registers with the reference's rounding).  t may be NULL only if depth is.
+ * Outputs (each optional): pixels [B,3], depth [B], acc [B], weights [B,S]. */
+int nerf_composite_fwd(const float* sigma, const float* rgb, const float* points,
+                       const float* rays_o, const float* rays_d, const float* t,
+                       int64_t B, int S, float* pixels, float* depth, float* acc,
+                       float* weights, void* stream);
+
+/* Backward of the above w.r.t. sigma and rgb (reverse-scan).  g_* are the
+ * incoming gradients (g_depth/g_acc/g_weights may be NULL).  d_sigma [B,S],
+ * d_rgb [B,S,3]. */
+int nerf_composite_bwd(const float* sigma, const float* rgb, const float* points,
+                       const float* rays_o, const float* rays_d, const float* t,
+                       int64_t B, int S, const float* g_pixels, const float* g_depth,
+                       const float* g_acc, const float* g_weights,
+                       float* d_sigma, float* d_rgb, void* stream);
+
+/* ------------------------------------------------------------------- MLP --- */
+
+/* Layout of the flat G1 parameter vector = state_dict order of
+ * examples/nerf.pth, generalised to Dx = 3+Sx position inputs and
+ * Dd = 3+Sd direction inputs.  offsets_host receives 44 element offsets in
+ * state_dict order; returns the total element count (638468 for Dx=Dd=3). */
+int64_t nerf_g1_param_layout(int Dx, int Dd, int64_t* offsets_host);
+
+/* Workspace (bytes) needed by nerf_g1_mlp_fwd for P points. */
+int64_t nerf_g1_mlp_workspace_bytes(int64_t P, int Dx, int Dd, int precision, int save_for_backward);
+
+/* The coordinate MLP of SURVEY A.3 (block_0 -> cat -> block_1 -> density;
+ * cat dir -> block_2 -> color): ex [P,20 Dx], ed [P/S,12 Dd] (one row per ray)
+ * -> sigma [P], rgb [P,3].  params = flat vector above.  With
+ * save_for_backward != 0 the workspace keeps what nerf_g1_mlp_bwd needs. */
+int nerf_g1_mlp_fwd(const float* params, const float* ex, const float* ed, int64_t P, int S,
+                    int Dx, int Dd, int precision, int save_for_backward,
+                    float* sigma, float* rgb, void* workspace, int64_t workspace_bytes,
+                    void* stream);
+
+/* Backward: d_sigma [P], d_rgb [P,3] -> ACCUMULATES into grads (flat, same layout
+ * as params).  Uses the workspace written by the matching forward call. */
+int nerf_g1_mlp_bwd(const float* params, const float* ex, const float* ed, int64_t P, int S,
+                    int Dx, int Dd, int precision, const float* d_sigma, const float* d_rgb,
+                    float* grads, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ----------------------------------------------------------------- fused --- */
+
+/* bytes of the bf16 weight image built by nerf_g1_pack_weights */
+int64_t nerf_g1_packed_bytes(int Dx, int Dd);
+/* fp32 flat params -> bf16 UMMA-ready (128B-swizzled, K-major) weight slabs with
+ * the previous LayerNorm's affine folded in, plus fp32 bias/head vectors. */
+int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* packed, void* stream);
+
+/* Fused render: ray-gen (or explicit rays) -> sample -> encode -> MLP (tcgen05)
+ * -> composite, nothing but rays in and pixels out through HBM.
+ * If rays_o/rays_d are NULL rays come from cam_o/cam_r/H/W/focal for ids
+ * [ray_begin, ray_begin+B).  out_pixels [B,3], out_depth/out_acc [B] optional,
+ * out_weights [B,S] optional (needed by the hierarchical sampler), t_in [B,S]
+ * optional explicit sample positions (else linspace(near,far,S) (+jitter from u)). */
+int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
+                         const float* rays_o, const float* rays_d,
+                         const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                         float focal, int64_t ray_begin, int64_t B, int S,
+                         float near_plane, float far_plane, const float* t_in, const float* u,
+                         const float* noise, const float* states_x, const float* states_d,
+                         float normalize_position, int normalize_direction,
+                         float* out_pixels, float* out_depth, float* out_acc,
+                         float* out_weights, float* out_sigma, float* out_rgb, void* stream);
+
+/* -------------------------------------------------------------- optimiser --- */
+
+/* torch.optim.Adam(lr, betas, eps) step over a flat buffer
+ * (train_conditional_nerf.py:106-107, 135): one launch for all 44 tensors.
+ * grad_scale multiplies the gradient first (1/world_size after an all-reduce). */
+int nerf_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq,
+                   int64_t n, int64_t step, float lr, float beta1, float beta2, float eps,
+                   float grad_scale, void* stream);
+
+/* mean((pixels - target)^2) and its gradient w.r.t. pixels
+ * (train_conditional_nerf.py:132): loss_out [1] (overwritten), g_pixels [B,3]. */
+int nerf_mse_loss(const float* pixels, const float* target, int64_t n, float* loss_out,
+                  float* g_pixels, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H_ */

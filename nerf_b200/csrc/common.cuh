@@ -1,0 +1,52 @@
+// Shared helpers for the nerf_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/nerf_b200.h"
+
+#define NERF_EPS_T 1e-10f      // nerf/model.py:469  (alpha + 1e-10 inside the cumprod)
+#define NERF_LAST_DIST 1e10f   // nerf/model.py:464  (last distance)
+#define NERF_LN_EPS 1e-5f      // torch.nn.LayerNorm default
+
+int nerf_set_error(cudaError_t e);   // records + returns (int)e
+#define NERF_CUDA_CHECK_LAUNCH() do { cudaError_t e__ = cudaGetLastError(); \
+    if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)
+#define NERF_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)
+
+static inline int nerf_num_sms() {
+    static int n = 0;
+    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+    return n;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- Philox4x32-10 (counter based; keyed by (seed), counter = (ray, sample)) ----
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+    uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
+    uint32_t hi1 = __umulhi(M1, c[2]), lo1 = M1 * c[2];
+    uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+    c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+__device__ __forceinline__ void philox4x32(uint64_t seed, uint64_t ctr_lo, uint32_t ctr_hi, uint32_t (&out)[4]) {
+    uint32_t c[4] = {(uint32_t)ctr_lo, (uint32_t)(ctr_lo >> 32), ctr_hi, 0u};
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) { philox_round(c, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
+}
+// uniform in [0,1) with 24 random bits (same grid as torch.rand for fp32)
+__device__ __forceinline__ float u01_from_bits(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+// torch.linspace(start, end, steps) element i in fp32 (ATen RangeFactories: symmetric halves)
+__device__ __forceinline__ float linspace_at(float start, float end, int steps, int i) {
+    if (steps == 1) return start;
+    float step = (end - start) / (float)(steps - 1);
+    return (i < steps / 2) ? __fadd_rn(start, __fmul_rn(step, (float)i))
+                           : __fsub_rn(end, __fmul_rn(step, (float)(steps - 1 - i)));
+}

@@ -1,0 +1,215 @@
+// fp32 FFMA tiles for the G1 coordinate MLP ("fp32 mode": the <=1e-3 parity path).
+// One kernel template does  C[64 x 256] = A[64 x K] * B  per CTA with
+//   MODE_FWD  : A = [gamma*n_prev+beta | seg2], B = W^T (W is [256][Kt] row-major),
+//               epilogue = +bias, ReLU, LayerNorm statistics, normalise  (the whole
+//               Linear->ReLU->LayerNorm unit of SURVEY A.3 without its affine, which
+//               the NEXT consumer applies when it loads the row)
+//   MODE_DGRAD: A = dz, B = W[:, :256] (natural), epilogue = plain store.
+#pragma once
+#include "common.cuh"
+
+#define HID NERF_HIDDEN
+#define BM 64
+#define BK 16
+#define A_STRIDE 68      // 64 + 4: keeps float4 alignment, <=2-way conflicts on the transposing store
+
+struct ASource {
+    const float* n_prev;     // [P,256] normalised activations of the previous unit (or null: K1 = 0)
+    const float* gamma;      // previous LayerNorm affine (applied on load)
+    const float* beta;
+    const float* seg2;       // extra input columns (PE of position: one row per point; PE of dir: one row per ray)
+    int K1, K2, row_div2;
+};
+
+__device__ __forceinline__ float4 load_a4(const ASource& s, int64_t row, int k, int64_t P) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row >= P) return v;
+    if (k < s.K1) {
+        float4 n = *reinterpret_cast<const float4*>(s.n_prev + row * HID + k);
+        float4 g = *reinterpret_cast<const float4*>(s.gamma + k);
+        float4 b = *reinterpret_cast<const float4*>(s.beta + k);
+        v.x = fmaf(g.x, n.x, b.x); v.y = fmaf(g.y, n.y, b.y); v.z = fmaf(g.z, n.z, b.z); v.w = fmaf(g.w, n.w, b.w);
+    } else if (k - s.K1 < s.K2) {
+        v = *reinterpret_cast<const float4*>(s.seg2 + (row / s.row_div2) * s.K2 + (k - s.K1));
+    }
+    return v;
+}
+
+enum { MODE_FWD = 0, MODE_DGRAD = 1 };
+
+template <int MODE>
+__global__ void __launch_bounds__(256) mlp_tile_kernel(
+        ASource src,                       // FWD: inputs; DGRAD: n_prev = dz, K1 = 256, gamma = null
+        const float* __restrict__ W, int Kt,        // weight [256][Kt]
+        const float* __restrict__ bias,             // FWD
+        float* __restrict__ out,                    // FWD: n_out [P,256]; DGRAD: G [P,256]
+        float* __restrict__ mu_out, float* __restrict__ rstd_out, int64_t P) {
+    __shared__ __align__(16) float As[2][BK][A_STRIDE];
+    __shared__ __align__(16) float Bs[2][BK][HID];
+    const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
+    const int64_t row0 = (int64_t)blockIdx.x * BM;
+    const int K = (MODE == MODE_FWD) ? (src.K1 + src.K2) : HID;
+    const int nchunks = (K + BK - 1) / BK;
+
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    float4 ra; float4 rb[4];
+    auto gload = [&](int chunk) {
+        const int k0 = chunk * BK;
+        {   // A tile: 64 rows x 16 k, one float4 per thread
+            const int r = tid >> 2, kq = (tid & 3) * 4;
+            if (MODE == MODE_FWD) ra = load_a4(src, row0 + r, k0 + kq, P);
+            else ra = (row0 + r < P) ? *reinterpret_cast<const float4*>(src.n_prev + (row0 + r) * HID + k0 + kq)
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (MODE == MODE_FWD) {     // B[k][n] = W[n][k]: thread = output feature n, 16 consecutive k
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int k = k0 + q * 4;
+                rb[q] = (k < Kt) ? *reinterpret_cast<const float4*>(W + (size_t)tid * Kt + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        } else {                    // B[kk][j] = W[n0+kk][j], j < 256: natural rows
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int idx = tid + q * 256; int kk = idx >> 6, j4 = (idx & 63) * 4;
+                rb[q] = *reinterpret_cast<const float4*>(W + (size_t)(k0 + kk) * Kt + j4);
+            }
+        }
+    };
+    auto sstore = [&](int buf) {
+        {
+            const int r = tid >> 2, kq = (tid & 3) * 4;
+            As[buf][kq + 0][r] = ra.x; As[buf][kq + 1][r] = ra.y; As[buf][kq + 2][r] = ra.z; As[buf][kq + 3][r] = ra.w;
+        }
+        if (MODE == MODE_FWD) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                Bs[buf][q * 4 + 0][tid] = rb[q].x; Bs[buf][q * 4 + 1][tid] = rb[q].y;
+                Bs[buf][q * 4 + 2][tid] = rb[q].z; Bs[buf][q * 4 + 3][tid] = rb[q].w;
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                int idx = tid + q * 256; int kk = idx >> 6, j4 = (idx & 63) * 4;
+                *reinterpret_cast<float4*>(&Bs[buf][kk][j4]) = rb[q];
+            }
+        }
+    };
+
+    gload(0); sstore(0); __syncthreads();
+    for (int c = 0; c < nchunks; ++c) {
+        const int buf = c & 1;
+        if (c + 1 < nchunks) gload(c + 1);
+#pragma unroll
+        for (int k = 0; k < BK; ++k) {
+            float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8]);
+            float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 8 + 4]);
+            float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+            float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][128 + tx * 4]);
+            const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        if (c + 1 < nchunks) { sstore(buf ^ 1); }
+        __syncthreads();
+    }
+
+    // ---- epilogue: thread owns rows ty*8..+7, columns tx*4..+3 and 128+tx*4..+3 ----
+    if (MODE == MODE_FWD) {
+        float bv[8];
+        { float4 b0 = *reinterpret_cast<const float4*>(bias + tx * 4), b1 = *reinterpret_cast<const float4*>(bias + 128 + tx * 4);
+          bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w; bv[4] = b1.x; bv[5] = b1.y; bv[6] = b1.z; bv[7] = b1.w; }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { float a = fmaxf(acc[i][j] + bv[j], 0.f); acc[i][j] = a; s += a; }
+            const float mean = warp_sum(s) * (1.0f / HID);
+            float q = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { float d = __fsub_rn(acc[i][j], mean); q = fmaf(d, d, q); }
+            const float var = warp_sum(q) * (1.0f / HID);
+            const float rstd = 1.0f / sqrtf(var + NERF_LN_EPS);
+            const int64_t row = row0 + ty * 8 + i;
+            if (row < P) {
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = __fmul_rn(__fsub_rn(acc[i][j], mean), rstd);
+                *reinterpret_cast<float4*>(out + row * HID + tx * 4) = make_float4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<float4*>(out + row * HID + 128 + tx * 4) = make_float4(o[4], o[5], o[6], o[7]);
+                if (tx == 0 && mu_out) { mu_out[row] = mean; rstd_out[row] = rstd; }
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int64_t row = row0 + ty * 8 + i;
+            if (row < P) {
+                *reinterpret_cast<float4*>(out + row * HID + tx * 4) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+                *reinterpret_cast<float4*>(out + row * HID + 128 + tx * 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+            }
+        }
+    }
+}
+
+// ---- weight gradient: dW[n][k] += sum_m dz[m][n] * x[m][k],  x = [gamma*n_prev+beta | seg2] ----
+// 64(n) x 64(k) tile per CTA, rows [m_begin, m_end) reduced in chunks of 16, atomics at the end.
+__global__ void __launch_bounds__(256) mlp_wgrad_kernel(
+        const float* __restrict__ dz, ASource src, int Kt, float* __restrict__ dW,
+        int64_t P, int64_t rows_per_split) {
+    __shared__ __align__(16) float As[2][BK][64];
+    __shared__ __align__(16) float Bs[2][BK][64];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int k0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
+    const int64_t m_begin = (int64_t)blockIdx.z * rows_per_split;
+    int64_t m_end = m_begin + rows_per_split; if (m_end > P) m_end = P;
+    if (m_begin >= m_end) return;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    const int lr = tid >> 4, lc = (tid & 15) * 4;     // loader: row within chunk, column group
+    float4 ra, rb;
+    auto gload = [&](int64_t m0) {
+        int64_t m = m0 + lr;
+        ra = (m < m_end) ? *reinterpret_cast<const float4*>(dz + m * HID + n0 + lc) : make_float4(0.f, 0.f, 0.f, 0.f);
+        rb = (m < m_end) ? load_a4(src, m, k0 + lc, P) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    auto sstore = [&](int buf) {
+        *reinterpret_cast<float4*>(&As[buf][lr][lc]) = ra;
+        *reinterpret_cast<float4*>(&Bs[buf][lr][lc]) = rb;
+    };
+    gload(m_begin); sstore(0); __syncthreads();
+    int buf = 0;
+    for (int64_t m0 = m_begin; m0 < m_end; m0 += BK) {
+        if (m0 + BK < m_end) gload(m0 + BK);
+#pragma unroll
+        for (int mm = 0; mm < BK; ++mm) {
+            float4 a = *reinterpret_cast<const float4*>(&As[buf][mm][ty * 4]);
+            float4 b = *reinterpret_cast<const float4*>(&Bs[buf][mm][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        if (m0 + BK < m_end) sstore(buf ^ 1);
+        __syncthreads();
+        buf ^= 1;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int n = n0 + ty * 4 + i, k = k0 + tx * 4 + j;
+            if (k < Kt) atomicAdd(dW + (size_t)n * Kt + k, acc[i][j]);
+        }
+}

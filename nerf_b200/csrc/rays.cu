@@ -1,0 +1,162 @@
+// Ray generation, world transform, stratified samplers, G1 positional encoder and
+// the batched PixelRayDataset gatherer.  HBM-bound, one thread per output element
+// group, coalesced stores.  Reference: nerf/model.py:242-278, 336-367, 412-435,
+// 216-240 (PE layout); nerf/dataset.py:283-316.
+#include "common.cuh"
+
+// ---------------------------------------------------------------- camera ray --
+// x = (col - 0.5 (W-1)) / f ; y = (row - 0.5 (H-1)) / f ; ray = (x, -y, -1)
+// (nerf/model.py:276-278), each op rounded separately like eager torch.
+__device__ __forceinline__ void camera_ray(int row, int col, int H, int W, float focal, float (&r)[3]) {
+    float cx = 0.5f * (float)(W - 1), cy = 0.5f * (float)(H - 1);   // python double -> fp32 scalar
+    r[0] = __fdiv_rn(__fsub_rn((float)col, cx), focal);
+    r[1] = -__fdiv_rn(__fsub_rn((float)row, cy), focal);
+    r[2] = -1.0f;
+}
+// d_i = sum_j R[i][j] ray[j]  ((camera_r * rays[..., None, :]).sum(-1), model.py:367)
+__device__ __forceinline__ void rotate_ray(const float* __restrict__ R, const float (&r)[3], float (&d)[3]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float p0 = __fmul_rn(R[i * 3 + 0], r[0]), p1 = __fmul_rn(R[i * 3 + 1], r[1]), p2 = __fmul_rn(R[i * 3 + 2], r[2]);
+        d[i] = __fadd_rn(__fadd_rn(p0, p1), p2);
+    }
+}
+
+__global__ void generate_rays_kernel(const float* __restrict__ cam_o, const float* __restrict__ cam_r,
+                                     int H, int W, float focal, int64_t ray_begin, int64_t n,
+                                     float* __restrict__ rays_o, float* __restrict__ rays_d) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int64_t id = ray_begin + i;
+    int col = (int)(id % W); int64_t q = id / W;
+    int row = (int)(q % H);  int cam = (int)(q / H);
+    float r[3], d[3];
+    camera_ray(row, col, H, W, focal, r);
+    rotate_ray(cam_r + (size_t)cam * 9, r, d);
+    if (rays_d) { rays_d[i * 3 + 0] = d[0]; rays_d[i * 3 + 1] = d[1]; rays_d[i * 3 + 2] = d[2]; }
+    if (rays_o) { rays_o[i * 3 + 0] = cam_o[cam * 3 + 0]; rays_o[i * 3 + 1] = cam_o[cam * 3 + 1]; rays_o[i * 3 + 2] = cam_o[cam * 3 + 2]; }
+}
+
+extern "C" int nerf_generate_rays(const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                  float focal, int64_t ray_begin, int64_t ray_end,
+                                  float* rays_o, float* rays_d, void* stream) {
+    if (!cam_o || !cam_r || n_cams <= 0 || H <= 0 || W <= 0 || !(focal != 0.0f)) return NERF_ERR_BAD_ARG;
+    if (ray_begin < 0 || ray_end < ray_begin || ray_end > (int64_t)n_cams * H * W) return NERF_ERR_BAD_ARG;
+    int64_t n = ray_end - ray_begin;
+    if (n == 0) return NERF_OK;
+    generate_rays_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        cam_o, cam_r, H, W, focal, ray_begin, n, rays_o, rays_d);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+// ------------------------------------------------------- dataset gatherer ----
+__global__ void gather_pixel_rays_kernel(const float* __restrict__ images, const float* __restrict__ poses,
+                                         int pose_rows, const float* __restrict__ states_x, int Sx,
+                                         int N, int H, int W, int C, float focal,
+                                         const int64_t* __restrict__ idx, int64_t B,
+                                         float* __restrict__ rays_o, float* __restrict__ rays_d,
+                                         float* __restrict__ pixels, float* __restrict__ states_out,
+                                         int64_t* __restrict__ bhw) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B) return;
+    int64_t id = idx[i];                       // dataset.py:283-291
+    int wi = (int)(id % W); id /= W;
+    int hi = (int)(id % H); id /= H;
+    int bi = (int)(id % N);
+    const float* pose = poses + (size_t)bi * pose_rows * 4;
+    float R[9], r[3], d[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) R[a * 3 + b] = pose[a * 4 + b];
+    camera_ray(hi, wi, H, W, focal, r);
+    rotate_ray(R, r, d);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { rays_o[i * 3 + a] = pose[a * 4 + 3]; rays_d[i * 3 + a] = d[a]; }
+    const float* px = images + (((size_t)bi * H + hi) * W + wi) * C;
+    for (int c = 0; c < C; ++c) pixels[i * C + c] = px[c];
+    if (states_out) for (int s = 0; s < Sx; ++s) states_out[i * Sx + s] = states_x[(size_t)bi * Sx + s];
+    if (bhw) { bhw[i * 3 + 0] = bi; bhw[i * 3 + 1] = hi; bhw[i * 3 + 2] = wi; }
+}
+
+extern "C" int nerf_gather_pixel_rays(const float* images, const float* poses, int pose_rows,
+                                      const float* states_x, int Sx, int N, int H, int W, int C,
+                                      float focal, const int64_t* idx, int64_t B,
+                                      float* rays_o, float* rays_d, float* pixels, float* states_out,
+                                      int64_t* bhw, void* stream) {
+    if (!images || !poses || !idx || !rays_o || !rays_d || !pixels) return NERF_ERR_BAD_ARG;
+    if ((pose_rows != 3 && pose_rows != 4) || N <= 0 || H <= 0 || W <= 0 || C <= 0 || B < 0) return NERF_ERR_BAD_ARG;
+    if (states_out && (!states_x || Sx <= 0)) return NERF_ERR_BAD_ARG;
+    if (B == 0) return NERF_OK;
+    gather_pixel_rays_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        images, poses, pose_rows, states_x, Sx, N, H, W, C, focal, idx, B, rays_o, rays_d, pixels, states_out, bhw);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+// ------------------------------------------------------------- samplers ------
+// mode 0: ladder = linspace(near, far, S);  mode 1: ladder = 2^linspace(lo, 0, S), result * scale
+__device__ __forceinline__ float ladder_at(const float* __restrict__ t_base, int mode, float a, float b, int S, int k) {
+    if (t_base) return t_base[k];
+    float v = linspace_at(a, b, S, k);
+    return mode == 0 ? v : exp2f(v);
+}
+
+__global__ void sample_stratified_kernel(const float* __restrict__ t_base, int mode, float a, float b,
+                                         float scale, int S, int64_t B, const float* __restrict__ u,
+                                         int jitter, uint64_t seed, int64_t ray_id_base,
+                                         float* __restrict__ t_out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // one thread per 4 samples
+    int64_t total = B * (int64_t)S;
+    int64_t e0 = i * 4;
+    if (e0 >= total) return;
+    float out[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        int64_t e = e0 + j;
+        if (e >= total) { out[j] = 0.f; continue; }
+        int64_t ray = e / S; int k = (int)(e - ray * S);
+        float tk = ladder_at(t_base, mode, a, b, S, k);
+        float v = tk;
+        if (jitter) {
+            // nerf/model.py:425-433: bins bounded by the midpoints of the ladder
+            float lo = tk, hi = tk;
+            if (k > 0)     lo = __fmul_rn(0.5f, __fadd_rn(tk, ladder_at(t_base, mode, a, b, S, k - 1)));
+            if (k < S - 1) hi = __fmul_rn(0.5f, __fadd_rn(ladder_at(t_base, mode, a, b, S, k + 1), tk));
+            float uu;
+            if (u) uu = u[e];
+            else { uint32_t r4[4]; philox4x32(seed, (uint64_t)(ray_id_base + ray), (uint32_t)(k >> 2), r4); uu = u01_from_bits(r4[k & 3]); }
+            v = __fadd_rn(lo, __fmul_rn(__fsub_rn(hi, lo), uu));
+        }
+        out[j] = (mode == 0) ? v : __fmul_rn(v, scale);
+    }
+    if (e0 + 3 < total && ((((uintptr_t)(t_out + e0)) & 15) == 0)) {
+        *reinterpret_cast<float4*>(t_out + e0) = make_float4(out[0], out[1], out[2], out[3]);
+    } else {
+        for (int j = 0; j < 4 && e0 + j < total; ++j) t_out[e0 + j] = out[j];
+    }
+}
+
+static int launch_sampler(const float* t_base, int mode, float a, float b, float scale, int S, int64_t B,
+                          const float* u, int jitter, uint64_t seed, int64_t ray_id_base, float* t_out, void* stream) {
+    if (S <= 0 || B < 0 || !t_out) return NERF_ERR_BAD_ARG;
+    if (B == 0) return NERF_OK;
+    int64_t groups = (B * (int64_t)S + 3) / 4;
+    sample_stratified_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        t_base, mode, a, b, scale, S, B, u, jitter, seed, ray_id_base, t_out);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int nerf_sample_linear(float near_plane, float far_plane, const float* t_base, int S,
+                                  int64_t B, const float* u, int jitter, uint64_t seed,
+                                  int64_t ray_id_base, float* t_out, void* stream) {
+    return launch_sampler(t_base, 0, near_plane, far_plane, 1.0f, S, B, u, jitter, seed, ray_id_base, t_out, stream);
+}
+
+extern "C" int nerf_sample_geometric(float box_diag, const float* t_base, int S, int64_t B,
+                                     const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                     float* t_out, void* stream) {
+    return launch_sampler(t_base, 1, -9.43633744014f, 0.0f, box_diag, S, B, u, jitter, seed, ray_id_base, t_out, stream);
+}

@@ -1,0 +1,260 @@
+"""Drop-in `NeRF` module: the method surface of the reference's nerf/model.py, with the
+bodies dispatching to the sm_100a kernels in libnerf_b200.so.
+
+Generations:
+  * G1  -- `NeRF(normalize_position=6.0)`; `render_rays(o, d, near, far, S, ...) -> [B,3]`;
+           the model examples/nerf.pth was saved from (example.ipynb cells 5-9).
+  * G2  -- `NeRF(normalize_position=, density_inputs=3+Sx)`;
+           `render_rays(..., states_x=) -> [B,stages,3]` (train_conditional_nerf.py:103-132).
+  * static helpers shared with HEAD: generate_rays, rays_to_world_coordinates,
+           alpha_compositing_coefficients, spherical_to_cartesian, get_rotation_matrix
+           (nerf/model.py:242-367, 437-469).
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from . import ops
+
+PE_X_OCTAVES, PE_D_OCTAVES, HIDDEN = 10, 6, 256
+
+
+def _unit(n_in, n_out):
+    return [nn.Linear(n_in, n_out), nn.ReLU(), nn.LayerNorm(n_out)]
+
+
+def g1_param_layout_py(dx, dd):
+    """Pure-python mirror of nerf_g1_param_layout (state_dict order of nerf.pth)."""
+    h, ex, ed = HIDDEN, 2 * PE_X_OCTAVES * dx, 2 * PE_D_OCTAVES * dd
+    sizes = [h, 1, 3 * h, 3]
+    for in0, units in ((ex, 4), (h + ex, 4), (h + ed, 2)):
+        for u in range(units):
+            sizes += [h * (in0 if u == 0 else h), h, h, h]
+    off, p = [], 0
+    for s in sizes:
+        off.append(p); p += s
+    return off, p
+
+
+class NeRF(nn.Module):
+
+    def __init__(self, normalize_position=1.0, density_inputs=None, color_inputs=None,
+                 hidden_size=HIDDEN, precision="fp32", normalize_direction=True,
+                 stages_axis=None, max_chunk_rays=32768):
+        super().__init__()
+        if hidden_size != HIDDEN:
+            raise ValueError("the sm_100a kernels are built for hidden_size=256 (examples/nerf.pth)")
+        if precision not in ops.PRECISIONS:
+            raise ValueError(f"precision must be one of {list(ops.PRECISIONS)}")
+        # G2 call sites pass density_inputs explicitly and expect a [B,stages,3] result
+        self.stages_axis = (density_inputs is not None) if stages_axis is None else bool(stages_axis)
+        self.normalize_position = float(normalize_position)
+        self.density_inputs = 3 if density_inputs is None else int(density_inputs)
+        self.color_inputs = 3 if color_inputs is None else int(color_inputs)
+        self.hidden_size = hidden_size
+        self.precision = precision
+        self.normalize_direction = bool(normalize_direction)
+        self.max_chunk_rays = int(max_chunk_rays)
+        ex = 2 * PE_X_OCTAVES * self.density_inputs
+        ed = 2 * PE_D_OCTAVES * self.color_inputs
+        h = hidden_size
+        # registration order == key order of examples/nerf.pth
+        self.density = nn.Linear(h, 1)
+        self.color = nn.Linear(h, 3)
+        self.block_0 = nn.Sequential(*(_unit(ex, h) + _unit(h, h) + _unit(h, h) + _unit(h, h)))
+        self.block_1 = nn.Sequential(*(_unit(h + ex, h) + _unit(h, h) + _unit(h, h) + _unit(h, h)))
+        self.block_2 = nn.Sequential(*(_unit(h + ed, h) + _unit(h, h)))
+        self._flat = None
+        self._ladders = {}
+        self._flatten()
+
+    # ---------------------------------------------------------- flat storage ----
+    def _flatten(self):
+        """Make the 44 parameters views of one contiguous fp32 vector (state_dict
+        order) so the kernels, the gradient all-reduce and Adam see a single buffer."""
+        params = list(self.parameters())
+        off, total = g1_param_layout_py(self.density_inputs, self.color_inputs)
+        assert len(params) == 44 and sum(p.numel() for p in params) == total
+        dev = params[0].device
+        flat = torch.empty(total, dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            for p, o in zip(params, off):
+                flat[o:o + p.numel()].copy_(p.detach().reshape(-1).float())
+                p.data = flat[o:o + p.numel()].view(p.shape)
+        self._flat, self._offsets = flat, off
+        return flat
+
+    def _flat_ok(self):
+        f = self._flat
+        if f is None:
+            return False
+        base = f.data_ptr()
+        for p, o in zip(self.parameters(), self._offsets):
+            if p.data_ptr() != base + 4 * o or p.device != f.device or p.dtype != torch.float32:
+                return False
+        return True
+
+    def flat_parameters(self):
+        if not self._flat_ok():
+            self._flatten()
+        return self._flat
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        self._flatten()
+        return out
+
+    # --------------------------------------------------------- static helpers ----
+    @staticmethod
+    def generate_rays(image_h, image_w, focal_length, dtype=torch.float32, device="cuda"):
+        """Camera-space rays [H,W,3] (reference nerf/model.py:242-278)."""
+        dev = torch.device(device)
+        cam_o = torch.zeros(1, 3, device=dev)
+        cam_r = torch.eye(3, device=dev).unsqueeze(0)
+        _, d = ops.generate_rays(cam_o, cam_r, image_h, image_w, focal_length)
+        return d.reshape(image_h, image_w, 3).to(dtype)
+
+    @staticmethod
+    def rays_to_world_coordinates(rays, camera_o, camera_r):
+        """(reference nerf/model.py:336-367) -- a 3x3 product per ray; host-side torch."""
+        return camera_o, (camera_r * rays.unsqueeze(-2)).sum(dim=-1)
+
+    @staticmethod
+    def spherical_to_cartesian(yaw, elevation):
+        """(reference nerf/model.py:280-306)"""
+        return torch.stack([torch.cos(yaw) * torch.cos(elevation),
+                            torch.sin(yaw) * torch.cos(elevation), torch.sin(elevation)], dim=-1)
+
+    @staticmethod
+    def get_rotation_matrix(eye_vector, up_vector):
+        """(reference nerf/model.py:308-334)"""
+        return torch.stack([torch.linalg.cross(eye_vector, up_vector, dim=-1), up_vector, -eye_vector], dim=-1)
+
+    @staticmethod
+    def direction_to_rotation_matrix(directions):
+        """G2 helper (train_conditional_nerf.py:86-87), source absent from the reference
+        tree; SURVEY A.4(4): camera looks along `directions`, up derived from world +z."""
+        eye = directions / torch.linalg.norm(directions, dim=-1, keepdim=True)
+        z = torch.zeros_like(eye); z[..., 2] = 1.0
+        right = torch.linalg.cross(eye, z, dim=-1)
+        degenerate = torch.linalg.norm(right, dim=-1, keepdim=True) < 1e-6
+        alt = torch.zeros_like(eye); alt[..., 1] = 1.0
+        right = torch.where(degenerate, torch.linalg.cross(eye, alt, dim=-1), right)
+        right = right / torch.linalg.norm(right, dim=-1, keepdim=True)
+        up = torch.linalg.cross(right, eye, dim=-1)
+        return NeRF.get_rotation_matrix(eye, up)
+
+    @staticmethod
+    def alpha_compositing_coefficients(points, density_outputs):
+        """Weights [...,S,1] (reference nerf/model.py:437-469) via the warp-scan kernel."""
+        shape = density_outputs.shape
+        s = shape[-2]
+        sigma = density_outputs.reshape(-1, s)
+        pts = points.reshape(-1, s, 3)
+        rgb = torch.zeros(sigma.shape[0], s, 3, device=sigma.device)
+        _, _, _, w = ops.composite(sigma, rgb, points=pts)
+        return w.reshape(shape)
+
+    # --------------------------------------------------------------- sampling ----
+    def _ladder(self, near, far, num_samples, device):
+        """torch.linspace's own output, so bins are bit-identical to the reference's."""
+        key = (float(near), float(far), int(num_samples), str(device))
+        if key not in self._ladders:
+            self._ladders[key] = torch.linspace(near, far, num_samples, dtype=torch.float32).to(device)
+        return self._ladders[key]
+
+    def sample_along_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
+                          randomly_sample=True, u=None):
+        b = rays_o.shape[0]
+        if randomly_sample and u is None:
+            u = torch.rand(b, num_samples, dtype=torch.float32, device=rays_o.device)
+        return ops.sample_linear(near, far, num_samples, b, rays_o.device, u=u if randomly_sample else None,
+                                 t_base=self._ladder(near, far, num_samples, rays_o.device))
+
+    # ---------------------------------------------------------------- network ----
+    def forward(self, rays_o, rays_d, samples, states_x=None, states_d=None):
+        """-> (points [B,S,3], density [B,S,1], color [B,S,3])."""
+        ex, ed, pts = ops.encode_g1(rays_o, rays_d, samples, self.normalize_position, states_x, states_d,
+                                    self.normalize_direction, want_points=True)
+        b, s = samples.shape
+        flat = self.flat_parameters()
+        sigma, rgb = ops.g1_mlp(ex.view(b * s, -1), ed, s, self.density_inputs, self.color_inputs,
+                                ops.PREC_FP32, flat, list(self.parameters()))
+        return pts, sigma.view(b, s, 1), rgb.view(b, s, 3)
+
+    def _render_chunk(self, rays_o, rays_d, near, far, num_samples, states_x, states_d, u, noise, t=None):
+        if t is None:
+            t = ops.sample_linear(near, far, num_samples, rays_o.shape[0], rays_o.device, u=u,
+                                  t_base=self._ladder(near, far, num_samples, rays_o.device))
+        _, sigma, rgb = self.forward(rays_o, rays_d, t, states_x, states_d)
+        if noise is not None:
+            sigma = sigma + noise
+        pixels, depth, acc, weights = ops.composite(sigma.squeeze(-1), rgb, rays_o=rays_o, rays_d=rays_d, t=t)
+        return dict(pixels=pixels, depth=depth, acc=acc, weights=weights, t=t,
+                    density=sigma, color=rgb)
+
+    def render_rays_full(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
+                         u=None, noise=None, t=None):
+        """All outputs of one pass (dict); `u`/`noise` are host-supplied draws (parity mode)."""
+        rays_o = rays_o.float().contiguous(); rays_d = rays_d.float().contiguous()
+        b = rays_o.shape[0]
+        if b <= self.max_chunk_rays:
+            return self._render_chunk(rays_o, rays_d, near, far, num_samples, states_x, states_d, u, noise, t)
+        outs = []
+        sl = lambda x, i: None if x is None else x[i:i + self.max_chunk_rays]
+        for i in range(0, b, self.max_chunk_rays):
+            outs.append(self._render_chunk(sl(rays_o, i), sl(rays_d, i), near, far, num_samples,
+                                           sl(states_x, i), sl(states_d, i), sl(u, i), sl(noise, i), sl(t, i)))
+        return {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
+
+    def render_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
+                    randomly_sample=False, density_noise_std=0.0):
+        """G1: -> pixels [B,3] (example.ipynb cell 8); G2: -> [B,stages,3]
+        (train_conditional_nerf.py:120-132).  RNG order follows the reference: rand for
+        the jitter, then randn for the density noise (drawn even when std == 0,
+        nerf/model.py:652-654)."""
+        b = rays_o.shape[0]
+        dev = rays_o.device
+        u = torch.rand(b, num_samples, dtype=torch.float32, device=dev) if randomly_sample else None
+        noise = torch.randn(b, num_samples, 1, dtype=torch.float32, device=dev) * density_noise_std
+        out = self.render_rays_full(rays_o, rays_d, near, far, num_samples, states_x, states_d,
+                                    u=u, noise=noise if density_noise_std != 0.0 else None)
+        pixels = out["pixels"]
+        return pixels.unsqueeze(-2) if self.stages_axis else pixels
+
+    def render_rays_hierarchical(self, rays_o, rays_d, near, far, num_coarse, num_fine,
+                                 states_x=None, states_d=None):
+        """64 coarse + num_fine inverse-CDF samples, fine pass over the sorted union (D3)."""
+        with torch.no_grad():
+            coarse = self.render_rays_full(rays_o, rays_d, near, far, num_coarse, states_x, states_d)
+            t_all = ops.sample_pdf_merge(coarse["t"], coarse["weights"], num_fine)
+        return self.render_rays_full(rays_o, rays_d, near, far, num_coarse + num_fine, states_x, states_d, t=t_all)
+
+    def render_image(self, camera_o, camera_r, image_h, image_w, focal_length, near, far, num_samples,
+                     states_x=None, states_d=None, max_chunk_size=None, num_fine=0,
+                     ray_begin=0, ray_end=None):
+        """-> [Bc,H,W,3] (example.ipynb cell 8 lines 29-37; flatten order and chunking
+        of nerf/model.py:748-770).  `ray_begin/ray_end` render a slice of the flattened
+        ray ids (multi-GPU sharding); then the result is [n,3]."""
+        bc = camera_o.shape[0]
+        total = bc * image_h * image_w
+        full = ray_begin == 0 and ray_end is None
+        ray_end = total if ray_end is None else ray_end
+        chunk = self.max_chunk_rays if max_chunk_size is None else int(max_chunk_size)
+        outs = []
+        for i in range(ray_begin, ray_end, chunk):
+            j = min(i + chunk, ray_end)
+            o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, i, j)
+            sx = sd = None
+            if states_x is not None or states_d is not None:
+                cam = torch.arange(i, j, device=o.device) // (image_h * image_w)
+                sx = None if states_x is None else states_x.float()[cam].contiguous()
+                sd = None if states_d is None else states_d.float()[cam].contiguous()
+            if num_fine > 0:
+                r = self.render_rays_hierarchical(o, d, near, far, num_samples, num_fine, sx, sd)
+            else:
+                r = self.render_rays_full(o, d, near, far, num_samples, sx, sd)
+            outs.append(r["pixels"])
+        img = torch.cat(outs, dim=0)
+        return img.reshape(bc, image_h, image_w, 3) if full else img

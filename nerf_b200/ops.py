@@ -1,0 +1,213 @@
+"""Host-side operators over the C ABI (include/nerf_b200.h).  PyTorch supplies device
+memory, streams and autograd plumbing only; all arithmetic is in libnerf_b200.so."""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import check, lib, ptr, stream
+
+PREC_FP32, PREC_BF16 = 0, 1
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
+HIDDEN = 256
+
+
+def _f32c(t):
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+# ------------------------------------------------------------------ rays -------
+def generate_rays(camera_o, camera_r, image_h, image_w, focal_length, ray_begin=0, ray_end=None):
+    """World-space rays of the flattened ids [ray_begin, ray_end) of render_image
+    (reference nerf/model.py:727-753)."""
+    camera_o, camera_r = _f32c(camera_o), _f32c(camera_r)
+    n_cams = camera_o.shape[0]
+    total = n_cams * image_h * image_w
+    ray_end = total if ray_end is None else ray_end
+    n = ray_end - ray_begin
+    o = torch.empty(n, 3, device=camera_o.device, dtype=torch.float32)
+    d = torch.empty(n, 3, device=camera_o.device, dtype=torch.float32)
+    check(lib().nerf_generate_rays(ptr(camera_o), ptr(camera_r), n_cams, image_h, image_w,
+                                   float(focal_length), ray_begin, ray_end, ptr(o), ptr(d), stream()),
+          "nerf_generate_rays")
+    return o, d
+
+
+def gather_pixel_rays(images, poses, focal_length, idx, states_x=None):
+    """Batched PixelRayDataset.__getitem__ (reference nerf/dataset.py:283-316)."""
+    images, poses = _f32c(images), _f32c(poses)
+    idx = idx.to(device=images.device, dtype=torch.int64).contiguous()
+    n, h, w, c = images.shape
+    b = idx.numel()
+    dev = images.device
+    o = torch.empty(b, 3, device=dev); d = torch.empty(b, 3, device=dev)
+    px = torch.empty(b, c, device=dev)
+    bhw = torch.empty(b, 3, device=dev, dtype=torch.int64)
+    sx = 0 if states_x is None else states_x.shape[-1]
+    st = None
+    if sx:
+        states_x = _f32c(states_x)
+        st = torch.empty(b, sx, device=dev)
+    check(lib().nerf_gather_pixel_rays(ptr(images), ptr(poses), poses.shape[1], ptr(states_x) if sx else None, sx,
+                                       n, h, w, c, float(focal_length), ptr(idx), b, ptr(o), ptr(d), ptr(px),
+                                       ptr(st), ptr(bhw), stream()), "nerf_gather_pixel_rays")
+    return o, d, px, st, bhw
+
+
+def sample_linear(near, far, num_samples, num_rays, device, u=None, jitter=False, seed=0,
+                  ray_id_base=0, t_base=None):
+    t = torch.empty(num_rays, num_samples, device=device, dtype=torch.float32)
+    u = _f32c(u)
+    check(lib().nerf_sample_linear(float(near), float(far), ptr(t_base), num_samples, num_rays, ptr(u),
+                                   int(bool(jitter) or u is not None), seed, ray_id_base, ptr(t), stream()),
+          "nerf_sample_linear")
+    return t
+
+
+def sample_geometric(box_diag, num_samples, num_rays, device, u=None, jitter=False, seed=0,
+                     ray_id_base=0, t_base=None):
+    t = torch.empty(num_rays, num_samples, device=device, dtype=torch.float32)
+    u = _f32c(u)
+    check(lib().nerf_sample_geometric(float(box_diag), ptr(t_base), num_samples, num_rays, ptr(u),
+                                      int(bool(jitter) or u is not None), seed, ray_id_base, ptr(t), stream()),
+          "nerf_sample_geometric")
+    return t
+
+
+def sample_pdf_merge(t, weights, num_fine, u_fine=None):
+    t, weights, u_fine = _f32c(t), _f32c(weights.detach()), _f32c(u_fine)
+    b, s = t.shape
+    out = torch.empty(b, s + num_fine, device=t.device, dtype=torch.float32)
+    check(lib().nerf_sample_pdf_merge(ptr(t), ptr(weights), s, num_fine, ptr(u_fine), b, ptr(out), stream()),
+          "nerf_sample_pdf_merge")
+    return out
+
+
+def encode_g1(rays_o, rays_d, t, normalize_position, states_x=None, states_d=None,
+              normalize_direction=True, want_points=False):
+    rays_o, rays_d, t = _f32c(rays_o), _f32c(rays_d), _f32c(t)
+    b, s = t.shape
+    sx = 0 if states_x is None else states_x.shape[-1]
+    sd = 0 if states_d is None else states_d.shape[-1]
+    states_x = _f32c(states_x) if sx else None
+    states_d = _f32c(states_d) if sd else None
+    dev = t.device
+    ex = torch.empty(b, s, 20 * (3 + sx), device=dev)
+    ed = torch.empty(b, 12 * (3 + sd), device=dev)
+    pts = torch.empty(b, s, 3, device=dev) if want_points else None
+    check(lib().nerf_encode_g1(ptr(rays_o), ptr(rays_d), ptr(t), ptr(states_x), sx, ptr(states_d), sd,
+                               b, s, float(normalize_position), int(normalize_direction),
+                               ptr(ex), ptr(ed), ptr(pts), stream()), "nerf_encode_g1")
+    return ex, ed, pts
+
+
+# ------------------------------------------------------------ compositing ------
+class _Composite(torch.autograd.Function):
+    """pixels/depth/acc/weights = composite(sigma, rgb | geometry); reference
+    nerf/model.py:462-469, 660.  Geometry carries no gradient."""
+
+    @staticmethod
+    def forward(ctx, sigma, rgb, points, rays_o, rays_d, t):
+        sigma, rgb = _f32c(sigma), _f32c(rgb)
+        b, s = sigma.shape
+        dev = sigma.device
+        pixels = torch.empty(b, 3, device=dev); depth = torch.empty(b, device=dev) if t is not None else None
+        acc = torch.empty(b, device=dev); weights = torch.empty(b, s, device=dev)
+        check(lib().nerf_composite_fwd(ptr(sigma), ptr(rgb), ptr(points), ptr(rays_o), ptr(rays_d), ptr(t),
+                                       b, s, ptr(pixels), ptr(depth), ptr(acc), ptr(weights), stream()),
+              "nerf_composite_fwd")
+        ctx.save_for_backward(sigma, rgb, points, rays_o, rays_d, t)
+        if depth is None:
+            depth = torch.zeros(b, device=dev)
+        return pixels, depth, acc, weights
+
+    @staticmethod
+    def backward(ctx, g_pixels, g_depth, g_acc, g_weights):
+        sigma, rgb, points, rays_o, rays_d, t = ctx.saved_tensors
+        b, s = sigma.shape
+        d_sigma = torch.empty_like(sigma); d_rgb = torch.empty_like(rgb)
+        g_pixels, g_acc, g_weights = _f32c(g_pixels), _f32c(g_acc), _f32c(g_weights)
+        g_depth = _f32c(g_depth) if t is not None else None
+        check(lib().nerf_composite_bwd(ptr(sigma), ptr(rgb), ptr(points), ptr(rays_o), ptr(rays_d), ptr(t),
+                                       b, s, ptr(g_pixels), ptr(g_depth), ptr(g_acc), ptr(g_weights),
+                                       ptr(d_sigma), ptr(d_rgb), stream()), "nerf_composite_bwd")
+        return d_sigma, d_rgb, None, None, None, None
+
+
+def composite(sigma, rgb, points=None, rays_o=None, rays_d=None, t=None):
+    """sigma [B,S], rgb [B,S,3]; positions from points [B,S,3] or (rays_o, rays_d, t).
+    Returns pixels [B,3], depth [B], acc [B], weights [B,S]."""
+    return _Composite.apply(sigma, rgb, _f32c(points), _f32c(rays_o), _f32c(rays_d), _f32c(t))
+
+
+# --------------------------------------------------------------------- MLP -----
+def g1_param_layout(dx, dd):
+    off = (ctypes.c_int64 * 44)()
+    total = lib().nerf_g1_param_layout(dx, dd, off)
+    if total < 0:
+        raise ValueError("bad Dx/Dd")
+    return list(off), int(total)
+
+
+class _G1MLP(torch.autograd.Function):
+    """sigma [P], rgb [P,3] = MLP(ex [P,20Dx], ed [P/S,12Dd]); SURVEY A.3.  `flat` is
+    the flat fp32 parameter vector the 44 `params` alias; grads are produced in one
+    flat buffer and handed back as 44 views (one all-reduce / one Adam launch)."""
+
+    @staticmethod
+    def forward(ctx, ex, ed, samples_per_ray, dx, dd, precision, flat, *params):
+        p = ex.shape[0]
+        need_grad = any(q.requires_grad for q in params) and torch.is_grad_enabled()
+        nbytes = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, precision, int(need_grad))
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=ex.device)
+        sigma = torch.empty(p, device=ex.device); rgb = torch.empty(p, 3, device=ex.device)
+        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), p, samples_per_ray, dx, dd, precision,
+                                    int(need_grad), ptr(sigma), ptr(rgb), ptr(ws), nbytes, stream()),
+              "nerf_g1_mlp_fwd")
+        ctx.save_for_backward(ex, ed, flat, ws)
+        ctx.cfg = (samples_per_ray, dx, dd, precision, [tuple(q.shape) for q in params], nbytes)
+        return sigma, rgb
+
+    @staticmethod
+    def backward(ctx, d_sigma, d_rgb):
+        ex, ed, flat, ws = ctx.saved_tensors
+        s, dx, dd, precision, shapes, nbytes = ctx.cfg
+        p = ex.shape[0]
+        grads = torch.zeros_like(flat)
+        d_sigma = _f32c(d_sigma) if d_sigma is not None else torch.zeros(p, device=ex.device)
+        d_rgb = _f32c(d_rgb) if d_rgb is not None else torch.zeros(p, 3, device=ex.device)
+        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), p, s, dx, dd, precision, ptr(d_sigma),
+                                    ptr(d_rgb), ptr(grads), ptr(ws), nbytes, stream()), "nerf_g1_mlp_bwd")
+        off, _ = g1_param_layout(dx, dd)
+        views = tuple(grads[o:o + _numel(sh)].view(sh) for o, sh in zip(off, shapes))
+        return (None, None, None, None, None, None, None) + views
+
+
+def _numel(shape):
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+def g1_mlp(ex, ed, samples_per_ray, dx, dd, precision, flat, params):
+    return _G1MLP.apply(ex, ed, samples_per_ray, dx, dd, precision, flat, *params)
+
+
+# ---------------------------------------------------------------- optimiser ----
+def adam_step(flat_param, flat_grad, exp_avg, exp_avg_sq, step, lr=1e-4, betas=(0.9, 0.999), eps=1e-8,
+              grad_scale=1.0):
+    check(lib().nerf_adam_step(ptr(flat_param), ptr(flat_grad), ptr(exp_avg), ptr(exp_avg_sq), flat_param.numel(),
+                               step, lr, betas[0], betas[1], eps, grad_scale, stream()), "nerf_adam_step")
+
+
+def mse_loss(pixels, target, want_grad=True):
+    pixels, target = _f32c(pixels), _f32c(target)
+    loss = torch.empty(1, device=pixels.device)
+    g = torch.empty_like(pixels) if want_grad else None
+    check(lib().nerf_mse_loss(ptr(pixels), ptr(target), pixels.numel(), ptr(loss), ptr(g), stream()), "nerf_mse_loss")
+    return loss, g
