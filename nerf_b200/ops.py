@@ -161,7 +161,7 @@ class _G1MLP(torch.autograd.Function):
     @staticmethod
     def forward(ctx, ex, ed, samples_per_ray, dx, dd, precision, flat, *params):
         p = ex.shape[0]
-        need_grad = any(q.requires_grad for q in params) and torch.is_grad_enabled()
+        need_grad = any(ctx.needs_input_grad)
         nbytes = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, precision, int(need_grad))
         ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=ex.device)
         sigma = torch.empty(p, device=ex.device); rgb = torch.empty(p, 3, device=ex.device)

@@ -35,7 +35,8 @@ def positional_encoding(v, octaves):
     """sin/cos features, layout of /root/reference/nerf/model.py:235-240:
     per coordinate ``[sin(v f_0..f_{L-1}) | cos(v f_0..f_{L-1})]``, then flatten.
     Frequencies f_j = pi * 2^j."""
-    freq = (2.0 ** torch.arange(octaves, dtype=v.dtype, device=v.device)) * np.pi
+    # exact powers of two (torch.pow is not exact on every CPU), times float32(pi)
+    freq = torch.tensor([2.0 ** j for j in range(octaves)], dtype=v.dtype, device=v.device) * np.pi
     arg = v.unsqueeze(-1) * freq
     emb = torch.cat([torch.sin(arg), torch.cos(arg)], dim=-1)
     return torch.flatten(emb, start_dim=-2, end_dim=-1)
