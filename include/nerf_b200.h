@@ -82,6 +82,11 @@ int nerf_sample_geometric(float box_diag, const float* t_base, int S, int64_t B,
                           const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
                           float* t_out, void* stream);
 
+/* density noise of the training pass (nerf/model.py:652-654): sigma [B,S] +=
+ * N(0,1)*std in place, Philox4x32-10 keyed by (seed, ray_id_base + ray, sample). */
+int nerf_add_density_noise(float* sigma, int S, int64_t B, float std, uint64_t seed,
+                           int64_t ray_id_base, void* stream);
+
 /* Hierarchical inverse-CDF sampler (promised at nerf/model.py:191-193, never
  * implemented there; NeRF paper sec. 5.2): per ray, n_fine draws from the pdf of
  * the interior coarse weights over the midpoint bins, merged and sorted with the

@@ -24,6 +24,7 @@ SIGNATURES = {
                                      c_p, c_p, c_p, c_p, c_p, c_p]),
     "nerf_sample_linear": (c_i, [c_f, c_f, c_p, c_i, c_l, c_p, c_i, c_u64, c_l, c_p, c_p]),
     "nerf_sample_geometric": (c_i, [c_f, c_p, c_i, c_l, c_p, c_i, c_u64, c_l, c_p, c_p]),
+    "nerf_add_density_noise": (c_i, [c_p, c_i, c_l, c_f, c_u64, c_l, c_p]),
     "nerf_sample_pdf_merge": (c_i, [c_p, c_p, c_i, c_i, c_p, c_l, c_p, c_p]),
     "nerf_encode_g1": (c_i, [c_p, c_p, c_p, c_p, c_i, c_p, c_i, c_l, c_i, c_f, c_i, c_p, c_p, c_p, c_p]),
     "nerf_composite_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p]),

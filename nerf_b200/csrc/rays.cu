@@ -160,3 +160,37 @@ extern "C" int nerf_sample_geometric(float box_diag, const float* t_base, int S,
                                      float* t_out, void* stream) {
     return launch_sampler(t_base, 1, -9.43633744014f, 0.0f, box_diag, S, B, u, jitter, seed, ray_id_base, t_out, stream);
 }
+
+// ------------------------------------------------------- density noise -------
+// sigma += N(0,1) * std  (nerf/model.py:652-654), counter-based so that a ray's
+// noise does not depend on how rays are sharded: Philox keyed by (seed ^ tag,
+// global ray id, sample/4), Box-Muller on pairs.
+__global__ void density_noise_kernel(float* __restrict__ sigma, int S, int64_t B, float std,
+                                     uint64_t seed, int64_t ray_id_base) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;     // one thread per 4 samples of a ray
+    const int groups = (S + 3) / 4;
+    if (i >= B * groups) return;
+    int64_t ray = i / groups; int g = (int)(i - ray * groups);
+    uint32_t r4[4];
+    philox4x32(seed ^ 0x6E6F697365ull, (uint64_t)(ray_id_base + ray), (uint32_t)g, r4);
+    float z[4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float u1 = ((float)(r4[2 * h] >> 8) + 1.0f) * (1.0f / 16777216.0f);     // (0,1]
+        float u2 = u01_from_bits(r4[2 * h + 1]);
+        float rad = sqrtf(-2.0f * logf(u1)), sn, cs;
+        sincospif(2.0f * u2, &sn, &cs);
+        z[2 * h] = rad * cs; z[2 * h + 1] = rad * sn;
+    }
+    for (int j = 0; j < 4; ++j) { int k = g * 4 + j; if (k < S) sigma[ray * S + k] += z[j] * std; }
+}
+
+extern "C" int nerf_add_density_noise(float* sigma, int S, int64_t B, float std, uint64_t seed,
+                                      int64_t ray_id_base, void* stream) {
+    if (!sigma || S <= 0 || B < 0) return NERF_ERR_BAD_ARG;
+    if (B == 0 || std == 0.0f) return NERF_OK;
+    int64_t n = B * ((S + 3) / 4);
+    density_noise_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(sigma, S, B, std, seed, ray_id_base);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}

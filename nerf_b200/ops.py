@@ -78,6 +78,14 @@ def sample_geometric(box_diag, num_samples, num_rays, device, u=None, jitter=Fal
     return t
 
 
+def add_density_noise_(sigma, std, seed=0, ray_id_base=0):
+    """In place sigma [B,S] += N(0,1)*std with the counter-based generator."""
+    b, s = sigma.shape
+    check(lib().nerf_add_density_noise(ptr(sigma), s, b, float(std), seed, ray_id_base, stream()),
+          "nerf_add_density_noise")
+    return sigma
+
+
 def sample_pdf_merge(t, weights, num_fine, u_fine=None):
     t, weights, u_fine = _f32c(t), _f32c(weights.detach()), _f32c(u_fine)
     b, s = t.shape

@@ -1,0 +1,90 @@
+"""The fused training step (reference loop body: train_conditional_nerf.py:120-135,
+example.ipynb cell 8 lines 10-23) without autograd: sample -> encode -> MLP ->
+noise -> composite -> MSE -> composite backward -> MLP backward -> [all-reduce] -> Adam.
+Every arithmetic stage is one of our kernels; torch only owns memory, streams and
+(multi-GPU) the NCCL all-reduce of the flat gradient buffer."""
+import torch
+import torch.distributed as dist
+
+from . import ops
+from ._lib import check, lib, ptr, stream
+
+
+class Trainer:
+    def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, near=2.0, far=6.0,
+                 num_samples=64, density_noise_std=1.0, randomly_sample=True, seed=0,
+                 precision=None, process_group=None):
+        self.model = model
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.near, self.far, self.num_samples = near, far, num_samples
+        self.noise_std, self.jitter, self.seed = density_noise_std, randomly_sample, seed
+        self.precision = ops.PRECISIONS[precision or model.precision]
+        self.group = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if self.world > 1 else 0
+        flat = model.flat_parameters()
+        self.flat_grad = torch.zeros_like(flat)
+        self.exp_avg = torch.zeros_like(flat)
+        self.exp_avg_sq = torch.zeros_like(flat)
+        self.step_count = 0
+        self.rays_seen = 0
+        self._ws = None
+        self.kernel_launches = 0        # kernels launched by the last step() (our .so only)
+
+    def _workspace(self, p):
+        dx, dd = self.model.density_inputs, self.model.color_inputs
+        n = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, self.precision, 1)
+        if self._ws is None or self._ws.numel() < n:
+            self._ws = torch.empty(n, dtype=torch.uint8, device=self.model.flat_parameters().device)
+        return self._ws, n
+
+    def step(self, rays_o, rays_d, target, states_x=None, states_d=None, u=None, noise=None,
+             apply_update=True):
+        """One optimisation step on a ray batch resident on the device.  Returns the loss
+        (1-element device tensor; reading it is the caller's device->host sync)."""
+        m = self.model
+        flat = m.flat_parameters()
+        b, s = rays_o.shape[0], self.num_samples
+        dx, dd = m.density_inputs, m.color_inputs
+        dev = flat.device
+        ray_base = self.rays_seen * self.world + self.rank * b      # global ray id for the counter RNG
+        launches = 0
+        t = ops.sample_linear(self.near, self.far, s, b, dev, u=u, jitter=self.jitter and u is None,
+                              seed=self.seed, ray_id_base=ray_base, t_base=m._ladder(self.near, self.far, s, dev))
+        launches += 1
+        ex, ed, _ = ops.encode_g1(rays_o, rays_d, t, m.normalize_position, states_x, states_d, m.normalize_direction)
+        launches += 2
+        ws, nbytes = self._workspace(b * s)
+        sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
+        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd, self.precision, 1,
+                                    ptr(sigma), ptr(rgb), ptr(ws), nbytes, stream()), "nerf_g1_mlp_fwd")
+        launches += 12
+        if noise is not None:
+            sigma += noise.view(b, s)
+        elif self.noise_std != 0.0:
+            ops.add_density_noise_(sigma, self.noise_std, self.seed, ray_base); launches += 1
+        pixels = torch.empty(b, 3, device=dev)
+        check(lib().nerf_composite_fwd(ptr(sigma), ptr(rgb), None, ptr(rays_o), ptr(rays_d), ptr(t), b, s,
+                                       ptr(pixels), None, None, None, stream()), "nerf_composite_fwd")
+        loss, g_pixels = ops.mse_loss(pixels, target)
+        d_sigma = torch.empty_like(sigma); d_rgb = torch.empty_like(rgb)
+        check(lib().nerf_composite_bwd(ptr(sigma), ptr(rgb), None, ptr(rays_o), ptr(rays_d), ptr(t), b, s,
+                                       ptr(g_pixels), None, None, None, ptr(d_sigma), ptr(d_rgb), stream()),
+              "nerf_composite_bwd")
+        launches += 3
+        self.flat_grad.zero_()
+        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd, self.precision,
+                                    ptr(d_sigma), ptr(d_rgb), ptr(self.flat_grad), ptr(ws), nbytes, stream()),
+              "nerf_g1_mlp_bwd")
+        launches += 29
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, group=self.group)        # one NCCL all-reduce of 2.55 MB
+        if apply_update:
+            self.step_count += 1
+            ops.adam_step(flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.step_count, self.lr,
+                          self.betas, self.eps, grad_scale=1.0 / self.world)
+            launches += 1
+        self.rays_seen += b
+        self.kernel_launches = launches
+        self.last_pixels = pixels
+        return loss
