@@ -160,21 +160,40 @@ int64_t nerf_g1_packed_bytes(int Dx, int Dd);
  * the previous LayerNorm's affine folded in, plus fp32 bias/head vectors. */
 int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* packed, void* stream);
 
-/* Fused render: ray-gen (or explicit rays) -> sample -> encode -> MLP (tcgen05)
- * -> composite, nothing but rays in and pixels out through HBM.
- * If rays_o/rays_d are NULL rays come from cam_o/cam_r/H/W/focal for ids
- * [ray_begin, ray_begin+B).  out_pixels [B,3], out_depth/out_acc [B] optional,
- * out_weights [B,S] optional (needed by the hierarchical sampler), t_in [B,S]
- * optional explicit sample positions (else linspace(near,far,S) (+jitter from u)). */
+/* Workspace of nerf_g1_render_fused: t, sigma, rgb per point and rays per ray. */
+int64_t nerf_g1_render_workspace_bytes(int64_t B, int S);
+
+/* Fused render (tcgen05 path): ray-gen (or explicit rays) -> stratified sample -> encode ->
+ * MLP, one persistent kernel whose activations never leave the SM, then the compositing
+ * kernel; replaces the body of NeRF.render_rays / one chunk of NeRF.render_image
+ * (nerf/model.py:596-668, 727-761).
+ * Rays: rays_o/rays_d [B,3], or both NULL -> camera rays of the flattened ids
+ * [ray_begin, ray_begin+B) from cam_o [n_cams,3], cam_r [n_cams,3,3], H, W, focal.
+ * Samples: t_in [B,S] if given, else the ladder t_base [S] (NULL: linspace(near,far,S)
+ * computed in-kernel) with jitter from u [B,S] or, when u == NULL and jitter != 0, from
+ * Philox keyed by (seed, ray_id_base + ray, sample).
+ * Density noise: noise_std != 0 adds Philox N(0,1)*std to sigma before compositing.
+ * Outputs (each optional): out_pixels [B,3], out_depth/out_acc [B], out_weights [B,S],
+ * out_t [B,S], out_sigma [B,S] (after noise), out_rgb [B,S,3].  Needs S >= 32. */
 int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                          const float* rays_o, const float* rays_d,
                          const float* cam_o, const float* cam_r, int n_cams, int H, int W,
                          float focal, int64_t ray_begin, int64_t B, int S,
-                         float near_plane, float far_plane, const float* t_in, const float* u,
-                         const float* noise, const float* states_x, const float* states_d,
+                         float near_plane, float far_plane, const float* t_base, const float* t_in,
+                         const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                         const float* noise, float noise_std,
                          float normalize_position, int normalize_direction,
-                         float* out_pixels, float* out_depth, float* out_acc,
-                         float* out_weights, float* out_sigma, float* out_rgb, void* stream);
+                         float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
+                         float* out_t, float* out_sigma, float* out_rgb,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Test hook: the tcgen05 MLP alone on explicit rays and sample positions t [B,S]; when dbg
+ * != NULL the normalised output of unit dbg_layer (fp32, [B*S,256]) is written there.
+ * scratch_t [B,S] is overwritten. */
+int nerf_g1_mlp_tc_debug(const void* packed, const float* rays_o, const float* rays_d, const float* t,
+                         int64_t B, int S, float normalize_position, int normalize_direction,
+                         float* out_sigma, float* out_rgb, float* scratch_t, float* dbg, int dbg_layer,
+                         void* stream);
 
 /* -------------------------------------------------------------- optimiser --- */
 

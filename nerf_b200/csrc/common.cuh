@@ -50,3 +50,22 @@ __device__ __forceinline__ float linspace_at(float start, float end, int steps, 
     return (i < steps / 2) ? __fadd_rn(start, __fmul_rn(step, (float)i))
                            : __fsub_rn(end, __fmul_rn(step, (float)(steps - 1 - i)));
 }
+
+// ---------------------------------------------------------------- camera ray --
+// x = (col - 0.5 (W-1)) / f ; y = (row - 0.5 (H-1)) / f ; ray = (x, -y, -1)
+// (nerf/model.py:276-278), each op rounded separately like eager torch.
+__device__ __forceinline__ void camera_ray(int row, int col, int H, int W, float focal, float (&r)[3]) {
+    float cx = 0.5f * (float)(W - 1), cy = 0.5f * (float)(H - 1);   // python double -> fp32 scalar
+    r[0] = __fdiv_rn(__fsub_rn((float)col, cx), focal);
+    r[1] = -__fdiv_rn(__fsub_rn((float)row, cy), focal);
+    r[2] = -1.0f;
+}
+// d_i = sum_j R[i][j] ray[j]  ((camera_r * rays[..., None, :]).sum(-1), model.py:367)
+__device__ __forceinline__ void rotate_ray(const float* __restrict__ R, const float (&r)[3], float (&d)[3]) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float p0 = __fmul_rn(R[i * 3 + 0], r[0]), p1 = __fmul_rn(R[i * 3 + 1], r[1]), p2 = __fmul_rn(R[i * 3 + 2], r[2]);
+        d[i] = __fadd_rn(__fadd_rn(p0, p1), p2);
+    }
+}
+

@@ -1,7 +1,202 @@
-// tcgen05 fused path (placeholder until the kernel lands)
-#include "common.cuh"
-extern "C" int64_t nerf_g1_packed_bytes(int Dx, int Dd) { (void)Dx; (void)Dd; return 0; }
-extern "C" int nerf_g1_pack_weights(const float*, int, int, void*, void*) { return NERF_ERR_UNSUPPORTED; }
-extern "C" int nerf_g1_render_fused(const void*, int, int, const float*, const float*, const float*, const float*, int, int, int,
-                         float, int64_t, int64_t, int, float, float, const float*, const float*, const float*, const float*,
-                         const float*, float, int, float*, float*, float*, float*, float*, float*, void*) { return NERF_ERR_UNSUPPORTED; }
+// tcgen05 fused path: kernel body (roles) and the C entry points built on it.
+#include "tc_fused_kernel.cuh"
+
+__global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = tc::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;                 // SW128 slabs need 1024 B alignment
+    uint8_t* sm = smem_raw + (base - raw);
+    float* vec_s = reinterpret_cast<float*>(sm + SM_VEC);
+    const uint32_t bar0 = base + SM_BAR;
+    // barriers: ring_full[R], ring_empty[R], act_ready[2], acc_ready[2]; then the TMEM base slot
+    auto ring_full = [&](int s) { return bar0 + 8u * s; };
+    auto ring_empty = [&](int s) { return bar0 + 8u * (TC_RING + s); };
+    auto act_ready = [&](int x) { return bar0 + 8u * (2 * TC_RING + x); };
+    auto acc_ready = [&](int x) { return bar0 + 8u * (2 * TC_RING + 2 + x); };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 4));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int G = gridDim.x;
+    const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + G - 1) / G : 0;
+    const int cnt0 = (n_my + 1) >> 1, cnt1 = n_my >> 1;           // tiles of slot 0 / slot 1
+
+    for (int i = threadIdx.x; i < TC_VEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[i];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), 1); tc::mbar_init(ring_empty(s), 1); }
+        for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), 128); tc::mbar_init(acc_ready(x), 1); }
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc(tc::smem_u32((const void*)tmem_slot), 512);
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int q = 0; q < cnt0; ++q)
+                for (int l = 0; l < 10; ++l)
+                    for (int x = 0; x < 2; ++x) {
+                        if (x == 1 && q >= cnt1) continue;
+                        const int ns = 2 * a.nk[l];
+                        const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
+                        for (int s = 0; s < ns; ++s, ++it) {
+                            const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                            tc::mbar_wait(ring_empty(slot), ph ^ 1);
+                            tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
+                            tc::tma_load_1d(base + SM_RING + slot * TC_STAGE_BYTES, src + (size_t)s * TC_STAGE_BYTES,
+                                            TC_STAGE_BYTES, ring_full(slot));
+                        }
+                    }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = tc::umma_idesc_bf16(128, 128);
+            uint32_t it = 0, act_it[2] = {0, 0};
+            for (int q = 0; q < cnt0; ++q)
+                for (int l = 0; l < 10; ++l)
+                    for (int x = 0; x < 2; ++x) {
+                        if (x == 1 && q >= cnt1) continue;
+                        tc::mbar_wait(act_ready(x), act_it[x] & 1); ++act_it[x];
+                        tc::tcgen05_fence_after();
+                        const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
+                        const int nk = a.nk[l];
+                        for (int ks = 0; ks < nk; ++ks) {
+                            const uint32_t a_addr = (l == 0 || ks >= 4) ? pe_addr : act_addr + ks * TC_SLAB_BYTES;
+                            for (int nh = 0; nh < 2; ++nh, ++it) {
+                                const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                                tc::mbar_wait(ring_full(slot), ph);
+                                tc::tcgen05_fence_after();
+                                const uint32_t b_addr = base + SM_RING + slot * TC_STAGE_BYTES;
+                                const uint32_t d_tmem = tmem_base + x * 256 + nh * 128;
+#pragma unroll
+                                for (int kk = 0; kk < 4; ++kk)
+                                    tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32),
+                                                  idesc, (ks | kk) != 0);
+                                tc::umma_commit(ring_empty(slot));       // frees the weight stage when these MMAs retire
+                            }
+                        }
+                        tc::umma_commit(acc_ready(x));                   // accumulator of (slot x, unit l) complete
+                    }
+        }
+    } else {
+        // ===================== encoder + epilogue groups =====================
+        const int x = (warp - 2) >> 2;                               // tile slot of this group
+        const uint32_t row = (warp & 3) * 32 + lane;                 // TMEM lane quarter = warp % 4
+        const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16) + x * 256;
+        const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
+        const int cnt = x == 0 ? cnt0 : cnt1;
+        uint32_t acc_it = 0;
+        for (int q = 0; q < cnt; ++q) {
+            const int tile = (int)blockIdx.x + (2 * q + x) * G;
+            RowState st;
+            encode_row(a, tile, row, pe_addr, st);
+            tc::fence_proxy_async_smem();
+            tc::mbar_arrive(act_ready(x));
+            for (int l = 0; l < 10; ++l) {
+                tc::mbar_wait(acc_ready(x), acc_it & 1); ++acc_it;
+                tc::tcgen05_fence_after();
+                epilogue_unit(a, l, taddr, act_addr, row, vec_s, st);
+                if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
+                if (l < 9) {
+                    tc::fence_proxy_async_smem();
+                    tc::tcgen05_fence_before();
+                    tc::mbar_arrive(act_ready(x));
+                }
+            }
+        }
+    }
+    tc::tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc(tmem_base, 512); }
+}
+
+// ------------------------------------------------------------------ host side ----
+static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaStream_t st) {
+    PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
+    if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;          // conditional inputs: fp32 path for now
+    for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.stage_begin[l] = L.stage_begin[l]; }
+    a.stages = (const uint8_t*)packed;
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
+    static bool attr_set = false;
+    if (!attr_set) {
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        attr_set = true;
+    }
+    int grid = a.n_tiles < nerf_num_sms() ? a.n_tiles : nerf_num_sms();
+    g1_fused_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int nerf_add_density_noise(float*, int, int64_t, float, uint64_t, int64_t, void*);
+
+static inline int64_t a256(int64_t x) { return (x + 255) & ~(int64_t)255; }
+
+extern "C" int64_t nerf_g1_render_workspace_bytes(int64_t B, int S) {
+    if (B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
+    int64_t P = B * S;
+    return a256(P * 4) * 2 + a256(P * 12) + 2 * a256(B * 12);      // t, sigma, rgb, rays_o, rays_d
+}
+
+extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
+                                    const float* rays_o, const float* rays_d,
+                                    const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                    float focal, int64_t ray_begin, int64_t B, int S,
+                                    float near_plane, float far_plane, const float* t_base, const float* t_in,
+                                    const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                    const float* noise, float noise_std,
+                                    float normalize_position, int normalize_direction,
+                                    float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
+                                    float* out_t, float* out_sigma, float* out_rgb,
+                                    void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!packed || B < 0 || S < 32 || S > 4096) return (S > 0 && S < 32) ? NERF_ERR_UNSUPPORTED : NERF_ERR_BAD_ARG;
+    if (!rays_o != !rays_d) return NERF_ERR_BAD_ARG;
+    if (!rays_o && (!cam_o || !cam_r || n_cams <= 0 || H <= 0 || W <= 0 || ray_begin < 0 ||
+                    ray_begin + B > (int64_t)n_cams * H * W)) return NERF_ERR_BAD_ARG;
+    if (B == 0) return NERF_OK;
+    if (!workspace || workspace_bytes < nerf_g1_render_workspace_bytes(B, S)) return NERF_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t P = B * S;
+    uint8_t* w = (uint8_t*)workspace;
+    float* ws_t = (float*)w; w += a256(P * 4);
+    float* ws_sigma = (float*)w; w += a256(P * 4);
+    float* ws_rgb = (float*)w; w += a256(P * 12);
+    float* ws_o = (float*)w; w += a256(B * 12);
+    float* ws_d = (float*)w;
+    FusedArgs a{};
+    a.rays_o = rays_o; a.rays_d = rays_d; a.cam_o = cam_o; a.cam_r = cam_r; a.H = H; a.W = W; a.focal = focal;
+    a.ray_begin = ray_begin; a.ws_rays_o = ws_o; a.ws_rays_d = ws_d;
+    a.B = B; a.S = S; a.P = P; a.n_tiles = (int)((P + 127) / 128);
+    a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
+    a.near_plane = near_plane; a.far_plane = far_plane; a.norm = normalize_position; a.normalize_dir = normalize_direction;
+    a.out_t = out_t ? out_t : ws_t; a.out_sigma = out_sigma ? out_sigma : ws_sigma; a.out_rgb = out_rgb ? out_rgb : ws_rgb;
+    a.dbg = nullptr; a.dbg_layer = -1;
+    int rc = launch_fused(packed, Dx, Dd, a, st); if (rc) return rc;
+    if (noise) return NERF_ERR_UNSUPPORTED;   // host-supplied noise is added by the binding on out_sigma before compositing
+    if (noise_std != 0.0f) { rc = nerf_add_density_noise(a.out_sigma, S, B, noise_std, seed, ray_id_base, stream); if (rc) return rc; }
+    if (out_pixels || out_depth || out_acc || out_weights) {
+        const float* ro = rays_o ? rays_o : ws_o; const float* rd = rays_o ? rays_d : ws_d;
+        rc = nerf_composite_fwd(a.out_sigma, a.out_rgb, nullptr, ro, rd, a.out_t, B, S, out_pixels, out_depth, out_acc,
+                                out_weights, stream);
+        if (rc) return rc;
+    }
+    return NERF_OK;
+}
+
+// test/debug entry: the MLP alone on explicit rays + t, optionally dumping the normalised
+// output of one unit (fp32, before bf16 rounding) -> per-layer parity against the oracle.
+extern "C" int nerf_g1_mlp_tc_debug(const void* packed, const float* rays_o, const float* rays_d, const float* t,
+                                    int64_t B, int S, float normalize_position, int normalize_direction,
+                                    float* out_sigma, float* out_rgb, float* scratch_t, float* dbg, int dbg_layer,
+                                    void* stream) {
+    if (!packed || !rays_o || !rays_d || !t || !out_sigma || !out_rgb || !scratch_t || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
+    FusedArgs a{};
+    a.rays_o = rays_o; a.rays_d = rays_d; a.B = B; a.S = S; a.P = B * S; a.n_tiles = (int)((a.P + 127) / 128);
+    a.t_in = t; a.norm = normalize_position; a.normalize_dir = normalize_direction;
+    a.out_t = scratch_t; a.out_sigma = out_sigma; a.out_rgb = out_rgb; a.dbg = dbg; a.dbg_layer = dbg_layer;
+    return launch_fused(packed, 3, 3, a, (cudaStream_t)stream);
+}

@@ -1,0 +1,199 @@
+// Fused ray-gen + sample + encode + G1 MLP on tcgen05 (bf16 in, fp32 accumulate in TMEM).
+//
+// One persistent CTA per SM, 320 threads:
+//   warp 0      TMA producer: streams the packed weight stages (16 KB: 128 n x 64 k) through a ring
+//   warp 1      MMA issuer (one lane): tcgen05.mma M=128 N=128 K=16, accumulators in TMEM
+//   warps 2-5   epilogue/encoder group of tile slot 0 (thread = point row = TMEM lane)
+//   warps 6-9   epilogue/encoder group of tile slot 1
+// Two 128-point tiles are in flight (slots), each with its own 256 TMEM columns, activation
+// buffer (4 K-slabs, SW128 K-major, written by the epilogue in exactly the layout the next
+// layer's A descriptor reads) and encoding slab.  While the tensor pipe runs unit l of one
+// slot, the other slot's epilogue (bias, ReLU, LayerNorm statistics, normalise, bf16, heads)
+// drains unit l of its tile.  Activations never leave the SM; HBM sees rays in and
+// (t, sigma, rgb) out.
+#pragma once
+#include "tc_layout.cuh"
+
+#define TC_THREADS 320
+#define TC_RING 3
+#define SM_ACT 0                                  // 2 x 64 KB
+#define SM_PE (2 * 65536)                         // 2 x 16 KB
+#define SM_RING (SM_PE + 2 * TC_SLAB_BYTES)       // TC_RING x 16 KB
+#define SM_VEC (SM_RING + TC_RING * TC_STAGE_BYTES)
+#define SM_BAR (SM_VEC + ((TC_VEC_FLOATS * 4 + 15) & ~15))
+#define SM_TOTAL (SM_BAR + 128)
+#define TC_SMEM_BYTES (SM_TOTAL + 1024)           // + slack for the manual 1024 B alignment
+
+struct FusedArgs {
+    const uint8_t* stages; const float* vec;
+    int nk[10]; int stage_begin[10];
+    const float* rays_o; const float* rays_d;     // [B,3] or null -> camera
+    const float* cam_o; const float* cam_r; int H, W; float focal; int64_t ray_begin;
+    float* ws_rays_o; float* ws_rays_d;           // written when rays come from the camera
+    int64_t B; int S; int64_t P; int n_tiles;
+    const float* t_in; const float* t_base; const float* u; int jitter; uint64_t seed; int64_t ray_id_base;
+    float near_plane, far_plane;
+    float norm; int normalize_dir;
+    float* out_t; float* out_sigma; float* out_rgb;
+    float* dbg; int dbg_layer;
+};
+
+__device__ __forceinline__ void store_row_chunk(uint32_t slab_addr, uint32_t row, uint32_t c16, uint4 v) {
+    uint32_t a = slab_addr + tc::sw128_offset(row, c16);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// sin(pi w), cos(pi w) with an exact reduction of w to [-1, 1]
+__device__ __forceinline__ void sincospi_fast(float w, float& s, float& c) {
+    float r = w - 2.0f * rintf(0.5f * w);
+    s = __sinf(3.14159265358979f * r); c = __cosf(3.14159265358979f * r);
+}
+
+// positional encoding of NV values -> one [128 x 64] bf16 slab row (features beyond NV*2*L are zero)
+template <int NV, int L>
+__device__ __forceinline__ void write_pe_row(uint32_t slab_addr, uint32_t row, const float (&v)[NV]) {
+    float f[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) f[i] = 0.f;
+#pragma unroll
+    for (int c = 0; c < NV; ++c) {
+        float w = v[c];
+#pragma unroll
+        for (int j = 0; j < L; ++j) {
+            float s, co; sincospi_fast(w, s, co);
+            f[c * 2 * L + j] = s; f[c * 2 * L + L + j] = co;
+            w = w + w;                                       // exact octave doubling
+        }
+    }
+#pragma unroll
+    for (int c16 = 0; c16 < 8; ++c16) {
+        uint4 q = make_uint4(tc::pack_bf16x2(f[c16 * 8 + 0], f[c16 * 8 + 1]), tc::pack_bf16x2(f[c16 * 8 + 2], f[c16 * 8 + 3]),
+                             tc::pack_bf16x2(f[c16 * 8 + 4], f[c16 * 8 + 5]), tc::pack_bf16x2(f[c16 * 8 + 6], f[c16 * 8 + 7]));
+        store_row_chunk(slab_addr, row, c16, q);
+    }
+}
+
+struct RowState { float d[3]; int64_t p; bool valid; };
+
+// ray-gen + stratified sample + position encoding for one point row of a tile
+__device__ __forceinline__ void encode_row(const FusedArgs& a, int tile, uint32_t row, uint32_t pe_addr, RowState& st) {
+    int64_t p = (int64_t)tile * 128 + row;
+    st.p = p; st.valid = p < a.P;
+    float v[3] = {0.f, 0.f, 0.f};
+    st.d[0] = st.d[1] = st.d[2] = 0.f;
+    if (st.valid) {
+        int64_t ray = p / a.S; int k = (int)(p - ray * a.S);
+        float o[3];
+        if (a.rays_o) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { o[c] = a.rays_o[ray * 3 + c]; st.d[c] = a.rays_d[ray * 3 + c]; }
+        } else {
+            int64_t id = a.ray_begin + ray;
+            int col = (int)(id % a.W); int64_t q = id / a.W; int r_ = (int)(q % a.H); int cam = (int)(q / a.H);
+            float cr[3]; camera_ray(r_, col, a.H, a.W, a.focal, cr);
+            rotate_ray(a.cam_r + (size_t)cam * 9, cr, st.d);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o[c] = a.cam_o[cam * 3 + c];
+            if (k == 0) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { a.ws_rays_o[ray * 3 + c] = o[c]; a.ws_rays_d[ray * 3 + c] = st.d[c]; }
+            }
+        }
+        float t;
+        if (a.t_in) t = a.t_in[p];
+        else {
+            auto lad = [&](int kk) { return a.t_base ? a.t_base[kk] : linspace_at(a.near_plane, a.far_plane, a.S, kk); };
+            float tk = lad(k); t = tk;
+            if (a.jitter) {                                    // nerf/model.py:425-433
+                float lo = tk, hi = tk;
+                if (k > 0) lo = __fmul_rn(0.5f, __fadd_rn(tk, lad(k - 1)));
+                if (k < a.S - 1) hi = __fmul_rn(0.5f, __fadd_rn(lad(k + 1), tk));
+                float uu;
+                if (a.u) uu = a.u[p];
+                else { uint32_t r4[4]; philox4x32(a.seed, (uint64_t)(a.ray_id_base + ray), (uint32_t)(k >> 2), r4); uu = u01_from_bits(r4[k & 3]); }
+                t = __fadd_rn(lo, __fmul_rn(__fsub_rn(hi, lo), uu));
+            }
+        }
+        a.out_t[p] = t;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) v[c] = __fdiv_rn(__fadd_rn(o[c], __fmul_rn(st.d[c], t)), a.norm);
+    }
+    write_pe_row<3, NERF_PE_X_OCTAVES>(pe_addr, row, v);
+}
+
+__device__ __forceinline__ void encode_dir_row(const FusedArgs& a, uint32_t row, uint32_t pe_addr, const RowState& st) {
+    float v[3] = {st.d[0], st.d[1], st.d[2]};
+    if (a.normalize_dir) {
+        float n = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        float inv = n > 0.f ? 1.0f / n : 0.f;
+        v[0] *= inv; v[1] *= inv; v[2] *= inv;
+    }
+    write_pe_row<3, NERF_PE_D_OCTAVES>(pe_addr, row, v);
+}
+
+// bias + ReLU + LayerNorm (no affine: folded into the consumer) for one unit of one tile slot.
+__device__ __forceinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
+                                              uint32_t row, const float* __restrict__ vec_s, const RowState& st) {
+    const float* bias = vec_s + TC_VEC_BIAS + l * 256;
+    uint32_t r[32];
+    float s = 0.f, q = 0.f;
+#pragma unroll 1
+    for (int ch = 0; ch < 8; ++ch) {
+        tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            float4 b = *reinterpret_cast<const float4*>(bias + ch * 32 + j);
+            float v0 = fmaxf(__uint_as_float(r[j]) + b.x, 0.f), v1 = fmaxf(__uint_as_float(r[j + 1]) + b.y, 0.f);
+            float v2 = fmaxf(__uint_as_float(r[j + 2]) + b.z, 0.f), v3 = fmaxf(__uint_as_float(r[j + 3]) + b.w, 0.f);
+            s += (v0 + v1) + (v2 + v3);
+            q = fmaf(v0, v0, q); q = fmaf(v1, v1, q); q = fmaf(v2, v2, q); q = fmaf(v3, v3, q);
+        }
+    }
+    const float mean = s * (1.0f / 256.f);
+    const float var = fmaxf(q * (1.0f / 256.f) - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + NERF_LN_EPS);
+    const float shift = -mean * rstd;
+    float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products (unit 7: density, unit 9: colour)
+    const float* hw = vec_s + TC_VEC_HEADW;
+#pragma unroll 1
+    for (int ch = 0; ch < 8; ++ch) {
+        tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait();
+        float n[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            float4 b = *reinterpret_cast<const float4*>(bias + ch * 32 + j);
+            n[j] = fmaf(fmaxf(__uint_as_float(r[j]) + b.x, 0.f), rstd, shift);
+            n[j + 1] = fmaf(fmaxf(__uint_as_float(r[j + 1]) + b.y, 0.f), rstd, shift);
+            n[j + 2] = fmaf(fmaxf(__uint_as_float(r[j + 2]) + b.z, 0.f), rstd, shift);
+            n[j + 3] = fmaf(fmaxf(__uint_as_float(r[j + 3]) + b.w, 0.f), rstd, shift);
+        }
+        if (l == 7) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) h0 = fmaf(n[j], hw[ch * 32 + j], h0);
+        } else if (l == 9) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                h0 = fmaf(n[j], hw[256 + ch * 32 + j], h0); h1 = fmaf(n[j], hw[512 + ch * 32 + j], h1);
+                h2 = fmaf(n[j], hw[768 + ch * 32 + j], h2);
+            }
+        }
+        if (a.dbg && a.dbg_layer == l && st.valid) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) a.dbg[st.p * 256 + ch * 32 + j] = n[j];
+        }
+        if (l < 9) {
+            const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                uint4 v = make_uint4(tc::pack_bf16x2(n[i * 8 + 0], n[i * 8 + 1]), tc::pack_bf16x2(n[i * 8 + 2], n[i * 8 + 3]),
+                                     tc::pack_bf16x2(n[i * 8 + 4], n[i * 8 + 5]), tc::pack_bf16x2(n[i * 8 + 6], n[i * 8 + 7]));
+                store_row_chunk(slab, row, (ch & 1) * 4 + i, v);
+            }
+        }
+    }
+    if (st.valid) {
+        const float* hb = vec_s + TC_VEC_HEADB;
+        if (l == 7) a.out_sigma[st.p] = h0 + hb[0];
+        if (l == 9) { a.out_rgb[st.p * 3] = h0 + hb[1]; a.out_rgb[st.p * 3 + 1] = h1 + hb[2]; a.out_rgb[st.p * 3 + 2] = h2 + hb[3]; }
+    }
+}

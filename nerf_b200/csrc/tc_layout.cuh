@@ -1,0 +1,40 @@
+// Shared description of the packed-weight image used by the tcgen05 kernels.
+#pragma once
+#include "common.cuh"
+#include "tc_common.cuh"
+
+#define TC_STAGE_BYTES 16384          // [128 n x 64 k] bf16, SW128 K-major
+#define TC_SLAB_BYTES 16384           // A-operand slab [128 rows x 64 k] bf16
+#define TC_VEC_BIAS 0                 // fp32 section: bias'[10][256]
+#define TC_VEC_HEADW (10 * 256)       //               head weights [4][256] (density, r, g, b) with gamma folded
+#define TC_VEC_HEADB (14 * 256)       //               head biases [4]
+#define TC_VEC_FLOATS (14 * 256 + 4)
+
+struct PackLayout {
+    int Dx, Dd, EX, ED;
+    int nk[10];                 // k-slabs (of 64) per unit
+    int stage_begin[11];        // first 16 KB stage of each unit (2 stages per k-slab)
+    int n_stages;
+    int Kt[10];
+    int64_t off_W[10], off_b[10], off_gamma[10], off_beta[10];
+    int64_t off_head_w[2], off_head_b[2];
+};
+
+static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
+    if (Dx < 3 || Dd < 3 || Dx > 16 || Dd > 16) return NERF_ERR_BAD_ARG;
+    int64_t off[44];
+    nerf_g1_param_layout(Dx, Dd, off);
+    L.Dx = Dx; L.Dd = Dd; L.EX = 2 * NERF_PE_X_OCTAVES * Dx; L.ED = 2 * NERF_PE_D_OCTAVES * Dd;
+    const int nkx = (L.EX + 63) / 64, nkd = (L.ED + 63) / 64;
+    int s = 0;
+    for (int l = 0; l < 10; ++l) {
+        L.nk[l] = (l == 0) ? nkx : (l == 4 ? 4 + nkx : (l == 8 ? 4 + nkd : 4));
+        L.Kt[l] = (l == 0) ? L.EX : (l == 4 ? 256 + L.EX : (l == 8 ? 256 + L.ED : 256));
+        L.stage_begin[l] = s; s += 2 * L.nk[l];
+        L.off_W[l] = off[4 + 4 * l]; L.off_b[l] = off[5 + 4 * l];
+        L.off_gamma[l] = off[6 + 4 * l]; L.off_beta[l] = off[7 + 4 * l];
+    }
+    L.stage_begin[10] = s; L.n_stages = s;
+    L.off_head_w[0] = off[0]; L.off_head_b[0] = off[1]; L.off_head_w[1] = off[2]; L.off_head_b[1] = off[3];
+    return NERF_OK;
+}

@@ -199,6 +199,15 @@ class NeRF(nn.Module):
         """All outputs of one pass (dict); `u`/`noise` are host-supplied draws (parity mode)."""
         rays_o = rays_o.float().contiguous(); rays_d = rays_d.float().contiguous()
         b = rays_o.shape[0]
+        if self._fused_ok(num_samples, states_x, states_d) and noise is None:
+            # tcgen05 path: one persistent kernel for sample+encode+MLP, then the compositing kernel
+            packed = ops.g1_pack_weights(self.flat_parameters())
+            out = ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position, self.normalize_direction,
+                                      rays_o=rays_o, rays_d=rays_d, t_in=t, u=u,
+                                      t_base=self._ladder(near, far, num_samples, rays_o.device),
+                                      want=("pixels", "depth", "acc", "weights", "t", "sigma", "rgb"))
+            out["density"] = out.pop("sigma").unsqueeze(-1); out["color"] = out.pop("rgb")
+            return out
         if b <= self.max_chunk_rays:
             return self._render_chunk(rays_o, rays_d, near, far, num_samples, states_x, states_d, u, noise, t)
         outs = []
@@ -207,6 +216,11 @@ class NeRF(nn.Module):
             outs.append(self._render_chunk(sl(rays_o, i), sl(rays_d, i), near, far, num_samples,
                                            sl(states_x, i), sl(states_d, i), sl(u, i), sl(noise, i), sl(t, i)))
         return {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
+
+    def _fused_ok(self, num_samples, states_x, states_d):
+        """bf16 tcgen05 path: inference only for now (training uses the fp32 kernels)."""
+        return (self.precision == "bf16" and not torch.is_grad_enabled() and num_samples >= 32
+                and self.density_inputs == 3 and self.color_inputs == 3 and states_x is None and states_d is None)
 
     def render_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
                     randomly_sample=False, density_noise_std=0.0):
@@ -243,6 +257,19 @@ class NeRF(nn.Module):
         ray_end = total if ray_end is None else ray_end
         chunk = self.max_chunk_rays if max_chunk_size is None else int(max_chunk_size)
         outs = []
+        if self._fused_ok(num_samples, states_x, states_d) and num_fine == 0:
+            packed = ops.g1_pack_weights(self.flat_parameters())
+            big = 1 << 20                                   # rays per launch (bounds the t/sigma/rgb workspace)
+            for i in range(ray_begin, ray_end, big):
+                j = min(i + big, ray_end)
+                r = ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position,
+                                        self.normalize_direction,
+                                        camera=(camera_o, camera_r, image_h, image_w, focal_length),
+                                        ray_begin=i, num_rays=j - i,
+                                        t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",))
+                outs.append(r["pixels"])
+            img = torch.cat(outs, dim=0)
+            return img.reshape(bc, image_h, image_w, 3) if full else img
         for i in range(ray_begin, ray_end, chunk):
             j = min(i + chunk, ray_end)
             o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, i, j)

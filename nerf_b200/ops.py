@@ -219,3 +219,57 @@ def mse_loss(pixels, target, want_grad=True):
     g = torch.empty_like(pixels) if want_grad else None
     check(lib().nerf_mse_loss(ptr(pixels), ptr(target), pixels.numel(), ptr(loss), ptr(g), stream()), "nerf_mse_loss")
     return loss, g
+
+
+# ------------------------------------------------------------ tcgen05 path ------
+def g1_pack_weights(flat, dx=3, dd=3):
+    """fp32 flat parameters -> bf16 UMMA-ready weight image (+ folded fp32 epilogue vectors)."""
+    n = lib().nerf_g1_packed_bytes(dx, dd)
+    if n <= 0:
+        raise ValueError("bad Dx/Dd")
+    packed = torch.empty(n, dtype=torch.uint8, device=flat.device)
+    check(lib().nerf_g1_pack_weights(ptr(flat), dx, dd, ptr(packed), stream()), "nerf_g1_pack_weights")
+    return packed
+
+
+def g1_mlp_tc_debug(packed, rays_o, rays_d, t, normalize_position, normalize_direction=True, dbg_layer=-1):
+    rays_o, rays_d, t = _f32c(rays_o), _f32c(rays_d), _f32c(t)
+    b, s = t.shape
+    dev = t.device
+    sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
+    scratch = torch.empty(b, s, device=dev)
+    dbg = torch.zeros(b * s, 256, device=dev) if dbg_layer >= 0 else None
+    check(lib().nerf_g1_mlp_tc_debug(ptr(packed), ptr(rays_o), ptr(rays_d), ptr(t), b, s, float(normalize_position),
+                                     int(normalize_direction), ptr(sigma), ptr(rgb), ptr(scratch), ptr(dbg), dbg_layer,
+                                     stream()), "nerf_g1_mlp_tc_debug")
+    return sigma, rgb, dbg
+
+
+def g1_render_fused(packed, num_samples, near, far, normalize_position, normalize_direction=True,
+                    rays_o=None, rays_d=None, camera=None, ray_begin=0, num_rays=None,
+                    t_base=None, t_in=None, u=None, jitter=False, seed=0, ray_id_base=0, noise_std=0.0,
+                    want=("pixels", "depth", "acc", "weights", "t")):
+    """One fused pass.  camera = (cam_o [n,3], cam_r [n,3,3], H, W, focal) when rays are not given."""
+    if rays_o is not None:
+        rays_o, rays_d = _f32c(rays_o), _f32c(rays_d)
+        b = rays_o.shape[0]; dev = rays_o.device
+        cam_o = cam_r = None; n_cams = h = w = 0; focal = 1.0
+    else:
+        cam_o, cam_r, h, w, focal = camera
+        cam_o, cam_r = _f32c(cam_o), _f32c(cam_r)
+        n_cams = cam_o.shape[0]; b = num_rays; dev = cam_o.device
+    s = num_samples
+    out = {}
+    alloc = {"pixels": (b, 3), "depth": (b,), "acc": (b,), "weights": (b, s), "t": (b, s), "sigma": (b, s), "rgb": (b, s, 3)}
+    for k in want:
+        out[k] = torch.empty(*alloc[k], device=dev, dtype=torch.float32)
+    nbytes = lib().nerf_g1_render_workspace_bytes(b, s)
+    ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    g = lambda k: ptr(out.get(k))
+    check(lib().nerf_g1_render_fused(ptr(packed), 3, 3, ptr(rays_o), ptr(rays_d), ptr(cam_o), ptr(cam_r), n_cams, h, w,
+                                     float(focal), ray_begin, b, s, float(near), float(far), ptr(t_base), ptr(_f32c(t_in)),
+                                     ptr(_f32c(u)), int(jitter), seed, ray_id_base, None, float(noise_std),
+                                     float(normalize_position), int(normalize_direction),
+                                     g("pixels"), g("depth"), g("acc"), g("weights"), g("t"), g("sigma"), g("rgb"),
+                                     ptr(ws), nbytes, stream()), "nerf_g1_render_fused")
+    return out
