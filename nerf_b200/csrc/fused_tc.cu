@@ -1,6 +1,13 @@
 // tcgen05 fused path: kernel body (roles) and the C entry points built on it.
 #include "tc_fused_kernel.cuh"
+#include <stdlib.h>
 
+// CG = 1: one CTA per SM works alone (M=128 MMAs, both weight halves per K-slab).
+// CG = 2: CTA pairs (cluster of 2, cta_group::2): M=256 MMAs issued by the leader over both CTAs'
+//         tiles; each CTA streams only ITS half (128 output features) of every weight K-slab, so
+//         the weight bytes per tile and SM halve -- the v1 profile showed the kernel bound by the
+//         weight ring's latency x depth, not by the tensor pipe or the epilogue.
+template <int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedArgs a) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = tc::smem_u32(smem_raw);
@@ -16,19 +23,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 4));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int G = gridDim.x;
-    const int n_my = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - (int)blockIdx.x + G - 1) / G : 0;
-    const int cnt0 = (n_my + 1) >> 1, cnt1 = n_my >> 1;           // tiles of slot 0 / slot 1
+    const uint32_t rank = (CG == 2) ? tc::cluster_ctarank() : 0u;
+    const bool leader = rank == 0;
+    // work units: CG=1 -> tiles; CG=2 -> tile pairs (this CTA takes tile 2*pair + rank)
+    const int G = gridDim.x / CG, me = blockIdx.x / CG;
+    const int n_units = (CG == 2) ? (a.n_tiles + 1) / 2 : a.n_tiles;
+    const int n_my = (me < n_units) ? (n_units - me + G - 1) / G : 0;
+    const int cnt0 = (n_my + 1) >> 1, cnt1 = n_my >> 1;           // units of slot 0 / slot 1
+    const int stages_per_slab = (CG == 2) ? 1 : 2;
 
     for (int i = threadIdx.x; i < TC_VEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[i];
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), 1); tc::mbar_init(ring_empty(s), 1); }
-        for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), 128); tc::mbar_init(acc_ready(x), 1); }
+        for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), (CG == 2 && leader) ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
+        for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), CG == 2 ? 8 : 128); tc::mbar_init(acc_ready(x), 1); }
         tc::fence_barrier_init();
     }
-    if (warp == 1) tc::tmem_alloc(tc::smem_u32((const void*)tmem_slot), 512);
+    if (warp == 1) { if (CG == 2) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 512); else tc::tmem_alloc(tc::smem_u32((const void*)tmem_slot), 512); }
     tc::tcgen05_fence_before();
-    __syncthreads();
+    if (CG == 2) tc::cluster_sync_all(); else __syncthreads();
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -40,46 +52,62 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 for (int l = 0; l < 10; ++l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
-                        const int ns = 2 * a.nk[l];
+                        const int nk = a.nk[l];
                         const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
-                        for (int s = 0; s < ns; ++s, ++it) {
-                            const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                            tc::mbar_wait(ring_empty(slot), ph ^ 1);
-                            tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
-                            tc::tma_load_1d(base + SM_RING + slot * TC_STAGE_BYTES, src + (size_t)s * TC_STAGE_BYTES,
-                                            TC_STAGE_BYTES, ring_full(slot));
-                        }
+                        for (int ks = 0; ks < nk; ++ks)
+                            for (int h = 0; h < stages_per_slab; ++h, ++it) {
+                                const int nh = (CG == 2) ? (int)rank : h;     // pair: this CTA owns one feature half
+                                const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                                tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
+                                tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
+                                tc::tma_load_1d(base + SM_RING + slot * TC_STAGE_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
+                                                TC_STAGE_BYTES, ring_full(slot));
+                            }
                     }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = tc::umma_idesc_bf16(128, 128);
+        if (lane == 0 && leader) {
+            // ===================== MMA issuer =====================
+            const uint32_t idesc = (CG == 2) ? tc::umma_idesc_bf16(256, 256) : tc::umma_idesc_bf16(128, 128);
             uint32_t it = 0, act_it[2] = {0, 0};
             for (int q = 0; q < cnt0; ++q)
                 for (int l = 0; l < 10; ++l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
-                        tc::mbar_wait(act_ready(x), act_it[x] & 1); ++act_it[x];
+                        tc::mbar_wait(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
                         tc::tcgen05_fence_after();
                         const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
                         const int nk = a.nk[l];
                         for (int ks = 0; ks < nk; ++ks) {
                             const uint32_t a_addr = (l == 0 || ks >= 4) ? pe_addr : act_addr + ks * TC_SLAB_BYTES;
-                            for (int nh = 0; nh < 2; ++nh, ++it) {
+                            for (int h = 0; h < stages_per_slab; ++h, ++it) {
                                 const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                                tc::mbar_wait(ring_full(slot), ph);
+                                tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
                                 tc::tcgen05_fence_after();
                                 const uint32_t b_addr = base + SM_RING + slot * TC_STAGE_BYTES;
-                                const uint32_t d_tmem = tmem_base + x * 256 + nh * 128;
+                                const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
 #pragma unroll
-                                for (int kk = 0; kk < 4; ++kk)
-                                    tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32),
-                                                  idesc, (ks | kk) != 0);
-                                tc::umma_commit(ring_empty(slot));       // frees the weight stage when these MMAs retire
+                                for (int kk = 0; kk < 4; ++kk) {
+                                    if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                    else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                }
+                                if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
                             }
                         }
-                        tc::umma_commit(acc_ready(x));                   // accumulator of (slot x, unit l) complete
+                        if (CG == 2) tc::umma_commit_2cta(acc_ready(x)); else tc::umma_commit(acc_ready(x));
+                    }
+        } else if (CG == 2 && lane == 0 && !leader) {
+            // ===================== peer relay: "my weight half has landed" -> leader's full barrier =====================
+            uint32_t it = 0;
+            for (int q = 0; q < cnt0; ++q)
+                for (int l = 0; l < 10; ++l)
+                    for (int x = 0; x < 2; ++x) {
+                        if (x == 1 && q >= cnt1) continue;
+                        for (int ks = 0; ks < a.nk[l]; ++ks, ++it) {
+                            const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                            tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
+                            tc::mbar_arrive_cluster(tc::mapa(ring_full(slot), 0));
+                        }
                     }
         }
     } else {
@@ -89,29 +117,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
         const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16) + x * 256;
         const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
         const int cnt = x == 0 ? cnt0 : cnt1;
+        const uint32_t act_bar_remote = (CG == 2) ? tc::mapa(act_ready(x), 0) : 0u;
+        auto signal_act = [&]() {
+            tc::fence_proxy_async_smem();
+            tc::tcgen05_fence_before();
+            if (CG == 2) { __syncwarp(); if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
+            else tc::mbar_arrive(act_ready(x));
+        };
         uint32_t acc_it = 0;
         for (int q = 0; q < cnt; ++q) {
-            const int tile = (int)blockIdx.x + (2 * q + x) * G;
+            const int unit = me + (2 * q + x) * G;
+            const int tile = (CG == 2) ? 2 * unit + (int)rank : unit;
             RowState st;
             encode_row(a, tile, row, pe_addr, st);
-            tc::fence_proxy_async_smem();
-            tc::mbar_arrive(act_ready(x));
+            signal_act();
             for (int l = 0; l < 10; ++l) {
-                tc::mbar_wait(acc_ready(x), acc_it & 1); ++acc_it;
+                tc::mbar_wait(acc_ready(x), acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
-                epilogue_unit(a, l, taddr, act_addr, row, vec_s, st);
+                if (a.dbg && a.dbg_layer == l) epilogue_unit<3>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 7) epilogue_unit<1>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 9) epilogue_unit<2>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else epilogue_unit<0>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
-                if (l < 9) {
-                    tc::fence_proxy_async_smem();
-                    tc::tcgen05_fence_before();
-                    tc::mbar_arrive(act_ready(x));
-                }
+                if (l < 9) signal_act();
             }
         }
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc(tmem_base, 512); }
+    if (CG == 2) tc::cluster_sync_all(); else __syncthreads();
+    if (warp == 1) { tc::tcgen05_fence_after(); if (CG == 2) tc::tmem_dealloc2(tmem_base, 512); else tc::tmem_dealloc(tmem_base, 512); }
 }
 
 // ------------------------------------------------------------------ host side ----
@@ -121,13 +155,26 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.stage_begin[l] = L.stage_begin[l]; }
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
-    static bool attr_set = false;
-    if (!attr_set) {
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        attr_set = true;
+    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
+    static int cg = -1;
+    if (cg < 0) {
+        const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2;
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
     }
-    int grid = a.n_tiles < nerf_num_sms() ? a.n_tiles : nerf_num_sms();
-    g1_fused_tc_kernel<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
+    const int sms = nerf_num_sms();
+    if (cg == 2) {
+        int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TC_SMEM_BYTES; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_tc_kernel<2>, a));
+    } else {
+        int grid = a.n_tiles < sms ? a.n_tiles : sms;
+        g1_fused_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
+    }
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }

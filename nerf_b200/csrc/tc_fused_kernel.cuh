@@ -36,6 +36,7 @@ struct FusedArgs {
     float norm; int normalize_dir;
     float* out_t; float* out_sigma; float* out_rgb;
     float* dbg; int dbg_layer;
+    uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
 };
 
 __device__ __forceinline__ void store_row_chunk(uint32_t slab_addr, uint32_t row, uint32_t c16, uint4 v) {
@@ -132,68 +133,104 @@ __device__ __forceinline__ void encode_dir_row(const FusedArgs& a, uint32_t row,
 }
 
 // bias + ReLU + LayerNorm (no affine: folded into the consumer) for one unit of one tile slot.
-__device__ __forceinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
-                                              uint32_t row, const float* __restrict__ vec_s, const RowState& st) {
-    const float* bias = vec_s + TC_VEC_BIAS + l * 256;
-    uint32_t r[32];
-    float s = 0.f, q = 0.f;
-#pragma unroll 1
-    for (int ch = 0; ch < 8; ++ch) {
-        tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait();
+// Two passes over the TMEM accumulator with packed f32x2 math and the next tcgen05.ld in
+// flight while the current 32 columns are processed:
+//   pass 1: z = acc + b, v = max(z, 0), sum v, sum v^2            (FADD2, FMNMX, FADD2, FFMA2)
+//   pass 2: n = max(acc*rstd + (b*rstd + shift), shift), shift = -mean*rstd  (rstd > 0, so this
+//           equals relu(z)*rstd + shift); the max is taken after the bf16 conversion
+//           (monotone rounding => identical result)              (FFMA2, FFMA2, F2FP, HMNMX2)
+__device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float2(__uint_as_float(a), __uint_as_float(b)); }
+
+// MODE: 0 = plain unit, 1 = unit 7 (+ density head), 2 = unit 9 (+ colour head, no activation
+// store), 3 = debug dump of the normalised row.  Chunk loops are unrolled by two only (static
+// register double-buffer) to keep the kernel inside the instruction cache.
+template <int MODE>
+__device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
+                                           uint32_t row, uint32_t vec_addr, const RowState& st) {
+    const uint32_t bias_addr = vec_addr + (TC_VEC_BIAS + l * 256) * 4;
+    uint32_t r0[32], r1[32];
+    float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f);
+    auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-            float4 b = *reinterpret_cast<const float4*>(bias + ch * 32 + j);
-            float v0 = fmaxf(__uint_as_float(r[j]) + b.x, 0.f), v1 = fmaxf(__uint_as_float(r[j + 1]) + b.y, 0.f);
-            float v2 = fmaxf(__uint_as_float(r[j + 2]) + b.z, 0.f), v3 = fmaxf(__uint_as_float(r[j + 3]) + b.w, 0.f);
-            s += (v0 + v1) + (v2 + v3);
-            q = fmaf(v0, v0, q); q = fmaf(v1, v1, q); q = fmaf(v2, v2, q); q = fmaf(v3, v3, q);
+            const float4 b = tc::lds128(bias_addr + (ch * 32 + j) * 4);
+            float2 z0 = __fadd2_rn(f2(rc[j], rc[j + 1]), make_float2(b.x, b.y));
+            float2 z1 = __fadd2_rn(f2(rc[j + 2], rc[j + 3]), make_float2(b.z, b.w));
+            z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
+            s2 = __fadd2_rn(s2, z0); s2 = __fadd2_rn(s2, z1);
+            q2 = __ffma2_rn(z0, z0, q2); q2 = __ffma2_rn(z1, z1, q2);
         }
+    };
+    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+#pragma unroll 1
+    for (int c2 = 0; c2 < 4; ++c2) {
+        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
+        pass1(r0, 2 * c2);
+        tc::tmem_ld_wait();
+        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
+        pass1(r1, 2 * c2 + 1);
+        tc::tmem_ld_wait();
     }
-    const float mean = s * (1.0f / 256.f);
-    const float var = fmaxf(q * (1.0f / 256.f) - mean * mean, 0.f);
+    const float mean = (s2.x + s2.y) * (1.0f / 256.f);
+    const float var = fmaxf((q2.x + q2.y) * (1.0f / 256.f) - mean * mean, 0.f);
     const float rstd = rsqrtf(var + NERF_LN_EPS);
     const float shift = -mean * rstd;
-    float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products (unit 7: density, unit 9: colour)
-    const float* hw = vec_s + TC_VEC_HEADW;
-#pragma unroll 1
-    for (int ch = 0; ch < 8; ++ch) {
-        tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait();
-        float n[32];
+    const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
+    const __nv_bfloat162 shift_bf = __floats2bfloat162_rn(shift, shift);
+    float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products
+    const uint32_t hw_addr = vec_addr + TC_VEC_HEADW * 4;
+    auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
+        uint32_t packed[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-            float4 b = *reinterpret_cast<const float4*>(bias + ch * 32 + j);
-            n[j] = fmaf(fmaxf(__uint_as_float(r[j]) + b.x, 0.f), rstd, shift);
-            n[j + 1] = fmaf(fmaxf(__uint_as_float(r[j + 1]) + b.y, 0.f), rstd, shift);
-            n[j + 2] = fmaf(fmaxf(__uint_as_float(r[j + 2]) + b.z, 0.f), rstd, shift);
-            n[j + 3] = fmaf(fmaxf(__uint_as_float(r[j + 3]) + b.w, 0.f), rstd, shift);
-        }
-        if (l == 7) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) h0 = fmaf(n[j], hw[ch * 32 + j], h0);
-        } else if (l == 9) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                h0 = fmaf(n[j], hw[256 + ch * 32 + j], h0); h1 = fmaf(n[j], hw[512 + ch * 32 + j], h1);
-                h2 = fmaf(n[j], hw[768 + ch * 32 + j], h2);
+            const float4 b = tc::lds128(bias_addr + (ch * 32 + j) * 4);
+            const float2 c0 = __ffma2_rn(make_float2(b.x, b.y), rstd2, shift2);
+            const float2 c1 = __ffma2_rn(make_float2(b.z, b.w), rstd2, shift2);
+            const float2 y0 = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, c0);
+            const float2 y1 = __ffma2_rn(f2(rc[j + 2], rc[j + 3]), rstd2, c1);
+            __nv_bfloat162 p0 = __hmax2(__float22bfloat162_rn(y0), shift_bf);
+            __nv_bfloat162 p1 = __hmax2(__float22bfloat162_rn(y1), shift_bf);
+            packed[j / 2] = *reinterpret_cast<uint32_t*>(&p0); packed[j / 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);
+            if (MODE != 0) {
+                const float n0 = fmaxf(y0.x, shift), n1 = fmaxf(y0.y, shift), n2 = fmaxf(y1.x, shift), n3 = fmaxf(y1.y, shift);
+                if (MODE == 1) {
+                    const float4 w = tc::lds128(hw_addr + (ch * 32 + j) * 4);
+                    h0 = fmaf(n0, w.x, h0); h0 = fmaf(n1, w.y, h0); h0 = fmaf(n2, w.z, h0); h0 = fmaf(n3, w.w, h0);
+                } else if (MODE == 2) {
+                    const float4 w0 = tc::lds128(hw_addr + (256 + ch * 32 + j) * 4);
+                    const float4 w1 = tc::lds128(hw_addr + (512 + ch * 32 + j) * 4);
+                    const float4 w2 = tc::lds128(hw_addr + (768 + ch * 32 + j) * 4);
+                    h0 = fmaf(n0, w0.x, h0); h0 = fmaf(n1, w0.y, h0); h0 = fmaf(n2, w0.z, h0); h0 = fmaf(n3, w0.w, h0);
+                    h1 = fmaf(n0, w1.x, h1); h1 = fmaf(n1, w1.y, h1); h1 = fmaf(n2, w1.z, h1); h1 = fmaf(n3, w1.w, h1);
+                    h2 = fmaf(n0, w2.x, h2); h2 = fmaf(n1, w2.y, h2); h2 = fmaf(n2, w2.z, h2); h2 = fmaf(n3, w2.w, h2);
+                } else if (st.valid) {
+                    float* o = a.dbg + st.p * 256 + ch * 32 + j;
+                    o[0] = n0; o[1] = n1; o[2] = n2; o[3] = n3;
+                }
             }
         }
-        if (a.dbg && a.dbg_layer == l && st.valid) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) a.dbg[st.p * 256 + ch * 32 + j] = n[j];
-        }
-        if (l < 9) {
+        if (MODE != 2) {
             const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                uint4 v = make_uint4(tc::pack_bf16x2(n[i * 8 + 0], n[i * 8 + 1]), tc::pack_bf16x2(n[i * 8 + 2], n[i * 8 + 3]),
-                                     tc::pack_bf16x2(n[i * 8 + 4], n[i * 8 + 5]), tc::pack_bf16x2(n[i * 8 + 6], n[i * 8 + 7]));
-                store_row_chunk(slab, row, (ch & 1) * 4 + i, v);
-            }
+            for (int i = 0; i < 4; ++i)
+                store_row_chunk(slab, row, (ch & 1) * 4 + i, make_uint4(packed[i * 4], packed[i * 4 + 1], packed[i * 4 + 2], packed[i * 4 + 3]));
         }
+    };
+    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+#pragma unroll 1
+    for (int c2 = 0; c2 < 4; ++c2) {
+        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
+        pass2(r0, 2 * c2);
+        tc::tmem_ld_wait();
+        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
+        pass2(r1, 2 * c2 + 1);
+        tc::tmem_ld_wait();
     }
     if (st.valid) {
-        const float* hb = vec_s + TC_VEC_HEADB;
-        if (l == 7) a.out_sigma[st.p] = h0 + hb[0];
-        if (l == 9) { a.out_rgb[st.p * 3] = h0 + hb[1]; a.out_rgb[st.p * 3 + 1] = h1 + hb[2]; a.out_rgb[st.p * 3 + 2] = h2 + hb[3]; }
+        if (MODE == 1) a.out_sigma[st.p] = h0 + a.vec[TC_VEC_HEADB];
+        if (MODE == 2) {
+            a.out_rgb[st.p * 3] = h0 + a.vec[TC_VEC_HEADB + 1]; a.out_rgb[st.p * 3 + 1] = h1 + a.vec[TC_VEC_HEADB + 2];
+            a.out_rgb[st.p * 3 + 2] = h2 + a.vec[TC_VEC_HEADB + 3];
+        }
     }
 }
