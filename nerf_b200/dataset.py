@@ -1,0 +1,111 @@
+"""`PixelRayDataset`: the reference's per-pixel dataset (nerf/dataset.py:175-316) with the same
+item dictionary, plus a batched GPU gatherer (`gather`, `batches`) that replaces 1024 Python
+`__getitem__` calls + default collate per batch by ONE kernel launch.
+
+Constructor generations:
+  G1  PixelRayDataset(images, poses[N,4,4], focal_length)                     (example.ipynb cell 5)
+  G2  PixelRayDataset(images, poses[N,3,4], focal_length, states_x=...)       (train_conditional_nerf.py:97)
+  HEAD PixelRayDataset(images, segmentation, poses, focal_length, ...)        (nerf/dataset.py:194)
+The HEAD form is recognised by its 4th positional being the focal length (a number).
+"""
+import numbers
+
+import torch
+import torch.utils.data as data
+
+from . import ops
+
+
+class PixelRayDataset(data.Dataset):
+
+    def __init__(self, images, *args, states_x=None, states_d=None, x_states=None, d_states=None):
+        if len(args) >= 3 and isinstance(args[2], numbers.Number):       # HEAD: (images, segmentation, poses, focal, ...)
+            segmentation, poses, focal_length = args[0], args[1], args[2]
+            rest = args[3:]
+        else:                                                           # G1/G2: (images, poses, focal, ...)
+            segmentation, poses, focal_length = None, args[0], args[1]
+            rest = args[2:]
+        if len(rest) > 0 and states_x is None:
+            states_x = rest[0]
+        if len(rest) > 1 and states_d is None:
+            states_d = rest[1]
+        self.images = images
+        self.segmentation = segmentation
+        self.poses = poses
+        self.focal_length = float(focal_length)
+        self.states_x = states_x if states_x is not None else x_states
+        self.states_d = states_d if states_d is not None else d_states
+        self.x_states, self.d_states = self.states_x, self.states_d     # attribute names seen in the notebook traceback
+        self._rays = None
+
+    @property
+    def rays(self):
+        """Camera-space rays [H,W,3] (reference: built once in __init__, nerf/dataset.py:228)."""
+        if self._rays is None:
+            h, w = self.images.shape[1], self.images.shape[2]
+            if self.images.is_cuda:
+                from .model import NeRF
+                self._rays = NeRF.generate_rays(h, w, self.focal_length, dtype=self.images.dtype, device=self.images.device)
+            else:       # host tensors: same arithmetic in torch (3 elementwise ops on an [H,W] grid)
+                y, x = torch.meshgrid(torch.arange(h, dtype=self.images.dtype), torch.arange(w, dtype=self.images.dtype), indexing="ij")
+                x = (x - 0.5 * float(w - 1)) / self.focal_length
+                y = (y - 0.5 * float(h - 1)) / self.focal_length
+                self._rays = torch.stack([x, -y, -torch.ones_like(x)], dim=-1)
+        return self._rays
+
+    def __len__(self):
+        return self.images.shape[0] * self.images.shape[1] * self.images.shape[2]
+
+    @staticmethod
+    def decode_index(idx, n, h, w):
+        """idx -> (image_bi, image_hi, image_wi), reference nerf/dataset.py:283-291."""
+        wi = idx % w; idx = idx // w
+        hi = idx % h; idx = idx // h
+        return idx % n, hi, wi
+
+    def __getitem__(self, idx):
+        """Per-item path kept for API parity (DataLoader users); same keys as the reference,
+        including its `pose_d = rays_d` quirk (nerf/dataset.py:315)."""
+        n, h, w = self.images.shape[:3]
+        bi, hi, wi = self.decode_index(int(idx), n, h, w)
+        pixel = self.images[bi, hi, wi]
+        ray = self.rays[hi, wi]
+        pose = self.poses[bi]
+        dev = pixel.device
+        state_x = self.states_x[bi] if self.states_x is not None else torch.zeros(0, device=dev)
+        state_d = self.states_d[bi] if self.states_d is not None else torch.zeros(0, device=dev)
+        pose_o, pose_r = pose[:3, 3], pose[:3, :3]
+        rays_d = (pose_r * ray.unsqueeze(-2)).sum(dim=-1)
+        item = dict(image_wi=torch.LongTensor([wi]).to(dev), image_hi=torch.LongTensor([hi]).to(dev),
+                    image_bi=torch.LongTensor([bi]).to(dev), states_x=state_x, states_d=state_d,
+                    pixels=pixel, rays=ray, pose_o=pose_o, pose_d=rays_d, rays_o=pose_o, rays_d=rays_d)
+        if self.segmentation is not None:
+            item["label"] = self.segmentation[bi, hi, wi]
+        return item
+
+    # ---- batched path: one kernel per batch ---------------------------------------------
+    def gather(self, idx):
+        """Whole batch at once on the GPU: same dictionary as default-collating __getitem__."""
+        idx = idx.to(self.images.device)
+        o, d, px, st, bhw = ops.gather_pixel_rays(self.images, self.poses, self.focal_length, idx, self.states_x)
+        b = idx.numel()
+        out = dict(image_bi=bhw[:, 0:1], image_hi=bhw[:, 1:2], image_wi=bhw[:, 2:3], pixels=px, rays_o=o, rays_d=d,
+                   pose_o=o, pose_d=d, states_x=st if st is not None else torch.zeros(b, 0, device=o.device),
+                   states_d=(self.states_d[bhw[:, 0]] if self.states_d is not None else torch.zeros(b, 0, device=o.device)))
+        out["rays"] = self.rays[bhw[:, 1], bhw[:, 2]]
+        if self.segmentation is not None:
+            out["label"] = self.segmentation[bhw[:, 0], bhw[:, 1], bhw[:, 2]]
+        return out
+
+    def batches(self, batch_size, shuffle=True, generator=None, rank=0, world_size=1, drop_last=False):
+        """DataLoader(dataset, batch_size, shuffle) replacement: yields gathered batches.  With
+        world_size > 1 every rank draws the same permutation and takes its strided share."""
+        n = len(self)
+        dev = self.images.device
+        order = torch.randperm(n, generator=generator) if shuffle else torch.arange(n)
+        order = order[rank::world_size].to(dev)
+        for i in range(0, order.numel(), batch_size):
+            sel = order[i:i + batch_size]
+            if drop_last and sel.numel() < batch_size:
+                break
+            yield self.gather(sel)
