@@ -195,6 +195,43 @@ int nerf_g1_mlp_tc_debug(const void* packed, const float* rays_o, const float* r
                          float* out_sigma, float* out_rgb, float* scratch_t, float* dbg, int dbg_layer,
                          void* stream);
 
+/* ------------------------------------------------- bf16 training (tcgen05) --- */
+
+/* Slab image: the HBM format the bf16 training kernels exchange activations and gradients in.
+ * A [P x 64*ns] bf16 matrix is stored per 128-point tile as ns consecutive 16 KB slabs
+ * [128 rows x 128 B]; inside a slab the 16-byte chunk c of row r sits at r*128 + ((c ^ (r&7))<<4)
+ * (the 128-byte-swizzled UMMA operand image, usable K-major and MN-major without a transpose). */
+
+/* Test hook for the weight-gradient GEMM (autograd of nn.Linear.weight / .bias, a12), P = 128*n_tiles:
+ *   out[256][ld] += dz^T [256 x P] * [xmain (cols 0..255) | xenc (cols 256..319) | 1 (cols 320..335, if ones)]
+ * dz, xmain: slab images with ns=4; xenc: ns=1; each may be NULL.  xsmall (excludes xmain): a
+ * [P x 16] bf16 operand stored per tile as [16 point groups][2 column halves][8 points][8 columns]
+ * (4 KB), result in cols 0..15. */
+int nerf_tc_wgrad_debug(const void* dz, const void* xmain, const void* xenc, const void* xsmall, int ones,
+                        int n_tiles, float* out, int ld, void* stream);
+
+/* bf16 training step of the G1 model = autograd of the loop body train_conditional_nerf.py:120-135
+ * / example.ipynb cell 8 on tcgen05.  The caller owns one workspace of
+ * nerf_g1_train_workspace_bytes(B, S) bytes shared by the forward and backward calls. */
+int64_t nerf_g1_train_workspace_bytes(int64_t B, int S);
+/* transposed bf16 weight stages (gamma folded) for the data-gradient MMAs */
+int64_t nerf_g1_packed_bwd_bytes(int Dx, int Dd);
+int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, void* packed_bwd, void* stream);
+/* forward: sample (as nerf_g1_render_fused) -> encode -> MLP; writes t, sigma, rgb [B,S(,3)] and
+ * keeps every unit's normalised output (bf16 slab images) + LayerNorm statistics in the workspace */
+int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
+                         int64_t B, int S, float near_plane, float far_plane, const float* t_base,
+                         const float* t_in, const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                         float normalize_position, int normalize_direction,
+                         float* out_t, float* out_sigma, float* out_rgb,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+/* backward: d_sigma [B,S], d_rgb [B,S,3] (from nerf_composite_bwd) -> grads (flat fp32, state_dict
+ * order, OVERWRITTEN).  stage = 0 runs everything; 1 / 2 stop after the data-gradient kernel / the
+ * weight-gradient GEMM (test hooks reading the workspace). */
+int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float* params, int Dx, int Dd,
+                         const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
+                         void* workspace, int64_t workspace_bytes, int stage, void* stream);
+
 /* -------------------------------------------------------------- optimiser --- */
 
 /* torch.optim.Adam(lr, betas, eps) step over a flat buffer

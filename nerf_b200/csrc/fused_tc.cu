@@ -7,7 +7,7 @@
 //         tiles; each CTA streams only ITS half (128 output features) of every weight K-slab, so
 //         the weight bytes per tile and SM halve -- the v1 profile showed the kernel bound by the
 //         weight ring's latency x depth, not by the tensor pipe or the epilogue.
-template <int CG>
+template <int CG, bool TRAIN>
 __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedArgs a) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = tc::smem_u32(smem_raw);
@@ -130,18 +130,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
             const int tile = (CG == 2) ? 2 * unit + (int)rank : unit;
             RowState st;
             encode_row(a, tile, row, pe_addr, st);
+            if (TRAIN) {                                             // position-encoding slab -> HBM (wgrad of units 0, 4)
+                tc::fence_proxy_async_smem(); tc::named_bar_sync(1 + x, 128);
+                if (row == 0) { tc::tma_store_1d(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES); tc::tma_store_commit(); }
+            }
             signal_act();
             for (int l = 0; l < 10; ++l) {
                 tc::mbar_wait(acc_ready(x), acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
-                if (a.dbg && a.dbg_layer == l) epilogue_unit<3>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                else if (l == 7) epilogue_unit<1>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                else if (l == 9) epilogue_unit<2>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                else epilogue_unit<0>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                if (TRAIN) {                                         // pending bulk stores must have read the slabs we overwrite
+                    if (row == 0) tc::tma_store_wait_read0();
+                    tc::named_bar_sync(1 + x, 128);
+                }
+                if (!TRAIN && a.dbg && a.dbg_layer == l) epilogue_unit<3, false>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 7) epilogue_unit<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 9) epilogue_unit<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else epilogue_unit<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
+                if (TRAIN) {                                         // normalised output of unit l (and the direction slab) -> HBM
+                    tc::fence_proxy_async_smem(); tc::named_bar_sync(1 + x, 128);
+                    if (row == 0) {
+                        tc::tma_store_1d(a.tr_act + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), act_addr, 4 * TC_SLAB_BYTES);
+                        if (l == 4) tc::tma_store_1d(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
+                        tc::tma_store_commit();
+                    }
+                }
                 if (l < 9) signal_act();
             }
         }
+        if (TRAIN && row == 0) tc::tma_store_wait_all0();
     }
     tc::tcgen05_fence_before();
     if (CG == 2) tc::cluster_sync_all(); else __syncthreads();
@@ -149,7 +166,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
 }
 
 // ------------------------------------------------------------------ host side ----
-static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaStream_t st) {
+static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaStream_t st, bool train = false) {
     PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
     if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;          // conditional inputs: fp32 path for now
     for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.stage_begin[l] = L.stage_begin[l]; }
@@ -159,8 +176,10 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     static int cg = -1;
     if (cg < 0) {
         const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2;
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
     }
     const int sms = nerf_num_sms();
     if (cg == 2) {
@@ -170,10 +189,12 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr; cfg.numAttrs = 1;
-        NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_tc_kernel<2>, a));
+        if (train) NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_tc_kernel<2, true>, a));
+        else NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_tc_kernel<2, false>, a));
     } else {
         int grid = a.n_tiles < sms ? a.n_tiles : sms;
-        g1_fused_tc_kernel<1><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
+        if (train) g1_fused_tc_kernel<1, true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
+        else g1_fused_tc_kernel<1, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
     }
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
@@ -246,4 +267,19 @@ extern "C" int nerf_g1_mlp_tc_debug(const void* packed, const float* rays_o, con
     a.t_in = t; a.norm = normalize_position; a.normalize_dir = normalize_direction;
     a.out_t = scratch_t; a.out_sigma = out_sigma; a.out_rgb = out_rgb; a.dbg = dbg; a.dbg_layer = dbg_layer;
     return launch_fused(packed, 3, 3, a, (cudaStream_t)stream);
+}
+
+// training forward: the fused kernel with TRAIN = true, storing what the backward needs into `ws`
+int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d, int64_t B, int S,
+                       float near_plane, float far_plane, const float* t_base, const float* t_in, const float* u, int jitter,
+                       uint64_t seed, int64_t ray_id_base, float norm, int normalize_dir,
+                       float* out_t, float* out_sigma, float* out_rgb, uint8_t* ws, const TrainLayout& T, cudaStream_t st) {
+    FusedArgs a{};
+    a.rays_o = rays_o; a.rays_d = rays_d; a.B = B; a.S = S; a.P = T.P; a.n_tiles = T.n_tiles;
+    a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
+    a.near_plane = near_plane; a.far_plane = far_plane; a.norm = norm; a.normalize_dir = normalize_dir;
+    a.out_t = out_t; a.out_sigma = out_sigma; a.out_rgb = out_rgb; a.dbg = nullptr; a.dbg_layer = -1;
+    a.tr_act = ws + T.off_act; a.tr_pex = ws + T.off_pex; a.tr_ped = ws + T.off_ped;
+    a.tr_stats = reinterpret_cast<float2*>(ws + T.off_stats); a.P_pad = T.P_pad; a.tr_tiles = T.tr_tiles;
+    return launch_fused(packed, Dx, Dd, a, st, true);
 }

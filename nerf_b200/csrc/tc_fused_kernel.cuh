@@ -36,6 +36,9 @@ struct FusedArgs {
     float norm; int normalize_dir;
     float* out_t; float* out_sigma; float* out_rgb;
     float* dbg; int dbg_layer;
+    // training forward (TRAIN = true): slab images of every unit's normalised output and of the two
+    // encodings, plus (rstd, -mean*rstd) per point and unit, for the backward and wgrad kernels
+    uint8_t* tr_act; uint8_t* tr_pex; uint8_t* tr_ped; float2* tr_stats; int64_t P_pad; int tr_tiles;
     uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
 };
 
@@ -144,7 +147,7 @@ __device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float
 // MODE: 0 = plain unit, 1 = unit 7 (+ density head), 2 = unit 9 (+ colour head, no activation
 // store), 3 = debug dump of the normalised row.  Chunk loops are unrolled by two only (static
 // register double-buffer) to keep the kernel inside the instruction cache.
-template <int MODE>
+template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
                                            uint32_t row, uint32_t vec_addr, const RowState& st) {
     const uint32_t bias_addr = vec_addr + (TC_VEC_BIAS + l * 256) * 4;
@@ -209,7 +212,7 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
                 }
             }
         }
-        if (MODE != 2) {
+        if (MODE != 2 || TRAIN) {
             const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
             for (int i = 0; i < 4; ++i)
@@ -226,6 +229,7 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
         pass2(r1, 2 * c2 + 1);
         tc::tmem_ld_wait();
     }
+    if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
     if (st.valid) {
         if (MODE == 1) a.out_sigma[st.p] = h0 + a.vec[TC_VEC_HEADB];
         if (MODE == 2) {

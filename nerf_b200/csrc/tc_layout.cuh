@@ -38,3 +38,27 @@ static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
     L.off_head_w[0] = off[0]; L.off_head_b[0] = off[1]; L.off_head_w[1] = off[2]; L.off_head_b[1] = off[3];
     return NERF_OK;
 }
+
+// ---- workspace of the bf16 training step (tc_train.cu): byte offsets, all 1024-aligned ----
+#define TC_GW_LD 336                   // dW' row: 256 hidden + 64 encoding + 16 x (column sum of dz = db')
+struct TrainLayout {
+    int64_t P, P_pad; int n_tiles, tr_tiles;
+    int64_t off_pex, off_ped, off_act, off_dz, off_stats, off_dh, off_gw, off_gh, off_hsum, total;
+    int64_t zero_begin, zero_bytes;    // [gw | gh | hsum]: accumulated with atomics, cleared every step
+};
+static inline void make_train_layout(int64_t B, int S, TrainLayout& T) {
+    auto up = [](int64_t x) { return (x + 1023) & ~(int64_t)1023; };
+    T.P = B * S; T.n_tiles = (int)((T.P + 127) / 128); T.tr_tiles = (T.n_tiles + 1) & ~1; T.P_pad = (int64_t)T.tr_tiles * 128;
+    int64_t o = 0;
+    T.off_pex = o; o += (int64_t)T.tr_tiles * TC_SLAB_BYTES;
+    T.off_ped = o; o += (int64_t)T.tr_tiles * TC_SLAB_BYTES;
+    T.off_act = o; o += 10ll * T.tr_tiles * 4 * TC_SLAB_BYTES;
+    T.off_dz = o; o += 10ll * T.tr_tiles * 4 * TC_SLAB_BYTES;
+    T.off_stats = o; o += up(10ll * T.P_pad * 8);
+    T.off_dh = o; o += (int64_t)T.tr_tiles * 4096;
+    T.off_gw = o; T.zero_begin = o; o += up(10ll * 256 * TC_GW_LD * 4);
+    T.off_gh = o; o += up(2ll * 256 * 16 * 4);
+    T.off_hsum = o; o += 1024;
+    T.zero_bytes = o - T.zero_begin;
+    T.total = o;
+}

@@ -1,0 +1,196 @@
+// bf16 training step on tcgen05: host entry points around the three tensor-core kernels
+//   g1_fused_tc_kernel<CG, true>  forward, stores slab images of every unit's output   (fused_tc.cu)
+//   g1_bwd_tc_kernel<CG>          data-gradient chain + LayerNorm/ReLU backward         (tc_bwd_kernel.cuh)
+//   g1_wgrad_tc_kernel            dW' = dZ^T X, db' = dZ^T 1, head gradients            (tc_wgrad.cu)
+// plus the transposed weight packing for the backward MMAs and the "unfold" kernels that turn
+// gradients w.r.t. the folded parameters (W' = W diag(gamma_prev), b' = b + W beta_prev) into the
+// gradients of the 44 state_dict tensors (reference: autograd of train_conditional_nerf.py:120-135).
+#include "tc_bwd_kernel.cuh"
+#include <stdlib.h>
+
+struct WgradArgs;
+int launch_wgrad_tc_units(const uint8_t* ws, const TrainLayout& T, cudaStream_t st);
+int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d, int64_t B, int S,
+                       float near_plane, float far_plane, const float* t_base, const float* t_in, const float* u, int jitter,
+                       uint64_t seed, int64_t ray_id_base, float norm, int normalize_dir,
+                       float* out_t, float* out_sigma, float* out_rgb, uint8_t* ws, const TrainLayout& T, cudaStream_t st);
+
+// ---- transposed weight stages for g_{l-1} = dz_l W'_l: stage (l-1)*8 + ks*2 + nh holds
+//      [128 rows r = input feature nh*128 + r] x [64 cols c = output feature ks*64 + c], K-major SW128
+__global__ void pack_bwd_stage_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 72ll * 128 * 8) return;
+    const int c16 = (int)(i & 7), r = (int)((i >> 3) & 127), stage = (int)(i >> 10);
+    const int l = 1 + stage / 8, rel = stage % 8, ks = rel >> 1, nh = rel & 1;
+    const int kin = nh * 128 + r;
+    const float* W = params + L.off_W[l];
+    const float g = params[L.off_gamma[l - 1] + kin];
+    const int Kt = L.Kt[l];
+    uint32_t out[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int n0 = ks * 64 + c16 * 8 + q * 2;
+        out[q] = tc::pack_bf16x2(W[(size_t)n0 * Kt + kin] * g, W[(size_t)(n0 + 1) * Kt + kin] * g);
+    }
+    *reinterpret_cast<uint4*>(packed + (size_t)stage * TC_STAGE_BYTES + tc::sw128_offset(r, c16)) = make_uint4(out[0], out[1], out[2], out[3]);
+}
+
+extern "C" int64_t nerf_g1_packed_bwd_bytes(int Dx, int Dd) {
+    PackLayout L;
+    if (make_pack_layout(Dx, Dd, L) != NERF_OK) return NERF_ERR_BAD_ARG;
+    return 72ll * TC_STAGE_BYTES;
+}
+
+extern "C" int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, void* packed_bwd, void* stream) {
+    if (!params || !packed_bwd) return NERF_ERR_BAD_ARG;
+    PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
+    const int64_t n = 72ll * 128 * 8;
+    pack_bwd_stage_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int64_t nerf_g1_train_workspace_bytes(int64_t B, int S) {
+    if (B <= 0 || S <= 0) return NERF_ERR_BAD_ARG;
+    TrainLayout T; make_train_layout(B, S, T);
+    return T.total;
+}
+
+// ---- unfold: gradients of folded parameters -> gradients of the state_dict tensors ----
+// gw [10][256][336]: G_l = dL/dW'_l (cols 0..255 hidden, 256..319 encoding), col 320 = c_l = dL/db'_l
+// gh [2][256][16]:   gh[0][k][0] = sum_p d_sigma n_7[k];  gh[1][k][1+c] = sum_p d_rgb_c n_9[k]
+// hsum [4]:          sum_p (d_sigma, d_rgb)
+//   dW_l[i,k] = G_l[i,k] gamma_{l-1}[k] + c_l[i] beta_{l-1}[k]  (hidden k);  = G_l[i, 256+k2]  (encoding)
+//   db_l = c_l;  heads: dw[k] = gamma[k] H[k] + beta[k] s,  db = s
+__global__ void unfold_weights_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
+                                      const float* __restrict__ gh, const float* __restrict__ hsum, float* __restrict__ grads) {
+    const int l = blockIdx.y;
+    if (l < 10) {
+        const int Kt = L.Kt[l], hid = (l == 0) ? 0 : 256;
+        const float* G = gw + (size_t)l * 256 * TC_GW_LD;
+        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < 256ll * (Kt + 1); e += (int64_t)gridDim.x * blockDim.x) {
+            const int i = (int)(e / (Kt + 1)), k = (int)(e % (Kt + 1));
+            const float c = G[(size_t)i * TC_GW_LD + 320];
+            if (k == Kt) { grads[L.off_b[l] + i] = c; continue; }
+            float v;
+            if (k < hid) v = fmaf(G[(size_t)i * TC_GW_LD + k], params[L.off_gamma[l - 1] + k], c * params[L.off_beta[l - 1] + k]);
+            else v = G[(size_t)i * TC_GW_LD + 256 + (k - hid)];
+            grads[L.off_W[l] + (size_t)i * Kt + k] = v;
+        }
+    } else {
+        for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < 4 * 256 + 4; e += gridDim.x * blockDim.x) {
+            if (e >= 4 * 256) {
+                const int c = e - 4 * 256;
+                if (c == 0) grads[L.off_head_b[0]] = hsum[0]; else grads[L.off_head_b[1] + c - 1] = hsum[c];
+                continue;
+            }
+            const int c = e >> 8, k = e & 255, unit = c == 0 ? 7 : 9;
+            const float H = gh[(size_t)(c == 0 ? 0 : 1) * 256 * 16 + k * 16 + c];
+            const float v = fmaf(params[L.off_gamma[unit] + k], H, params[L.off_beta[unit] + k] * hsum[c]);
+            if (c == 0) grads[L.off_head_w[0] + k] = v; else grads[L.off_head_w[1] + (size_t)(c - 1) * 256 + k] = v;
+        }
+    }
+}
+//   dgamma_j[k] = sum_i G_{j+1}[i,k] W_{j+1}[i,k]  (+ head: w[k] H[k]);  dbeta_j[k] = sum_i c_{j+1}[i] W_{j+1}[i,k]  (+ head: w[k] s)
+__global__ void unfold_affine_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
+                                     const float* __restrict__ gh, const float* __restrict__ hsum, float* __restrict__ grads) {
+    const int j = blockIdx.x, k = threadIdx.x & 255, part = threadIdx.x >> 8;      // 1024 threads: 4 row groups x 256 columns
+    __shared__ float sg[4][256], sb[4][256];
+    float dg = 0.f, db = 0.f;
+    if (j < 9) {
+        const int l = j + 1, Kt = L.Kt[l];
+        const float* G = gw + (size_t)l * 256 * TC_GW_LD;
+        const float* W = params + L.off_W[l];
+        for (int i = part * 64; i < part * 64 + 64; ++i) {
+            const float w = W[(size_t)i * Kt + k];
+            dg = fmaf(G[(size_t)i * TC_GW_LD + k], w, dg);
+            db = fmaf(G[(size_t)i * TC_GW_LD + 320], w, db);
+        }
+    }
+    sg[part][k] = dg; sb[part][k] = db;
+    __syncthreads();
+    if (part == 0) {
+        dg = sg[0][k] + sg[1][k] + sg[2][k] + sg[3][k]; db = sb[0][k] + sb[1][k] + sb[2][k] + sb[3][k];
+        if (j == 7) {
+            const float w = params[L.off_head_w[0] + k];
+            dg = fmaf(w, gh[k * 16], dg); db = fmaf(w, hsum[0], db);
+        } else if (j == 9) {
+            for (int c = 0; c < 3; ++c) {
+                const float w = params[L.off_head_w[1] + (size_t)c * 256 + k];
+                dg = fmaf(w, gh[256 * 16 + k * 16 + 1 + c], dg); db = fmaf(w, hsum[1 + c], db);
+            }
+        }
+        grads[L.off_gamma[j] + k] = dg; grads[L.off_beta[j] + k] = db;
+    }
+}
+
+template <int CG>
+static int launch_bwd(BwdArgs& a, cudaStream_t st) {
+    static bool init = false;
+    if (!init) { NERF_CUDA(cudaFuncSetAttribute(g1_bwd_tc_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, TB_SMEM_BYTES)); init = true; }
+    const int sms = nerf_num_sms();
+    if (CG == 2) {
+        int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TB_THREADS); cfg.dynamicSmemBytes = TB_SMEM_BYTES; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_bwd_tc_kernel<CG>, a));
+    } else {
+        int grid = a.n_tiles < sms ? a.n_tiles : sms;
+        g1_bwd_tc_kernel<CG><<<grid, TB_THREADS, TB_SMEM_BYTES, st>>>(a);
+    }
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
+                                    int64_t B, int S, float near_plane, float far_plane, const float* t_base,
+                                    const float* t_in, const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                    float normalize_position, int normalize_direction,
+                                    float* out_t, float* out_sigma, float* out_rgb,
+                                    void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!packed || !rays_o || !rays_d || !out_t || !out_sigma || !out_rgb || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
+    TrainLayout T; make_train_layout(B, S, T);
+    if (!workspace || workspace_bytes < T.total) return NERF_ERR_WORKSPACE;
+    return launch_fused_train(packed, Dx, Dd, rays_o, rays_d, B, S, near_plane, far_plane, t_base, t_in, u, jitter, seed,
+                              ray_id_base, normalize_position, normalize_direction, out_t, out_sigma, out_rgb,
+                              (uint8_t*)workspace, T, (cudaStream_t)stream);
+}
+
+// stage: 0 = all, 1 = stop after the data-gradient kernel, 2 = stop after the weight-gradient GEMM (tests)
+extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float* params, int Dx, int Dd,
+                                    const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
+                                    void* workspace, int64_t workspace_bytes, int stage, void* stream) {
+    if (!packed || !packed_bwd || !params || !d_sigma || !d_rgb || !grads || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
+    if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;
+    PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
+    TrainLayout T; make_train_layout(B, S, T);
+    if (!workspace || workspace_bytes < T.total) return NERF_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t* ws = (uint8_t*)workspace;
+    NERF_CUDA(cudaMemsetAsync(ws + T.zero_begin, 0, (size_t)T.zero_bytes, st));
+    BwdArgs a{};
+    a.stages = (const uint8_t*)packed_bwd;
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
+    a.act = ws + T.off_act; a.stats = reinterpret_cast<const float2*>(ws + T.off_stats);
+    a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz = ws + T.off_dz; a.dh = ws + T.off_dh;
+    a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
+    a.P = T.P; a.P_pad = T.P_pad; a.n_tiles = T.n_tiles; a.tr_tiles = T.tr_tiles;
+    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
+    static int cg = -1;
+    if (cg < 0) { const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2; }
+    rc = (cg == 2) ? launch_bwd<2>(a, st) : launch_bwd<1>(a, st); if (rc) return rc;
+    if (stage == 1) return NERF_OK;
+    rc = launch_wgrad_tc_units(ws, T, st); if (rc) return rc;
+    if (stage == 2) return NERF_OK;
+    const float* gw = reinterpret_cast<const float*>(ws + T.off_gw);
+    const float* gh = reinterpret_cast<const float*>(ws + T.off_gh);
+    const float* hsum = reinterpret_cast<const float*>(ws + T.off_hsum);
+    unfold_weights_kernel<<<dim3(80, 11), 256, 0, st>>>(params, L, gw, gh, hsum, grads);
+    NERF_CUDA_CHECK_LAUNCH();
+    unfold_affine_kernel<<<10, 1024, 0, st>>>(params, L, gw, gh, hsum, grads);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}

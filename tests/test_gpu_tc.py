@@ -118,3 +118,145 @@ def test_tc_hierarchical(model_bf16, g1_ref):
     err = np.abs(r["pixels"].cpu().numpy() - g1_ref["kat_hier_pixels"])
     print("hierarchical bf16 pixel err max/mean", err.max(), err.mean())
     assert err.max() < 0.06 and err.mean() < 6e-3
+
+
+# ------------------------------------------------------------ bf16 training kernels ------
+def _small_image(x16):
+    """[P,16] -> the 4 KB-per-tile small-operand image [16 point groups][2 halves][8 points][8 cols] bf16"""
+    p = x16.shape[0]
+    nt = p // 128
+    v = x16.to(torch.bfloat16).view(nt, 16, 8, 2, 8).permute(0, 1, 3, 2, 4).contiguous()
+    return v.view(torch.uint8).view(nt, 4096)
+
+
+@pytest.mark.parametrize("n_tiles,main,enc,small,ones", [(3, True, False, False, False), (5, False, True, False, True),
+                                                          (37, True, True, False, True), (400, True, True, False, True),
+                                                          (9, False, False, True, False), (300, False, False, True, False)])
+def test_tc_wgrad_gemm(n_tiles, main, enc, small, ones):
+    """dW = dZ^T [X | enc | 1] on tcgen05 with MN-major slab operands against an fp32 matmul of the
+    same bf16-rounded inputs."""
+    from nerf_b200 import _lib
+    from slab_utils import to_slabs, from_slabs
+    g = torch.Generator(device="cuda").manual_seed(n_tiles)
+    p = n_tiles * 128
+    bf = lambda t: t.bfloat16().float()
+    dz = torch.randn(p, 256, device="cuda", generator=g)
+    xm = torch.randn(p, 256, device="cuda", generator=g) if main else None
+    xe = torch.randn(p, 64, device="cuda", generator=g) if enc else None
+    xs = torch.randn(p, 16, device="cuda", generator=g) if small else None
+    dz_s = to_slabs(dz)
+    assert torch.equal(from_slabs(dz_s), bf(dz))
+    xm_s = to_slabs(xm) if main else None
+    xe_s = to_slabs(xe) if enc else None
+    xs_s = _small_image(xs) if small else None
+    ld = 336
+    out = torch.zeros(256, ld, device="cuda")
+    _lib.check(_lib.lib().nerf_tc_wgrad_debug(_lib.ptr(dz_s), _lib.ptr(xm_s), _lib.ptr(xe_s), _lib.ptr(xs_s), int(ones),
+                                              n_tiles, _lib.ptr(out), ld, _lib.stream()), "nerf_tc_wgrad_debug")
+    torch.cuda.synchronize()
+    want = torch.zeros(256, ld, device="cuda")
+    if main: want[:, :256] = bf(dz).T @ bf(xm)
+    if enc: want[:, 256:320] = bf(dz).T @ bf(xe)
+    if ones: want[:, 320:336] = bf(dz).sum(0)[:, None]
+    if small: want[:, :16] = bf(dz).T @ bf(xs)
+    rel = ((out - want).norm() / want.norm()).item()
+    print(f"wgrad n_tiles={n_tiles}: rel-L2 {rel:.2e}")
+    assert rel < 1e-5, rel
+    assert torch.equal(out == 0, want == 0)
+
+
+def _train_fwd(packed, o, d, t, norm=6.0):
+    from nerf_b200 import _lib
+    L = _lib.lib()
+    b, s = t.shape
+    n = L.nerf_g1_train_workspace_bytes(b, s)
+    ws = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    out_t = torch.empty(b, s, device="cuda"); sigma = torch.empty(b, s, device="cuda"); rgb = torch.empty(b, s, 3, device="cuda")
+    _lib.check(L.nerf_g1_train_fwd_tc(_lib.ptr(packed), 3, 3, _lib.ptr(o), _lib.ptr(d), b, s, 2.0, 6.0, None, _lib.ptr(t),
+                                      None, 0, 0, 0, norm, 1, _lib.ptr(out_t), _lib.ptr(sigma), _lib.ptr(rgb),
+                                      _lib.ptr(ws), n, _lib.stream()), "nerf_g1_train_fwd_tc")
+    torch.cuda.synchronize()
+    return ws, n, sigma, rgb
+
+
+def _ws_views(ws, b, s):
+    """mirror of make_train_layout (csrc/tc_layout.cuh)"""
+    up = lambda x: (x + 1023) & ~1023
+    P = b * s; nt = (P + 127) // 128; trt = (nt + 1) & ~1; ppad = trt * 128
+    o = 0; v = {}
+    v["pex"] = ws[o:o + trt * 16384].view(trt, 1, 128, 128); o += trt * 16384
+    v["ped"] = ws[o:o + trt * 16384].view(trt, 1, 128, 128); o += trt * 16384
+    v["act"] = ws[o:o + 10 * trt * 65536].view(10, trt, 4, 128, 128); o += 10 * trt * 65536
+    v["dz"] = ws[o:o + 10 * trt * 65536].view(10, trt, 4, 128, 128); o += 10 * trt * 65536
+    v["stats"] = ws[o:o + 10 * ppad * 8].view(torch.float32).view(10, ppad, 2); o += up(10 * ppad * 8)
+    o += trt * 4096
+    v["gw"] = ws[o:o + 10 * 256 * 336 * 4].view(torch.float32).view(10, 256, 336); o += up(10 * 256 * 336 * 4)
+    v["gh"] = ws[o:o + 2 * 256 * 16 * 4].view(torch.float32).view(2, 256, 16); o += up(2 * 256 * 16 * 4)
+    v["hsum"] = ws[o:o + 16].view(torch.float32)
+    return v
+
+
+def test_tc_train_forward_saves_activations(g1_ref, packed):
+    """The training forward returns exactly the inference kernel's sigma/rgb and leaves bf16 slab
+    images of every unit's normalised output (== the debug dump rounded to bf16) in the workspace."""
+    from nerf_b200 import ops
+    from slab_utils import from_slabs
+    o, d, t = _cuda(g1_ref["kat_o"]), _cuda(g1_ref["kat_d"]), _cuda(g1_ref["kat_t"])
+    b, s = t.shape
+    ws, n, sigma, rgb = _train_fwd(packed, o, d, t)
+    sig0, rgb0, _ = ops.g1_mlp_tc_debug(packed, o, d, t, 6.0)
+    assert torch.equal(sigma, sig0) and torch.equal(rgb, rgb0)
+    v = _ws_views(ws, b, s)
+    for layer in (0, 3, 4, 7, 9):
+        _, _, dbg = ops.g1_mlp_tc_debug(packed, o, d, t, 6.0, dbg_layer=layer)
+        got = from_slabs(v["act"][layer], b * s)
+        assert torch.equal(got, dbg.bfloat16().float()), layer
+        st = v["stats"][layer, :b * s]
+        assert torch.isfinite(st).all() and (st[:, 0] > 0).all()
+        # relu floor of every row is the stored shift
+        assert torch.allclose(got.min(dim=1).values, st[:, 1].bfloat16().float())
+    ex_want = from_slabs(v["pex"], b * s)[:, :60]
+    assert ex_want.abs().max().item() <= 1.0 and from_slabs(v["pex"], b * s)[:, 60:].abs().max().item() == 0.0
+
+
+def _oracle_param_grads(g1_oracle, o, d, t, d_sigma, d_rgb):
+    g1_oracle.zero_grad()
+    _, ex, ed = g1_oracle.encode(o, d, t)
+    density, color = g1_oracle.mlp(ex, ed)
+    ((density[..., 0] * d_sigma).sum() + (color * d_rgb).sum()).backward()
+    out = {k: p.grad.clone() for k, p in g1_oracle.named_parameters()}
+    g1_oracle.zero_grad()
+    return out
+
+
+def test_tc_train_backward_gradients(g1_oracle, g1_ref, model_bf16, packed, nerf_pth_state_dict):
+    """All 44 parameter gradients of the bf16 tensor-core backward against fp32 autograd of the
+    oracle for the same upstream (d_sigma, d_rgb): cosine >= 0.999 (SURVEY 8d D2, bf16 bar)."""
+    from nerf_b200 import _lib, ops
+    L = _lib.lib()
+    o, d, t = _cuda(g1_ref["kat_o"]), _cuda(g1_ref["kat_d"]), _cuda(g1_ref["kat_t"])
+    b, s = t.shape
+    gen = torch.Generator().manual_seed(11)
+    d_sigma = torch.randn(b, s, generator=gen) * 0.1
+    d_rgb = torch.randn(b, s, 3, generator=gen)
+    want = _oracle_param_grads(g1_oracle, o.cpu(), d.cpu(), t.cpu(), d_sigma, d_rgb)
+    flat = model_bf16.flat_parameters()
+    ws, n, _, _ = _train_fwd(packed, o, d, t)
+    pb = torch.empty(L.nerf_g1_packed_bwd_bytes(3, 3), dtype=torch.uint8, device="cuda")
+    _lib.check(L.nerf_g1_pack_weights_bwd(_lib.ptr(flat), 3, 3, _lib.ptr(pb), _lib.stream()), "pack_bwd")
+    grads = torch.full_like(flat, float("nan"))
+    ds, dc = d_sigma.cuda(), d_rgb.cuda()
+    _lib.check(L.nerf_g1_train_bwd_tc(_lib.ptr(packed), _lib.ptr(pb), _lib.ptr(flat), 3, 3, _lib.ptr(ds), _lib.ptr(dc),
+                                      b, s, _lib.ptr(grads), _lib.ptr(ws), n, 0, _lib.stream()), "nerf_g1_train_bwd_tc")
+    torch.cuda.synchronize()
+    assert torch.isfinite(grads).all()
+    off, total = ops.g1_param_layout(3, 3)
+    worst = 1.0
+    for (k, w), o_ in zip(want.items(), off):
+        got = grads[o_:o_ + w.numel()].view(w.shape).cpu()
+        cos = torch.nn.functional.cosine_similarity(got.flatten(), w.flatten(), dim=0).item()
+        rel = ((got - w).norm() / w.norm()).item()
+        print(f"{k:24s} cos {cos:.5f} rel-L2 {rel:.4f}")
+        worst = min(worst, cos)
+    assert list(want.keys()) == list(nerf_pth_state_dict.keys())
+    assert worst >= 0.999, worst
