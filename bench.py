@@ -233,23 +233,62 @@ def run_ours(args):
     # ---- dominant kernel group timed alone: MLP fwd+bwd through the C ABI ----
     b, s = RAYS, SAMPLES
     o, d, tgt = pool_d[0]
-    t = ops.sample_linear(NEAR, FAR, s, b, dev, jitter=True, seed=1)
-    ex, ed, _ = ops.encode_g1(o, d, t, 6.0)
-    prec = ops.PRECISIONS[args.precision]
-    nbytes = _lib.lib().nerf_g1_mlp_workspace_bytes(b * s, 3, 3, prec, 1)
-    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-    sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
-    dsig = torch.randn(b, s, device=dev); drgb = torch.randn(b, s, 3, device=dev)
-    grads = torch.zeros_like(model.flat_parameters())
     flat = model.flat_parameters()
     P = _lib.ptr
+    L = _lib.lib()
+    kernels = {}
+    if args.precision == "bf16":
+        z = trainer._tc_buffers(b, s, dev)
+        ladder = model._ladder(NEAR, FAR, s, dev)
+        grads = torch.zeros_like(flat)
 
-    def mlp_only(i):
-        _lib.check(_lib.lib().nerf_g1_mlp_fwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, 1, P(sigma), P(rgb), P(ws), nbytes, _lib.stream()), "fwd")
-        _lib.check(_lib.lib().nerf_g1_mlp_bwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, P(dsig), P(drgb), P(grads), P(ws), nbytes, _lib.stream()), "bwd")
-    for i in range(3):
-        mlp_only(i)
-    ms_mlp = float(np.mean(timed_steps(mlp_only, max(K // 2, 3), flush)))
+        def k_fwd(i):
+            _lib.check(L.nerf_g1_train_fwd_tc(P(z["packed"]), 3, 3, P(o), P(d), b, s, NEAR, FAR, P(ladder), None, None, 1, 1, 0,
+                                              6.0, 1, P(z["t"]), P(z["sigma"]), P(z["rgb"]), P(z["ws"]), z["n"], _lib.stream()), "fwd")
+
+        def k_bwd(stage):
+            def f(i):
+                _lib.check(L.nerf_g1_train_bwd_tc(P(z["packed"]), P(z["packed_bwd"]), P(flat), 3, 3, P(z["d_sigma"]), P(z["d_rgb"]),
+                                                  b, s, P(grads), P(z["ws"]), z["n"], stage, _lib.stream()), "bwd")
+            return f
+
+        def mlp_only(i):
+            k_fwd(i); k_bwd(0)(i)
+        for i in range(3):
+            mlp_only(i)
+        n_it = max(K // 2, 5)
+        ms_fwd = float(np.mean(timed_steps(k_fwd, n_it, flush)))
+        ms_dgrad = float(np.mean(timed_steps(k_bwd(1), n_it, flush)))
+        ms_dw = float(np.mean(timed_steps(k_bwd(2), n_it, flush)))
+        ms_mlp = float(np.mean(timed_steps(mlp_only, n_it, flush)))
+        n_tiles = (b * s + 127) // 128
+        wgrad_bytes = n_tiles * ((10 + 9 + 2) * 65536 + 3 * 16384 + 2 * 4096)     # dz + unit inputs + head inputs + encodings + dh
+        kernels = {
+            "g1_fused_tc_kernel<2,train>": {"ms": ms_fwd, "bound": "tensor", "achieved": FLOP_PER_POINT_FWD * b * s / ms_fwd / 1e9,
+                                            "unit": "TFLOP/s", "frac": FLOP_PER_POINT_FWD * b * s / ms_fwd / 1e9 / peaks["tensor_sustained"]},
+            "g1_bwd_tc_kernel<2>": {"ms": ms_dgrad, "bound": "tensor", "achieved": 2 * 9 * 65536 * b * s / ms_dgrad / 1e9,
+                                    "unit": "TFLOP/s", "frac": 2 * 9 * 65536 * b * s / ms_dgrad / 1e9 / peaks["tensor_sustained"]},
+            "g1_wgrad_tc_kernel": {"ms": ms_dw - ms_dgrad, "bound": "hbm", "achieved": wgrad_bytes / (ms_dw - ms_dgrad) / 1e6,
+                                   "unit": "GB/s", "frac": wgrad_bytes / (ms_dw - ms_dgrad) / 1e6 / peaks["hbm"]},
+        }
+        mlp_kernel_name = "G1 MLP fwd+bwd on tcgen05 (g1_fused_tc_kernel<train> + g1_bwd_tc_kernel + g1_wgrad_tc_kernel + unfold)"
+    else:
+        t = ops.sample_linear(NEAR, FAR, s, b, dev, jitter=True, seed=1)
+        ex, ed, _ = ops.encode_g1(o, d, t, 6.0)
+        prec = ops.PRECISIONS[args.precision]
+        nbytes = L.nerf_g1_mlp_workspace_bytes(b * s, 3, 3, prec, 1)
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
+        dsig = torch.randn(b, s, device=dev); drgb = torch.randn(b, s, 3, device=dev)
+        grads = torch.zeros_like(flat)
+
+        def mlp_only(i):
+            _lib.check(L.nerf_g1_mlp_fwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, 1, P(sigma), P(rgb), P(ws), nbytes, _lib.stream()), "fwd")
+            _lib.check(L.nerf_g1_mlp_bwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, P(dsig), P(drgb), P(grads), P(ws), nbytes, _lib.stream()), "bwd")
+        for i in range(3):
+            mlp_only(i)
+        ms_mlp = float(np.mean(timed_steps(mlp_only, max(K // 2, 3), flush)))
+        mlp_kernel_name = "G1 MLP fwd+bwd (nerf_g1_mlp_fwd + nerf_g1_mlp_bwd, FFMA tiles)"
     mlp_tflops = FLOP_PER_POINT_FWD_BWD * b * s / (ms_mlp * 1e-3) / 1e12
 
     # ---- compositing fwd+bwd alone at a sweep size larger than L2 (HBM roofline) ----
@@ -272,15 +311,17 @@ def run_ours(args):
     comp_bwd_gbs = COMPOSITE_BWD_BYTES_PER_RAY * cb / (ms_cb * 1e-3) / 1e9
     del csig, crgb, ct, dsg, drg
 
-    # ---- render throughput (D1-shape rays through render_image, 800x800 when the fused path exists) ----
+    # ---- render throughput: 800x800 x 64 (fused bf16 path) or 200x200 (fp32 path) through render_image ----
     from oracle.g1 import pose_spherical, TINY_NERF_FOCAL
     pose = pose_spherical(30.0, -30.0, 4.0311).to(dev)
-    rh = rw = 200
+    rh = rw = 800 if args.precision == "bf16" else 200
+    rfocal = TINY_NERF_FOCAL * rh / 100
     with torch.no_grad():
-        model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, TINY_NERF_FOCAL * 2, NEAR, FAR, SAMPLES)
+        model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES)
         ms_r = timed_steps(lambda i: model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw,
-                                                        TINY_NERF_FOCAL * 2, NEAR, FAR, SAMPLES), 3, flush)
+                                                        rfocal, NEAR, FAR, SAMPLES), 3, flush)
     render_rps = rh * rw / (float(np.mean(ms_r)) * 1e-3)
+    render_tflops = render_rps * SAMPLES * FLOP_PER_POINT_FWD / 1e12
 
     # max over ranks of the timed totals
     if world > 1:
@@ -307,14 +348,16 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": RAYS * 9 * 4, "d2h_bytes_per_step": 4},
             "gpu_launches": trainer.kernel_launches * K,
             "clocks": clk.summary(),
-            "roofline": {"bound": "tensor", "kernel": "G1 MLP fwd+bwd (nerf_g1_mlp_fwd + nerf_g1_mlp_bwd)",
+            "roofline": {"bound": "tensor", "kernel": mlp_kernel_name,
                          "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
                          "frac": mlp_tflops / tensor_peak, "traffic": None, "peak_source": peaks["src"] + " bf16 sustained",
                          "ms": ms_mlp},
             "roofline_hbm": {"composite_fwd": {"achieved": comp_fwd_gbs, "frac": comp_fwd_gbs / peaks["hbm"], "ms": ms_cf},
                              "composite_bwd": {"achieved": comp_bwd_gbs, "frac": comp_bwd_gbs / peaks["hbm"], "ms": ms_cb},
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
-            "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image"},
+            "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
+                       "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},
+            "kernels": kernels,
             "loss": loss_val,
         }
         if cpu:
@@ -330,7 +373,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
