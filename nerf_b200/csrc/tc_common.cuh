@@ -49,6 +49,17 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     return v;
 }
 
+// One lane of a CONVERGED warp (elect.sync).  Role loops (TMA producer, MMA issuer) are run by the
+// whole warp with warp-uniform values and only the asynchronous instruction itself is guarded by
+// this predicate: the operands then live in uniform registers.  Under `if (lane == 0)` the loop is
+// divergent, operands sit in vector registers and every UTCHMMA / UBLKCP is wrapped in an
+// ELECT + R2UR waterfall loop (~130 cycles per MMA issued, measured).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 // ------------------------------------------------------------- proxies/fences ----
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -149,8 +160,13 @@ __device__ __forceinline__ void cluster_sync_all() {
 __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
     uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank)); return r;
 }
+// Remote arrive with the default (.release.cta) semantics, as CUTLASS's ClusterBarrier::arrive does.
+// The explicit .release.cluster form lowers to MEMBAR.ALL.GPU + ERRBAR in front of every arrive
+// (~0.8 us with stores in flight), which made the one-thread weight-arrival relay THE bottleneck of
+// all three tensor-core kernels.  Data hand-offs stay ordered by fence.proxy.async (generic -> async
+// proxy) on the producer side and by the mbarrier phase itself on the consumer side.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc2(uint32_t smem_result_addr, uint32_t ncols) {   // one warp in EACH CTA of the pair
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_result_addr), "r"(ncols) : "memory");

@@ -159,7 +159,8 @@ extern "C" int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const fl
                               (uint8_t*)workspace, T, (cudaStream_t)stream);
 }
 
-// stage: 0 = all, 1 = stop after the data-gradient kernel, 2 = stop after the weight-gradient GEMM (tests)
+// stage: 0 = all, 1 = stop after the data-gradient kernel, 2 = stop after the weight-gradient GEMM (tests),
+//        3 = the weight-gradient GEMM alone on whatever the workspace holds (timing)
 extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float* params, int Dx, int Dd,
                                     const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
                                     void* workspace, int64_t workspace_bytes, int stage, void* stream) {
@@ -181,10 +182,10 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
     static int cg = -1;
     if (cg < 0) { const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2; }
-    rc = (cg == 2) ? launch_bwd<2>(a, st) : launch_bwd<1>(a, st); if (rc) return rc;
+    if (stage != 3) { rc = (cg == 2) ? launch_bwd<2>(a, st) : launch_bwd<1>(a, st); if (rc) return rc; }
     if (stage == 1) return NERF_OK;
     rc = launch_wgrad_tc_units(ws, T, st); if (rc) return rc;
-    if (stage == 2) return NERF_OK;
+    if (stage == 2 || stage == 3) return NERF_OK;
     const float* gw = reinterpret_cast<const float*>(ws + T.off_gw);
     const float* gh = reinterpret_cast<const float*>(ws + T.off_gh);
     const float* hsum = reinterpret_cast<const float*>(ws + T.off_hsum);

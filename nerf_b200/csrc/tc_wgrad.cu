@@ -8,20 +8,29 @@
 // the CONTRACTION index here, so both operands are "MN-major" UMMA operands (feature index
 // contiguous): the same bytes the forward consumed K-major feed this GEMM without a transpose.
 //
-// Work = 20 (unit, out-half) combinations x n_tiles point tiles, cut into 148 equal-cost
-// contiguous segments (one per persistent CTA).  A CTA accumulates its segment's 128 x K_l block
-// in TMEM over all its tiles and flushes it once with vector fp32 reductions into dW'_l.
-//   warp 0   TMA producer (1-D bulk copies of half slabs: 64 points per pipeline stage)
-//   warp 1   MMA issuer   (M=128, N=256 hidden + N=64 encoding columns, K=16 points per MMA)
+// Work = 12 (unit | head) x n_tiles point tiles, cut into 74 equal-cost contiguous segments, one
+// per CTA PAIR (cluster of 2, cta_group::2): the pair issues M=256 MMAs, CTA r holding output
+// features [128r, 128r+128) (its half of dZ) and input features [128r, 128r+128) (its half of the
+// B operand), so every byte is fetched from HBM/L2 exactly once per pair.  A pair accumulates its
+// segment's 256 x K_l block in TMEM over all its tiles and flushes it once with vector fp32
+// reductions into dW'_l.
+//   warp 0   TMA producer (64-point stages; lanes 0-4 issue the stage's five 8 KB bulk copies together)
+//   warp 1   MMA issuer (leader; N=256 hidden + N=128 [encoding | ones] or N=32 ones, K=16 points
+//            per MMA, descriptors advanced with one 32-bit add) / arrival relay (peer)
 //   warps 2-5 flush       (tcgen05.ld -> red.global.add.v4.f32)
-// The kernel is HBM-bound: 32 KB of dZ + 64..80 KB of activations per 128-point tile and half.
+// The kernel is HBM-bound: 64 KB of dZ + 64..80 KB of activations per 128-point tile and unit.
+// (v1 ran one CTA per out-half with M=128 MMAs on 64-point stages: its single issuing thread needed
+//  ~2.6 K cycles per stage for 12 small MMAs and 7 copies -- instruction-latency bound at 0.95 ms.)
 #include "tc_layout.cuh"
 #include <stdlib.h>
+#include <stdio.h>
 
 #define WG_THREADS 192
-#define WG_STAGES 4
-#define WG_HALF 8192                      // half a slab: 64 points x 128 B
-#define WG_STAGE_BYTES (7 * WG_HALF)      // 2 dZ + 4 hidden + 1 encoding half slabs
+#define WG_STAGES 5
+#define WG_HALF 8192                      // half a slab: 64 points x 128 B; one pipeline stage covers 64 points
+#define WG_OFF_B (2 * WG_HALF)            // stage: [A: 2 dZ half slabs | B: 2 hidden half slabs (or 2 KB of the small operand) | E: encoding half slab]
+#define WG_OFF_E (4 * WG_HALF)
+#define WG_STAGE_BYTES (5 * WG_HALF)
 #define WG_MAX_SEGS 24
 #define WG_SM_ONES (WG_STAGES * WG_STAGE_BYTES)      // 1 KB of bf16 1.0: the "ones" operand that yields column sums
 #define WG_SM_BAR (WG_SM_ONES + 1024)
@@ -44,9 +53,11 @@ struct WgradArgs {
     int ones[WG_NU];
     int n_tiles;
     uint32_t wait_hint;
+    int dbg;                         // experiments: bit 0 = no MMAs, bit 1 = no loads
+    long long* prof;                 // NERF_WG_PROF: per-CTA cycle counters [8]
 };
-__host__ __device__ inline int wg_cost(const WgradArgs& a, int l) {      // quarter half-slabs loaded per tile half
-    return 8 + (a.xmain[l] ? 16 : 0) + (a.xenc[l] ? 4 : 0) + (a.xsmall[l] ? 1 : 0);
+__host__ __device__ inline int wg_cost(const WgradArgs& a, int l) {      // quarter slabs the leader CTA loads per tile
+    return 8 + (a.xmain[l] ? 8 : 0) + (a.xenc[l] ? 4 : 0) + (a.xsmall[l] ? 1 : 0);
 }
 
 namespace tc {
@@ -86,7 +97,9 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 }
 }  // namespace tc
 
-struct WgSeg { int l, h, tb, te; };
+struct WgSeg { int l, tb, te, pad; };
+
+__device__ __forceinline__ uint64_t wg_desc(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
 
 __global__ void __launch_bounds__(WG_THREADS, 1) g1_wgrad_tc_kernel(const WgradArgs a) {
     extern __shared__ uint8_t smem_raw[];
@@ -101,112 +114,151 @@ __global__ void __launch_bounds__(WG_THREADS, 1) g1_wgrad_tc_kernel(const WgradA
     volatile int* n_segs_s = reinterpret_cast<volatile int*>(sm + WG_SM_BAR + 8 * (2 * WG_STAGES + 2) + 4);
     WgSeg* segs = reinterpret_cast<WgSeg*>(sm + WG_SM_SEGS);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int n_pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < WG_STAGES; ++s) { tc::mbar_init(full(s), 1); tc::mbar_init(empty(s), 1); }
-        tc::mbar_init(acc_done, 1); tc::mbar_init(acc_free, 128);
+        for (int s = 0; s < WG_STAGES; ++s) { tc::mbar_init(full(s), leader ? 2 : 1); tc::mbar_init(empty(s), 1); }
+        tc::mbar_init(acc_done, 1); tc::mbar_init(acc_free, 8);
         tc::fence_barrier_init();
-        // equal-cost contiguous cut of the (unit, half, tile) work list
+        // equal-cost contiguous cut of the (unit, tile) work list over the CTA pairs
         int64_t total = 0;
-        for (int l = 0; l < WG_NU; ++l) if (a.dz[l]) total += 2ll * a.n_tiles * wg_cost(a, l);
-        const int64_t lo = total * blockIdx.x / gridDim.x, hi = total * (blockIdx.x + 1) / gridDim.x;
+        for (int l = 0; l < WG_NU; ++l) if (a.dz[l]) total += (int64_t)a.n_tiles * wg_cost(a, l);
+        const int64_t lo = total * pair / n_pairs, hi = total * (pair + 1) / n_pairs;
         int n = 0; int64_t pre = 0;
         for (int l = 0; l < WG_NU; ++l) {
             if (!a.dz[l]) continue;
             const int64_t c = wg_cost(a, l);
-            for (int h = 0; h < 2; ++h) {
-                const int64_t end = pre + c * a.n_tiles;
-                const int64_t s0 = lo > pre ? lo : pre, s1 = hi < end ? hi : end;
-                if (s1 > s0) {
-                    const int tb = (int)((s0 - pre + c - 1) / c), te = (int)((s1 - pre + c - 1) / c);
-                    if (te > tb && n < WG_MAX_SEGS) { segs[n].l = l; segs[n].h = h; segs[n].tb = tb; segs[n].te = te; ++n; }
-                }
-                pre = end;
+            const int64_t end = pre + c * a.n_tiles;
+            const int64_t s0 = lo > pre ? lo : pre, s1 = hi < end ? hi : end;
+            if (s1 > s0) {
+                const int tb = (int)((s0 - pre + c - 1) / c), te = (int)((s1 - pre + c - 1) / c);
+                if (te > tb && n < WG_MAX_SEGS) { segs[n].l = l; segs[n].tb = tb; segs[n].te = te; ++n; }
             }
+            pre = end;
         }
         *n_segs_s = n;
     }
+    // constant "ones" operands: a 1 KB no-swizzle block, and (peer CTA) the encoding position of every stage
     for (int i = threadIdx.x; i < 256; i += WG_THREADS) reinterpret_cast<uint32_t*>(sm + WG_SM_ONES)[i] = 0x3F803F80u;
+    if (!leader)
+        for (int s = 0; s < WG_STAGES; ++s)
+            for (int i = threadIdx.x; i < WG_HALF / 4; i += WG_THREADS)
+                reinterpret_cast<uint32_t*>(sm + s * WG_STAGE_BYTES + WG_OFF_E)[i] = 0x3F803F80u;
     tc::fence_proxy_async_smem();
-    if (warp == 1) tc::tmem_alloc(tc::smem_u32((const void*)tmem_slot), 512);
+    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 512);
     tc::tcgen05_fence_before();
-    __syncthreads();
+    tc::cluster_sync_all();
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const int n_segs = *n_segs_s;
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int si = 0; si < n_segs; ++si) {
-                const WgSeg sg = segs[si];
-                const uint8_t* dz = a.dz[sg.l]; const uint8_t* xm = a.xmain[sg.l]; const uint8_t* xe = a.xenc[sg.l];
-                const uint8_t* xs = a.xsmall[sg.l];
-                const uint32_t bytes = (2 + (xm ? 4 : 0) + (xe ? 1 : 0)) * WG_HALF + (xs ? 2048 : 0);
-                for (int t = sg.tb; t < sg.te; ++t)
-                    for (int hf = 0; hf < 2; ++hf, ++it) {
-                        const int slot = it % WG_STAGES; const uint32_t ph = (it / WG_STAGES) & 1;
-                        tc::mbar_wait(empty(slot), ph ^ 1, a.wait_hint);
-                        tc::mbar_arrive_expect_tx(full(slot), bytes);
-                        const uint32_t st = base + slot * WG_STAGE_BYTES;
-                        const size_t toff = (size_t)t * 4 * TC_SLAB_BYTES + hf * WG_HALF;
-                        tc::tma_load_1d(st, dz + toff + (size_t)(2 * sg.h) * TC_SLAB_BYTES, WG_HALF, full(slot));
-                        tc::tma_load_1d(st + WG_HALF, dz + toff + (size_t)(2 * sg.h + 1) * TC_SLAB_BYTES, WG_HALF, full(slot));
-                        if (xm)
-                            for (int s = 0; s < 4; ++s)
-                                tc::tma_load_1d(st + (2 + s) * WG_HALF, xm + toff + (size_t)s * TC_SLAB_BYTES, WG_HALF, full(slot));
-                        if (xe) tc::tma_load_1d(st + 6 * WG_HALF, xe + (size_t)t * TC_SLAB_BYTES + hf * WG_HALF, WG_HALF, full(slot));
-                        if (xs) tc::tma_load_1d(st + 2 * WG_HALF, xs + (size_t)t * 4096 + hf * 2048, 2048, full(slot));
+        // ===================== TMA producer: this CTA's halves of both operands =====================
+        // (whole warp, warp-uniform addresses; one elected lane issues the stage's bulk copies)
+        uint32_t it = 0;
+        for (int si = 0; si < n_segs; ++si) {
+            const WgSeg sg = segs[si];
+            const uint8_t* xm = a.xmain[sg.l]; const uint8_t* xs = a.xsmall[sg.l];
+            const uint8_t* xe = leader ? a.xenc[sg.l] : nullptr;
+            const uint32_t bytes = 2 * WG_HALF + (xm ? 2 * WG_HALF : 0) + (xe ? WG_HALF : 0) + (xs ? 2048 : 0);
+            const uint8_t* pa = a.dz[sg.l] + ((size_t)sg.tb * 4 + 2 * rank) * TC_SLAB_BYTES;
+            const uint8_t* pm = xm ? xm + ((size_t)sg.tb * 4 + 2 * rank) * TC_SLAB_BYTES : nullptr;
+            const uint8_t* pe = xe ? xe + (size_t)sg.tb * TC_SLAB_BYTES : nullptr;
+            const uint8_t* ps = xs ? xs + (size_t)sg.tb * 4096 : nullptr;
+            for (int n = 2 * (sg.te - sg.tb), hf = 0; n > 0; --n, ++it, hf ^= 1) {
+                const int slot = it % WG_STAGES; const uint32_t ph = (it / WG_STAGES) & 1;
+                const long long c0 = a.prof ? clock64() : 0;
+                tc::mbar_wait(empty(slot), ph ^ 1, a.wait_hint);
+                if (a.prof && lane == 0) a.prof[blockIdx.x * 8 + 0] += clock64() - c0;
+                const uint32_t st = base + slot * WG_STAGE_BYTES, fb = full(slot);
+                if (tc::elect_one()) {
+                    if (a.dbg & 2) tc::mbar_arrive(fb);
+                    else {
+                        tc::mbar_arrive_expect_tx(fb, bytes);
+                        tc::tma_load_1d(st, pa, WG_HALF, fb);
+                        tc::tma_load_1d(st + WG_HALF, pa + TC_SLAB_BYTES, WG_HALF, fb);
+                        if (pm) { tc::tma_load_1d(st + WG_OFF_B, pm, WG_HALF, fb); tc::tma_load_1d(st + WG_OFF_B + WG_HALF, pm + TC_SLAB_BYTES, WG_HALF, fb); }
+                        if (pe) tc::tma_load_1d(st + WG_OFF_E, pe, WG_HALF, fb);
+                        if (ps) tc::tma_load_1d(st + WG_OFF_B, ps, 2048, fb);
                     }
+                }
+                __syncwarp();
+                const size_t adv = hf ? (size_t)(4 * TC_SLAB_BYTES - WG_HALF) : (size_t)WG_HALF;
+                pa += adv; if (pm) pm += adv; if (pe) pe += WG_HALF; if (ps) ps += 2048;
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc_main = tc::umma_idesc_bf16_mn(128, 256), idesc_enc = tc::umma_idesc_bf16_mn(128, 64);
-            constexpr uint32_t idesc_16 = tc::umma_idesc_bf16_mn(128, 16);
-            const uint64_t ones_desc = tc::umma_desc_noswz_mn(base + WG_SM_ONES, 128, 128);
+        if (leader) {
+            // ===================== MMA issuer =====================
+            constexpr uint32_t idesc_main = tc::umma_idesc_bf16_mn(256, 256), idesc_enc = tc::umma_idesc_bf16_mn(256, 128);
+            constexpr uint32_t idesc_32 = tc::umma_idesc_bf16_mn(256, 32);
+            // descriptor words: hi = SBO | version | layout, lo = start address | LBO; K advances by 2048 B (+128 in lo)
+            constexpr uint32_t hi_sw = (1024u >> 4) | (1u << 14) | (2u << 29), hi_ns = (128u >> 4) | (1u << 14);
+            constexpr uint32_t lbo_half = (uint32_t)(WG_HALF >> 4) << 16;
+            const uint64_t ones_desc = wg_desc(hi_ns, (((base + WG_SM_ONES) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16));
             uint32_t it = 0;
             for (int si = 0; si < n_segs; ++si) {
                 const WgSeg sg = segs[si];
                 const bool has_main = a.xmain[sg.l] != nullptr, has_enc = a.xenc[sg.l] != nullptr;
                 const bool has_small = a.xsmall[sg.l] != nullptr, has_ones = a.ones[sg.l] != 0;
-                if (si > 0) { tc::mbar_wait(acc_free, (si - 1) & 1, a.wait_hint); tc::tcgen05_fence_after(); }
-                bool first = true;
-                for (int t = sg.tb; t < sg.te; ++t)
-                    for (int hf = 0; hf < 2; ++hf, ++it) {
-                        const int slot = it % WG_STAGES; const uint32_t ph = (it / WG_STAGES) & 1;
-                        tc::mbar_wait(full(slot), ph, a.wait_hint);
-                        tc::tcgen05_fence_after();
-                        const uint32_t st = base + slot * WG_STAGE_BYTES;
+                if (si > 0) { const long long cf = a.prof ? clock64() : 0; tc::mbar_wait(acc_free, (si - 1) & 1, a.wait_hint); tc::tcgen05_fence_after();
+                              if (a.prof && lane == 0) a.prof[blockIdx.x * 8 + 4] += clock64() - cf; }
+                uint32_t acc = 0;
+                for (int n = 2 * (sg.te - sg.tb); n > 0; --n, ++it) {
+                    const int slot = it % WG_STAGES; const uint32_t ph = (it / WG_STAGES) & 1;
+                    const long long c0 = a.prof ? clock64() : 0;
+                    tc::mbar_wait(full(slot), ph, a.wait_hint);
+                    const long long c1 = a.prof ? clock64() : 0;
+                    if (a.prof && lane == 0) { a.prof[blockIdx.x * 8 + 1] += c1 - c0; a.prof[blockIdx.x * 8 + 3] += 1; }
+                    tc::tcgen05_fence_after();
+                    if (a.dbg & 1) { if (lane == 0) { tc::mbar_arrive_cluster(tc::mapa(empty(slot), 0)); tc::mbar_arrive_cluster(tc::mapa(empty(slot), 1)); } continue; }
+                    const uint32_t st = ((base + slot * WG_STAGE_BYTES) & 0x3FFFFu) >> 4;
+                    uint32_t a_lo = st | lbo_half, m_lo = (st + (WG_OFF_B >> 4)) | lbo_half, e_lo = (st + (WG_OFF_E >> 4)) | lbo_half;
+                    uint32_t s_lo = (st + (WG_OFF_B >> 4)) | ((256u >> 4) << 16);
+                    if (tc::elect_one()) {
 #pragma unroll
                         for (int kk = 0; kk < 4; ++kk) {
-                            const uint64_t ad = tc::umma_desc_sw128_mn(st + kk * 2048, WG_HALF, 1024);
-                            if (has_main)
-                                tc::umma_bf16(tmem_base, ad, tc::umma_desc_sw128_mn(st + 2 * WG_HALF + kk * 2048, WG_HALF, 1024),
-                                              idesc_main, first ? 0u : 1u);
-                            if (has_enc)
-                                tc::umma_bf16(tmem_base + 256, ad,
-                                              tc::umma_desc_sw128_mn(st + 6 * WG_HALF + kk * 2048, WG_HALF, 1024), idesc_enc, first ? 0u : 1u);
-                            if (has_ones) tc::umma_bf16(tmem_base + 320, ad, ones_desc, idesc_16, first ? 0u : 1u);
-                            if (has_small)
-                                tc::umma_bf16(tmem_base, ad, tc::umma_desc_noswz_mn(st + 2 * WG_HALF + kk * 512, 256, 128), idesc_16, first ? 0u : 1u);
-                            first = false;
+                            const uint64_t ad = wg_desc(hi_sw, a_lo + kk * 128);
+                            const uint32_t ac = (kk == 0) ? acc : 1u;
+                            if (has_main) tc::umma_bf16_2cta(tmem_base, ad, wg_desc(hi_sw, m_lo + kk * 128), idesc_main, ac);
+                            if (has_enc) tc::umma_bf16_2cta(tmem_base + 256, ad, wg_desc(hi_sw, e_lo + kk * 128), idesc_enc, ac);
+                            else if (has_ones) tc::umma_bf16_2cta(tmem_base + 320, ad, ones_desc, idesc_32, ac);
+                            if (has_small) tc::umma_bf16_2cta(tmem_base, ad, wg_desc(hi_ns, s_lo + kk * 32), idesc_32, ac);
                         }
-                        tc::umma_commit(empty(slot));
+                        tc::umma_commit_2cta(empty(slot));
                     }
-                tc::umma_commit(acc_done);
+                    __syncwarp();
+                    acc = 1;
+                    if (a.prof && lane == 0) a.prof[blockIdx.x * 8 + 2] += clock64() - c1;
+                }
+                if (tc::elect_one()) tc::umma_commit_2cta(acc_done);
+                __syncwarp();
             }
+        } else if (lane == 0 && !leader) {
+            // ===================== peer relay: "my halves have landed" -> leader's full barrier =====================
+            uint32_t it = 0;
+            for (int si = 0; si < n_segs; ++si)
+                for (int n = 2 * (segs[si].te - segs[si].tb); n > 0; --n, ++it) {
+                    const int slot = it % WG_STAGES; const uint32_t ph = (it / WG_STAGES) & 1;
+                    tc::mbar_wait(full(slot), ph, a.wait_hint);
+                    tc::mbar_arrive_cluster(tc::mapa(full(slot), 0));
+                }
         }
     } else {
+        // ===================== flush: this CTA's 128 output features =====================
         const uint32_t q = warp & 3;                                   // TMEM lane quarter of this warp
         const uint32_t row = q * 32 + lane;
         const uint32_t taddr = tmem_base + ((q * 32u) << 16);
+        const uint32_t free_remote = tc::mapa(acc_free, 0);
         for (int si = 0; si < n_segs; ++si) {
             const WgSeg sg = segs[si];
             const bool has_main = a.xmain[sg.l] != nullptr, has_enc = a.xenc[sg.l] != nullptr;
-            float* o = a.out[sg.l] + (size_t)(sg.h * 128 + row) * a.ld[sg.l];
+            float* o = a.out[sg.l] + (size_t)(rank * 128 + row) * a.ld[sg.l];
             tc::mbar_wait(acc_done, si & 1, a.wait_hint);
             tc::tcgen05_fence_after();
+            const long long cfl = a.prof ? clock64() : 0;
             for (int c = 0; c < 336; c += 16) {
                 const bool live = c < 256 ? (has_main || (c == 0 && a.xsmall[sg.l])) : (c < 320 ? has_enc : a.ones[sg.l] != 0);
                 if (!live) continue;
@@ -217,12 +269,14 @@ __global__ void __launch_bounds__(WG_THREADS, 1) g1_wgrad_tc_kernel(const WgradA
                     tc::red_add_v4(o + c + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
             }
             tc::tcgen05_fence_before();
-            tc::mbar_arrive(acc_free);
+            __syncwarp();
+            if (a.prof && threadIdx.x == 64) a.prof[blockIdx.x * 8 + 5] += clock64() - cfl;
+            if (lane == 0) tc::mbar_arrive_cluster(free_remote);
         }
     }
     tc::tcgen05_fence_before();
-    __syncthreads();
-    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc(tmem_base, 512); }
+    tc::cluster_sync_all();
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 512); }
 }
 
 int launch_wgrad_tc(WgradArgs& a, cudaStream_t st) {
@@ -232,11 +286,32 @@ int launch_wgrad_tc(WgradArgs& a, cudaStream_t st) {
         init = true;
     }
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
-    int grid = nerf_num_sms();
-    const int64_t work = 2ll * WG_NU * a.n_tiles;
-    if (work < grid) grid = (int)(work > 0 ? work : 1);
-    g1_wgrad_tc_kernel<<<grid, WG_THREADS, WG_SMEM_BYTES, st>>>(a);
+    { const char* e = getenv("NERF_WG_DBG"); a.dbg = e ? atoi(e) : 0; }
+    int n_units = 0;
+    for (int l = 0; l < WG_NU; ++l) n_units += a.dz[l] != nullptr;
+    int pairs = nerf_num_sms() / 2;
+    const int64_t work = (int64_t)n_units * a.n_tiles;
+    if (work < pairs) pairs = (int)(work > 0 ? work : 1);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(WG_THREADS); cfg.dynamicSmemBytes = WG_SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    a.prof = nullptr;
+    if (getenv("NERF_WG_PROF")) { cudaMalloc(&a.prof, 2 * pairs * 8 * sizeof(long long)); cudaMemset(a.prof, 0, 2 * pairs * 8 * sizeof(long long)); }
+    NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_wgrad_tc_kernel, a));
     NERF_CUDA_CHECK_LAUNCH();
+    if (a.prof) {
+        cudaDeviceSynchronize();
+        static long long h[148 * 8];
+        cudaMemcpy(h, a.prof, 2 * pairs * 8 * sizeof(long long), cudaMemcpyDeviceToHost);
+        double s0 = 0, s1 = 0, s2 = 0, n = 0, p1 = 0, s4 = 0, s5 = 0;
+        for (int i = 0; i < pairs; ++i) { s4 += h[(2 * i) * 8 + 4]; s5 += h[(2 * i) * 8 + 5]; s0 += h[(2 * i) * 8]; p1 += h[(2 * i + 1) * 8]; s1 += h[(2 * i) * 8 + 1]; s2 += h[(2 * i) * 8 + 2]; n += h[(2 * i) * 8 + 3]; }
+        fprintf(stderr, "wgrad prof: stages/pair %.0f; per stage cycles: leader producer wait-empty %.0f, peer producer wait-empty %.0f, mma wait-full %.0f, mma issue %.0f\n",
+                n / pairs, s0 / n, p1 / n, s1 / n, s2 / n);
+        fprintf(stderr, "wgrad prof: per pair cycles: mma wait acc_free %.0f, leader flush (all segs) %.0f\n", s4 / pairs, s5 / pairs);
+        cudaFree(a.prof);
+    }
     return NERF_OK;
 }
 

@@ -42,6 +42,8 @@ def main():
                                                     P(tr.flat_grad), P(z["ws"]), z["n"], 1, st()),
         "bwd_dgrad+wgrad": lambda: L.nerf_g1_train_bwd_tc(P(z["packed"]), P(z["packed_bwd"]), P(flat), 3, 3, P(z["d_sigma"]), P(z["d_rgb"]), b, s,
                                                           P(tr.flat_grad), P(z["ws"]), z["n"], 2, st()),
+        "wgrad": lambda: L.nerf_g1_train_bwd_tc(P(z["packed"]), P(z["packed_bwd"]), P(flat), 3, 3, P(z["d_sigma"]), P(z["d_rgb"]), b, s,
+                                                P(tr.flat_grad), P(z["ws"]), z["n"], 3, st()),
         "bwd_all": lambda: L.nerf_g1_train_bwd_tc(P(z["packed"]), P(z["packed_bwd"]), P(flat), 3, 3, P(z["d_sigma"]), P(z["d_rgb"]), b, s,
                                                   P(tr.flat_grad), P(z["ws"]), z["n"], 0, st()),
         "step": lambda: tr.step(o, d, tgt),
@@ -49,7 +51,7 @@ def main():
     out = {}
     for name, fn in calls.items():
         if a.only and name not in a.only.split(","):
-            if name in ("pack", "fwd", "composite_fwd", "mse", "composite_bwd"):
+            if name in ("pack", "fwd", "composite_fwd", "mse", "composite_bwd", "bwd_dgrad"):
                 fn()
             continue
         fn(); fn()
