@@ -45,29 +45,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            uint32_t it = 0;
-            for (int q = 0; q < cnt0; ++q)
-                for (int l = 0; l < 10; ++l)
-                    for (int x = 0; x < 2; ++x) {
-                        if (x == 1 && q >= cnt1) continue;
-                        const int nk = a.nk[l];
-                        const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
-                        for (int ks = 0; ks < nk; ++ks)
-                            for (int h = 0; h < stages_per_slab; ++h, ++it) {
-                                const int nh = (CG == 2) ? (int)rank : h;     // pair: this CTA owns one feature half
-                                const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                                tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
+        // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
+        uint32_t it = 0;
+        for (int q = 0; q < cnt0; ++q)
+            for (int l = 0; l < 10; ++l)
+                for (int x = 0; x < 2; ++x) {
+                    if (x == 1 && q >= cnt1) continue;
+                    const int nk = a.nk[l];
+                    const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
+                    for (int ks = 0; ks < nk; ++ks)
+                        for (int h = 0; h < stages_per_slab; ++h, ++it) {
+                            const int nh = (CG == 2) ? (int)rank : h;     // pair: this CTA owns one feature half
+                            const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                            tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
+                            if (tc::elect_one()) {
                                 tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
                                 tc::tma_load_1d(base + SM_RING + slot * TC_STAGE_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
                                                 TC_STAGE_BYTES, ring_full(slot));
                             }
-                    }
-        }
+                            __syncwarp();
+                        }
+                }
     } else if (warp == 1) {
-        if (lane == 0 && leader) {
-            // ===================== MMA issuer =====================
+        if (leader) {
+            // ===================== MMA issuer (whole warp converged; one elected lane issues) =====================
             const uint32_t idesc = (CG == 2) ? tc::umma_idesc_bf16(256, 256) : tc::umma_idesc_bf16(128, 128);
             uint32_t it = 0, act_it[2] = {0, 0};
             for (int q = 0; q < cnt0; ++q)
@@ -86,15 +87,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                                 tc::tcgen05_fence_after();
                                 const uint32_t b_addr = base + SM_RING + slot * TC_STAGE_BYTES;
                                 const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
+                                if (tc::elect_one()) {
 #pragma unroll
-                                for (int kk = 0; kk < 4; ++kk) {
-                                    if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
-                                    else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                    for (int kk = 0; kk < 4; ++kk) {
+                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                        else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                    }
+                                    if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
+                                    if (ks == nk - 1 && h == stages_per_slab - 1) {
+                                        if (CG == 2) tc::umma_commit_2cta(acc_ready(x)); else tc::umma_commit(acc_ready(x));
+                                    }
                                 }
-                                if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
+                                __syncwarp();
                             }
                         }
-                        if (CG == 2) tc::umma_commit_2cta(acc_ready(x)); else tc::umma_commit(acc_ready(x));
                     }
         } else if (CG == 2 && lane == 0 && !leader) {
             // ===================== peer relay: "my weight half has landed" -> leader's full barrier =====================
