@@ -117,13 +117,16 @@ int nerf_composite_fwd(const float* sigma, const float* rgb, const float* points
                        int64_t B, int S, float* pixels, float* depth, float* acc,
                        float* weights, void* stream);
 
-/* Backward of the above w.r.t. sigma and rgb (reverse-scan).  g_* are the
- * incoming gradients (g_depth/g_acc/g_weights may be NULL).  d_sigma [B,S],
- * d_rgb [B,S,3]. */
+/* Backward of the above w.r.t. sigma and rgb.  g_* are the incoming gradients
+ * (g_depth/g_acc/g_weights may be NULL).  saved_pixels [B,3] / saved_depth [B] /
+ * saved_acc [B] are the forward call's outputs (each optional): with them
+ * sum_j w_j s_j is known up front and the suffix sums need no extra pass over
+ * the ray.  d_sigma [B,S], d_rgb [B,S,3]. */
 int nerf_composite_bwd(const float* sigma, const float* rgb, const float* points,
                        const float* rays_o, const float* rays_d, const float* t,
                        int64_t B, int S, const float* g_pixels, const float* g_depth,
                        const float* g_acc, const float* g_weights,
+                       const float* saved_pixels, const float* saved_depth, const float* saved_acc,
                        float* d_sigma, float* d_rgb, void* stream);
 
 /* ------------------------------------------------------------------- MLP --- */

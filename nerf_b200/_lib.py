@@ -28,7 +28,7 @@ SIGNATURES = {
     "nerf_sample_pdf_merge": (c_i, [c_p, c_p, c_i, c_i, c_p, c_l, c_p, c_p]),
     "nerf_encode_g1": (c_i, [c_p, c_p, c_p, c_p, c_i, c_p, c_i, c_l, c_i, c_f, c_i, c_p, c_p, c_p, c_p]),
     "nerf_composite_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p]),
-    "nerf_composite_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "nerf_composite_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "nerf_g1_param_layout": (c_l, [c_i, c_i, ctypes.POINTER(c_l)]),
     "nerf_g1_mlp_workspace_bytes": (c_l, [c_l, c_i, c_i, c_i, c_i]),
     "nerf_g1_mlp_fwd": (c_i, [c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_l, c_p]),

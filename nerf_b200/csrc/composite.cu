@@ -5,6 +5,7 @@
 //   T_k = prod_{j<k} (a_j + 1e-10);  w_k = (1 - a_k) T_k;  pixel = sum_k w_k sigmoid(rgb_k)
 // HBM-bound: 20 S + 20 (+24) bytes per ray forward, 36 S + 40 (+24) backward.
 #include "common.cuh"
+#include "composite_tile.cuh"
 
 struct RayGeom {            // how sample positions are obtained
     const float* points;    // [B,S,3] or null
@@ -162,6 +163,12 @@ extern "C" int nerf_composite_fwd(const float* sigma, const float* rgb, const fl
     if (pixels && !rgb) return NERF_ERR_BAD_ARG;
     if (!rgb) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
+    if (!points && S % CT_CH == 0 && ct_aligned16(sigma) && ct_aligned16(rgb) && ct_aligned16(t) && (!weights || ct_aligned16(weights))) {
+        composite_fwd_tile_kernel<<<(unsigned)((B + CT_RAYS - 1) / CT_RAYS), CT_RAYS, 0, (cudaStream_t)stream>>>(
+            sigma, rgb, rays_o, rays_d, t, B, S, pixels, depth, acc, weights);
+        NERF_CUDA_CHECK_LAUNCH();
+        return NERF_OK;
+    }
     composite_fwd_kernel<<<grid_for_rays(B), 256, 0, (cudaStream_t)stream>>>(
         sigma, rgb, points, rays_o, rays_d, t, B, S, pixels, depth, acc, weights);
     NERF_CUDA_CHECK_LAUNCH();
@@ -172,6 +179,7 @@ extern "C" int nerf_composite_bwd(const float* sigma, const float* rgb, const fl
                                   const float* rays_o, const float* rays_d, const float* t,
                                   int64_t B, int S, const float* g_pixels, const float* g_depth,
                                   const float* g_acc, const float* g_weights,
+                                  const float* saved_pixels, const float* saved_depth, const float* saved_acc,
                                   float* d_sigma, float* d_rgb, void* stream) {
     if (!sigma || !rgb || !d_sigma || !d_rgb || B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
     if (!points && (!rays_o || !rays_d || !t)) return NERF_ERR_BAD_ARG;
@@ -179,6 +187,13 @@ extern "C" int nerf_composite_bwd(const float* sigma, const float* rgb, const fl
     if (S > 1024) return NERF_ERR_UNSUPPORTED;
     if (B == 0) return NERF_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if (!points && !g_weights && S % CT_CH == 0 && ct_aligned16(sigma) && ct_aligned16(rgb) && ct_aligned16(t) &&
+        ct_aligned16(d_sigma) && ct_aligned16(d_rgb)) {
+        composite_bwd_tile_kernel<<<(unsigned)((B + CT_RAYS - 1) / CT_RAYS), CT_RAYS, 0, st>>>(
+            sigma, rgb, rays_o, rays_d, t, B, S, g_pixels, g_depth, g_acc, saved_pixels, saved_depth, saved_acc, d_sigma, d_rgb);
+        NERF_CUDA_CHECK_LAUNCH();
+        return NERF_OK;
+    }
     unsigned grid = grid_for_rays(B);
 #define LAUNCH_BWD(N) composite_bwd_kernel<N><<<grid, 256, 0, st>>>(sigma, rgb, points, rays_o, rays_d, t, B, S, \
         g_pixels, g_depth, g_acc, g_weights, d_sigma, d_rgb)

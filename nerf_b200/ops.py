@@ -128,20 +128,21 @@ class _Composite(torch.autograd.Function):
         check(lib().nerf_composite_fwd(ptr(sigma), ptr(rgb), ptr(points), ptr(rays_o), ptr(rays_d), ptr(t),
                                        b, s, ptr(pixels), ptr(depth), ptr(acc), ptr(weights), stream()),
               "nerf_composite_fwd")
-        ctx.save_for_backward(sigma, rgb, points, rays_o, rays_d, t)
+        ctx.save_for_backward(sigma, rgb, points, rays_o, rays_d, t, pixels, depth, acc)
         if depth is None:
             depth = torch.zeros(b, device=dev)
         return pixels, depth, acc, weights
 
     @staticmethod
     def backward(ctx, g_pixels, g_depth, g_acc, g_weights):
-        sigma, rgb, points, rays_o, rays_d, t = ctx.saved_tensors
+        sigma, rgb, points, rays_o, rays_d, t, pixels, depth, acc = ctx.saved_tensors
         b, s = sigma.shape
         d_sigma = torch.empty_like(sigma); d_rgb = torch.empty_like(rgb)
         g_pixels, g_acc, g_weights = _f32c(g_pixels), _f32c(g_acc), _f32c(g_weights)
         g_depth = _f32c(g_depth) if t is not None else None
         check(lib().nerf_composite_bwd(ptr(sigma), ptr(rgb), ptr(points), ptr(rays_o), ptr(rays_d), ptr(t),
                                        b, s, ptr(g_pixels), ptr(g_depth), ptr(g_acc), ptr(g_weights),
+                                       ptr(pixels), ptr(depth), ptr(acc),
                                        ptr(d_sigma), ptr(d_rgb), stream()), "nerf_composite_bwd")
         return d_sigma, d_rgb, None, None, None, None
 

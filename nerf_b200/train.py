@@ -83,7 +83,8 @@ class Trainer:
                                    ptr(z["pixels"]), None, None, None, st), "nerf_composite_fwd")
         check(L.nerf_mse_loss(ptr(z["pixels"]), ptr(target), b * 3, ptr(z["loss"]), ptr(z["g_pixels"]), st), "nerf_mse_loss")
         check(L.nerf_composite_bwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
-                                   ptr(z["g_pixels"]), None, None, None, ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
+                                   ptr(z["g_pixels"]), None, None, None, ptr(z["pixels"]), None, None,
+                                   ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
               "nerf_composite_bwd")
         check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), 3, 3, ptr(z["d_sigma"]),
                                      ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
@@ -135,7 +136,8 @@ class Trainer:
         loss, g_pixels = ops.mse_loss(pixels, target)
         d_sigma = torch.empty_like(sigma); d_rgb = torch.empty_like(rgb)
         check(lib().nerf_composite_bwd(ptr(sigma), ptr(rgb), None, ptr(rays_o), ptr(rays_d), ptr(t), b, s,
-                                       ptr(g_pixels), None, None, None, ptr(d_sigma), ptr(d_rgb), stream()),
+                                       ptr(g_pixels), None, None, None, ptr(pixels), None, None,
+                                       ptr(d_sigma), ptr(d_rgb), stream()),
               "nerf_composite_bwd")
         launches += 3
         self.flat_grad.zero_()

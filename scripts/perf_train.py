@@ -36,7 +36,7 @@ def main():
                                                P(z["t"]), P(z["sigma"]), P(z["rgb"]), P(z["ws"]), z["n"], st()),
         "composite_fwd": lambda: L.nerf_composite_fwd(P(z["sigma"]), P(z["rgb"]), None, P(o), P(d), P(z["t"]), b, s, P(z["pixels"]), None, None, None, st()),
         "mse": lambda: L.nerf_mse_loss(P(z["pixels"]), P(tgt), b * 3, P(z["loss"]), P(z["g_pixels"]), st()),
-        "composite_bwd": lambda: L.nerf_composite_bwd(P(z["sigma"]), P(z["rgb"]), None, P(o), P(d), P(z["t"]), b, s, P(z["g_pixels"]), None, None, None,
+        "composite_bwd": lambda: L.nerf_composite_bwd(P(z["sigma"]), P(z["rgb"]), None, P(o), P(d), P(z["t"]), b, s, P(z["g_pixels"]), None, None, None, P(z["pixels"]), None, None,
                                                       P(z["d_sigma"]), P(z["d_rgb"]), st()),
         "bwd_dgrad": lambda: L.nerf_g1_train_bwd_tc(P(z["packed"]), P(z["packed_bwd"]), P(flat), 3, 3, P(z["d_sigma"]), P(z["d_rgb"]), b, s,
                                                     P(tr.flat_grad), P(z["ws"]), z["n"], 1, st()),

@@ -334,3 +334,40 @@ def test_api_compat_g1_g2(nerf_pth_state_dict):
     assert rot.shape == (5, 3, 3)
     img = g2.render_image(o[:1], rot[:1], 4, 5, 10.0, 0.0, 20.0, 16, states_x=sx[:1])
     assert img.shape == (1, 4, 5, 3)
+
+
+@pytest.mark.parametrize("b,s", [(1, 16), (130, 32), (300, 64), (77, 128), (5, 256)])
+@pytest.mark.parametrize("saved", [True, False])
+def test_composite_tile_kernels_vs_autograd(b, s, saved):
+    """The thread-per-ray tile kernels (S % 16 == 0, ray geometry): forward outputs and the
+    backward in both modes (suffix sums from the saved forward outputs / from a first sweep)."""
+    from oracle import g1
+    from nerf_b200 import _lib
+    L = _lib.lib(); P = _lib.ptr
+    gen = torch.Generator().manual_seed(7 * b + s)
+    o = torch.randn(b, 3, generator=gen); d = torch.randn(b, 3, generator=gen)
+    t = (torch.rand(b, s, generator=gen) * 4 + 2).sort(dim=-1)[0]
+    sigma = (torch.randn(b, s, generator=gen) * 3).requires_grad_(True)
+    rgb = torch.randn(b, s, 3, generator=gen).requires_grad_(True)
+    pts = o[:, None] + d[:, None] * t[..., None]
+    w = g1.alpha_compositing_coefficients(pts, sigma.unsqueeze(-1))
+    pix = (w * torch.sigmoid(rgb)).sum(-2); dep = (w[..., 0] * t).sum(-1); acc = w[..., 0].sum(-1)
+    gp = torch.randn(b, 3, generator=gen); gd = torch.randn(b, generator=gen); ga = torch.randn(b, generator=gen)
+    ((pix * gp).sum() + (dep * gd).sum() + (acc * ga).sum()).backward()
+    c = lambda x: x.detach().cuda().contiguous()
+    sg, cg, oc, dc, tc_ = c(sigma), c(rgb), c(o), c(d), c(t)
+    p2 = torch.empty(b, 3, device="cuda"); d2 = torch.empty(b, device="cuda"); a2 = torch.empty(b, device="cuda")
+    w2 = torch.empty(b, s, device="cuda")
+    _lib.check(L.nerf_composite_fwd(P(sg), P(cg), None, P(oc), P(dc), P(tc_), b, s, P(p2), P(d2), P(a2), P(w2), _lib.stream()), "fwd")
+    np.testing.assert_allclose(w2.cpu().numpy(), w[..., 0].detach().numpy(), rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(p2.cpu().numpy(), pix.detach().numpy(), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(d2.cpu().numpy(), dep.detach().numpy(), rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(a2.cpu().numpy(), acc.detach().numpy(), rtol=1e-5, atol=1e-6)
+    ds = torch.full((b, s), float("nan"), device="cuda"); dcol = torch.full((b, s, 3), float("nan"), device="cuda")
+    sv = (P(p2), P(d2), P(a2)) if saved else (None, None, None)
+    gpc, gdc, gac = c(gp), c(gd), c(ga)                       # keep alive: P() only takes the address
+    _lib.check(L.nerf_composite_bwd(P(sg), P(cg), None, P(oc), P(dc), P(tc_), b, s, P(gpc), P(gdc), P(gac), None,
+                                    *sv, P(ds), P(dcol), _lib.stream()), "bwd")
+    scale = sigma.grad.abs().max().item() + 1e-6
+    np.testing.assert_allclose(ds.cpu().numpy(), sigma.grad.numpy(), rtol=1e-4, atol=2e-5 * scale)
+    np.testing.assert_allclose(dcol.cpu().numpy(), rgb.grad.numpy(), rtol=1e-4, atol=1e-6)
