@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(CT_RAYS, 4) composite_bwd_tile_kernel(
                         else {
                             prefix += w * s;
                             const float coef = sv[j] > 0.f ? dl * a : 0.f;
-                            ds[j] = coef * (T * s - (total - prefix) / ae);
+                            ds[j] = coef * (T * s - __fdividef(total - prefix, ae));
                             dc[j * 3] = w * gr * s0 * (1.0f - s0); dc[j * 3 + 1] = w * gg * s1 * (1.0f - s1); dc[j * 3 + 2] = w * gb * s2 * (1.0f - s2);
                         }
                         T *= ae;

@@ -94,6 +94,35 @@ __global__ void sample_stratified_kernel(const float* __restrict__ t_base, int m
     int64_t e0 = i * 4;
     if (e0 >= total) return;
     float out[4];
+    if ((S & 3) == 0) {
+        // fast path: the 4 samples belong to one ray and share one Philox block (counter k>>2), one
+        // ray/sample split and a 6-entry window of the ladder -- same values as the generic path
+        const int64_t ray = (total < (1ll << 31)) ? (int64_t)((uint32_t)e0 / (uint32_t)S) : e0 / S;   // 32-bit divide when it fits
+        const int k0 = (int)(e0 - ray * S);
+        float lad[6];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) { const int k = k0 - 1 + j; lad[j] = (k >= 0 && k < S) ? ladder_at(t_base, mode, a, b, S, k) : 0.f; }
+        uint32_t r4[4] = {0u, 0u, 0u, 0u};
+        float4 uv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (jitter) {
+            if (u) uv = *reinterpret_cast<const float4*>(u + e0);
+            else { philox4x32(seed, (uint64_t)(ray_id_base + ray), (uint32_t)(k0 >> 2), r4);
+                   uv = make_float4(u01_from_bits(r4[0]), u01_from_bits(r4[1]), u01_from_bits(r4[2]), u01_from_bits(r4[3])); }
+        }
+        const float uu[4] = {uv.x, uv.y, uv.z, uv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int k = k0 + j; const float tk = lad[j + 1];
+            float v = tk;
+            if (jitter) {
+                float lo = tk, hi = tk;
+                if (k > 0)     lo = __fmul_rn(0.5f, __fadd_rn(tk, lad[j]));
+                if (k < S - 1) hi = __fmul_rn(0.5f, __fadd_rn(lad[j + 2], tk));
+                v = __fadd_rn(lo, __fmul_rn(__fsub_rn(hi, lo), uu[j]));
+            }
+            out[j] = (mode == 0) ? v : __fmul_rn(v, scale);
+        }
+    } else
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         int64_t e = e0 + j;
