@@ -235,6 +235,32 @@ int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float
                          const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
                          void* workspace, int64_t workspace_bytes, int stage, void* stream);
 
+/* ------------------------------------------------ HEAD generation (mip-NeRF) --- */
+
+/* NeRF.integrated_pe (nerf/model.py:544-551 -> cast_rays :112-136, conical_frustum_to_gaussian
+ * :74-81, lift_gaussian :35-45, integrated_pos_enc :139-163, expected_sin :24-30).
+ * t [B,S] fenceposts -> S-1 intervals per ray: mean_out/cov_out [B,S-1,3] (optional),
+ * feat_out [B,S-1,6*n_deg] (sin block, then sin(.+pi/2) block; index deg*3+c).
+ * base_radius = 1/(sqrt(3)*focal_length of the constructor); degrees min_deg .. min_deg+n_deg-1. */
+int nerf_head_encode(const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
+                     float base_radius, int min_deg, int n_deg, float* mean_out, float* cov_out,
+                     float* feat_out, void* stream);
+
+/* NeRF.prediction_heads (nerf/model.py:525-542): 5 x (Linear, LayerNorm, ReLU) + Linear n_out.
+ * params_host: HOST array of 22 DEVICE pointers in state_dict order (prediction_heads.0.weight,
+ * .0.bias, .1.weight, .1.bias, .3.weight, ... .15.weight, .15.bias).  feat [P,n_in], out [P,n_out]. */
+int64_t nerf_head_mlp_workspace_bytes(int64_t P);
+int nerf_head_mlp_fwd(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
+                      float* out, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Colour + segmentation composite of NeRF.render_rays (nerf/model.py:652-663) on the trunk's
+ * interleaved rows out [B,S,n_out] = [density | colour(3) | segmentation(n_seg)], n_out = 4+n_seg,
+ * n_seg <= 64; points [B,S,3] are the Gaussian means.  noise [B,S] (or NULL) * noise_std is added
+ * to the density.  pixels [B,3], seg_out [B,n_seg], weights [B,S] (optional). */
+int nerf_head_composite(const float* out, int n_out, int n_seg, const float* points, const float* noise,
+                        float noise_std, int64_t B, int S, float* pixels, float* seg_out, float* weights,
+                        void* stream);
+
 /* -------------------------------------------------------------- optimiser --- */
 
 /* torch.optim.Adam(lr, betas, eps) step over a flat buffer

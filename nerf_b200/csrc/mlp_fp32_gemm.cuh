@@ -5,6 +5,9 @@
 //               Linear->ReLU->LayerNorm unit of SURVEY A.3 without its affine, which
 //               the NEXT consumer applies when it loads the row)
 //   MODE_DGRAD: A = dz, B = W[:, :256] (natural), epilogue = plain store.
+//   MODE_FWD_LN: HEAD trunk unit Linear->LayerNorm->ReLU (nerf/model.py:525-542): epilogue = +bias,
+//               LayerNorm statistics, normalise; the consumer applies the affine AND the ReLU on load
+//               (ASource.relu).   MODE_LINEAR: plain Linear with n_out <= 256 outputs (HEAD's 256->54).
 #pragma once
 #include "common.cuh"
 
@@ -19,6 +22,7 @@ struct ASource {
     const float* beta;
     const float* seg2;       // extra input columns (PE of position: one row per point; PE of dir: one row per ray)
     int K1, K2, row_div2;
+    int relu;                // HEAD: the producing unit is Linear->LayerNorm->ReLU, so relu(gamma*n+beta)
 };
 
 __device__ __forceinline__ float4 load_a4(const ASource& s, int64_t row, int k, int64_t P) {
@@ -29,13 +33,14 @@ __device__ __forceinline__ float4 load_a4(const ASource& s, int64_t row, int k, 
         float4 g = *reinterpret_cast<const float4*>(s.gamma + k);
         float4 b = *reinterpret_cast<const float4*>(s.beta + k);
         v.x = fmaf(g.x, n.x, b.x); v.y = fmaf(g.y, n.y, b.y); v.z = fmaf(g.z, n.z, b.z); v.w = fmaf(g.w, n.w, b.w);
+        if (s.relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
     } else if (k - s.K1 < s.K2) {
         v = *reinterpret_cast<const float4*>(s.seg2 + (row / s.row_div2) * s.K2 + (k - s.K1));
     }
     return v;
 }
 
-enum { MODE_FWD = 0, MODE_DGRAD = 1 };
+enum { MODE_FWD = 0, MODE_DGRAD = 1, MODE_FWD_LN = 2, MODE_LINEAR = 3 };
 
 template <int MODE>
 __global__ void __launch_bounds__(256) mlp_tile_kernel(
@@ -43,12 +48,13 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
         const float* __restrict__ W, int Kt,        // weight [256][Kt]
         const float* __restrict__ bias,             // FWD
         float* __restrict__ out,                    // FWD: n_out [P,256]; DGRAD: G [P,256]
-        float* __restrict__ mu_out, float* __restrict__ rstd_out, int64_t P) {
+        float* __restrict__ mu_out, float* __restrict__ rstd_out, int64_t P, int n_out = HID) {
+    constexpr bool IS_FWD = MODE != MODE_DGRAD;               // A from ASource, B = W^T
     __shared__ __align__(16) float As[2][BK][A_STRIDE];
     __shared__ __align__(16) float Bs[2][BK][HID];
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
     const int64_t row0 = (int64_t)blockIdx.x * BM;
-    const int K = (MODE == MODE_FWD) ? (src.K1 + src.K2) : HID;
+    const int K = IS_FWD ? (src.K1 + src.K2) : HID;
     const int nchunks = (K + BK - 1) / BK;
 
     float acc[8][8];
@@ -62,15 +68,15 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
         const int k0 = chunk * BK;
         {   // A tile: 64 rows x 16 k, one float4 per thread
             const int r = tid >> 2, kq = (tid & 3) * 4;
-            if (MODE == MODE_FWD) ra = load_a4(src, row0 + r, k0 + kq, P);
+            if (IS_FWD) ra = load_a4(src, row0 + r, k0 + kq, P);
             else ra = (row0 + r < P) ? *reinterpret_cast<const float4*>(src.n_prev + (row0 + r) * HID + k0 + kq)
                                      : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (MODE == MODE_FWD) {     // B[k][n] = W[n][k]: thread = output feature n, 16 consecutive k
+        if (IS_FWD) {     // B[k][n] = W[n][k]: thread = output feature n, 16 consecutive k
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 int k = k0 + q * 4;
-                rb[q] = (k < Kt) ? *reinterpret_cast<const float4*>(W + (size_t)tid * Kt + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                rb[q] = (k < Kt && tid < n_out) ? *reinterpret_cast<const float4*>(W + (size_t)tid * Kt + k) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         } else {                    // B[kk][j] = W[n0+kk][j], j < 256: natural rows
 #pragma unroll
@@ -85,7 +91,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
             const int r = tid >> 2, kq = (tid & 3) * 4;
             As[buf][kq + 0][r] = ra.x; As[buf][kq + 1][r] = ra.y; As[buf][kq + 2][r] = ra.z; As[buf][kq + 3][r] = ra.w;
         }
-        if (MODE == MODE_FWD) {
+        if (IS_FWD) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 Bs[buf][q * 4 + 0][tid] = rb[q].x; Bs[buf][q * 4 + 1][tid] = rb[q].y;
@@ -122,7 +128,18 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
     }
 
     // ---- epilogue: thread owns rows ty*8..+7, columns tx*4..+3 and 128+tx*4..+3 ----
-    if (MODE == MODE_FWD) {
+    if (MODE == MODE_LINEAR) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int64_t row = row0 + ty * 8 + i;
+            if (row >= P) continue;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int col = (j < 4 ? 0 : 128) + tx * 4 + (j & 3);
+                if (col < n_out) out[row * n_out + col] = acc[i][j] + bias[col];
+            }
+        }
+    } else if (MODE == MODE_FWD || MODE == MODE_FWD_LN) {
         float bv[8];
         { float4 b0 = *reinterpret_cast<const float4*>(bias + tx * 4), b1 = *reinterpret_cast<const float4*>(bias + 128 + tx * 4);
           bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w; bv[4] = b1.x; bv[5] = b1.y; bv[6] = b1.z; bv[7] = b1.w; }
@@ -130,7 +147,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
         for (int i = 0; i < 8; ++i) {
             float s = 0.f;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { float a = fmaxf(acc[i][j] + bv[j], 0.f); acc[i][j] = a; s += a; }
+            for (int j = 0; j < 8; ++j) { float a = acc[i][j] + bv[j]; if (MODE == MODE_FWD) a = fmaxf(a, 0.f); acc[i][j] = a; s += a; }
             const float mean = warp_sum(s) * (1.0f / HID);
             float q = 0.f;
 #pragma unroll
@@ -161,7 +178,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
 
 // ---- weight gradient: dW[n][k] += sum_m dz[m][n] * x[m][k],  x = [gamma*n_prev+beta | seg2] ----
 // 64(n) x 64(k) tile per CTA, rows [m_begin, m_end) reduced in chunks of 16, atomics at the end.
-__global__ void __launch_bounds__(256) mlp_wgrad_kernel(
+static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
         const float* __restrict__ dz, ASource src, int Kt, float* __restrict__ dW,
         int64_t P, int64_t rows_per_split) {
     __shared__ __align__(16) float As[2][BK][64];

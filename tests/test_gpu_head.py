@@ -1,0 +1,99 @@
+"""HEAD generation (the model whose source is in the reference tree) against outputs of the UNMODIFIED
+reference stored in tests/golden/head_ref.npz (tests/golden/make_golden.py imports /root/reference)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _cuda(a):
+    return torch.from_numpy(np.asarray(a)).cuda()
+
+
+@pytest.fixture(scope="module")
+def head_ref():
+    return load_golden("head_ref.npz")
+
+
+@pytest.fixture(scope="module")
+def head_model(head_ref):
+    from nerf.model import NeRF
+    from nerf_b200.head import HeadNeRF
+    m = NeRF().cuda()                                           # the reference's default construction
+    assert isinstance(m, HeadNeRF) and isinstance(m, NeRF)
+    sd = {str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]}
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    m.load_state_dict(sd, strict=True)
+    return m
+
+
+def test_head_sampler(head_model, head_ref):
+    o, d = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"])
+    t = head_model.sample_along_rays(o, d, 16, randomly_sample=False)
+    assert np.array_equal(t.cpu().numpy(), head_ref["head_t_det"])
+    t = head_model.sample_along_rays(o, d, 16, u=_cuda(head_ref["head_u"]))
+    assert np.array_equal(t.cpu().numpy(), head_ref["head_t_rand"])
+
+
+def test_head_integrated_pe(head_model, head_ref):
+    """a5-H: conical-frustum Gaussians and the integrated positional encoding."""
+    o, d, t = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"]), _cuda(head_ref["head_t_rand"])
+    mean, cov, feat = head_model.integrated_pe(o, d, t)
+    np.testing.assert_allclose(mean.cpu().numpy(), head_ref["head_ipe_mean"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(cov.cpu().numpy(), head_ref["head_ipe_cov"], rtol=1e-5, atol=1e-9)
+    # features with |argument| up to mean * 2^11 ~ 1e5: one ulp of the argument is ~1e-2 rad, so the
+    # comparison is only meaningful where the amplitude exp(-var/2) has not already damped the feature
+    np.testing.assert_allclose(feat.cpu().numpy(), head_ref["head_ipe_feat"], rtol=0, atol=2e-5)
+
+
+def test_head_forward(head_model, head_ref):
+    """a6-H/a7: trunk outputs (density, colour, segmentation logits)."""
+    o, d, t = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"]), _cuda(head_ref["head_t_rand"])
+    mean, dens, col, seg = head_model(o, d, t)
+    assert dens.shape == (6, 15, 1) and col.shape == (6, 15, 3) and seg.shape == (6, 15, 50)
+    np.testing.assert_allclose(mean.cpu().numpy(), head_ref["head_ipe_mean"], rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(dens.cpu().numpy(), head_ref["head_fwd_density"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(col.cpu().numpy(), head_ref["head_fwd_color"], rtol=0, atol=1e-4)
+    np.testing.assert_allclose(seg.cpu().numpy(), head_ref["head_fwd_seg"], rtol=0, atol=1e-4)
+
+
+def test_head_render_rays(head_model, head_ref):
+    """a9-a11: colour composite (<= 1e-3 bar) and the segmentation logsumexp composite."""
+    o, d = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"])
+    img, seg = head_model.render_rays(o, d, 16, randomly_sample=False, density_noise_std=0.0)
+    assert img.shape == (6, 1, 3) and seg.shape == (6, 1, 50)
+    err = np.abs(img.cpu().numpy() - head_ref["head_rr_img"]).max()
+    print("HEAD render_rays pixel max|diff|", err)
+    assert err <= 1e-3
+    np.testing.assert_allclose(img.cpu().numpy(), head_ref["head_rr_img"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(seg.cpu().numpy(), head_ref["head_rr_seg"], rtol=1e-5, atol=1e-4)
+
+
+def test_head_render_image(head_model, head_ref):
+    """a1-a3 + the whole HEAD chain through render_image (the reference ran it with max_chunk_size=7)."""
+    co, cr = _cuda(head_ref["head_ri_co"]), _cuda(head_ref["head_ri_cr"])
+    img, seg = head_model.render_image(co, cr, 6, 5, 7.5, 12, max_chunk_size=7)
+    assert img.shape == (2, 6, 5, 3) and seg.shape == (2, 6, 5, 50)
+    np.testing.assert_allclose(img.cpu().numpy(), head_ref["head_ri_img"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(seg.cpu().numpy(), head_ref["head_ri_seg"], rtol=1e-5, atol=1e-4)
+    part_img, part_seg = head_model.render_image(co, cr, 6, 5, 7.5, 12, ray_begin=7, ray_end=41)
+    assert torch.equal(part_img, img.reshape(-1, 3)[7:41]) and torch.equal(part_seg, seg.reshape(-1, 50)[7:41])
+
+
+def test_head_vs_oracle_large(head_model, head_ref):
+    """Sizes beyond the fixture (ragged tiles, several segments per ray) against the pinned oracle."""
+    from oracle import head as oh
+    om = oh.HeadNeRF()
+    om.load_state_dict({str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]})
+    g = torch.Generator().manual_seed(21)
+    o = torch.randn(77, 3, generator=g) * 2; d = torch.randn(77, 3, generator=g)
+    u = torch.rand(77, 65, generator=g); noise = torch.randn(77, 64, 1, generator=g)
+    with torch.no_grad():
+        wi, ws = om.render_rays(o, d, 65, u=u, noise=noise)
+    gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+    assert np.abs(gi.cpu().numpy() - wi.numpy()).max() <= 1e-3
+    np.testing.assert_allclose(gi.cpu().numpy(), wi.numpy(), rtol=0, atol=2e-5)
+    np.testing.assert_allclose(gs.cpu().numpy(), ws.numpy(), rtol=1e-4, atol=1e-3)
