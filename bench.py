@@ -74,7 +74,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True); self.thread.start()
         except OSError:
@@ -218,15 +218,16 @@ def run_ours(args):
     for i in range(W):
         step_resident(i)
     barrier()
-    with ClockSampler(local) as clk:
+    with ClockSampler(local) as clk:                     # spans both timed regions (value and e2e)
         ms = timed_steps(step_resident, K, flush)
         barrier()
-    total_ms = float(np.sum(ms))
-    for i in range(max(W // 2, 1)):
-        step_e2e(i)
-    barrier()
-    ms_e2e = timed_steps(step_e2e, K, flush)
-    barrier()
+        total_ms = float(np.sum(ms))
+        for i in range(max(W // 2, 1)):
+            step_e2e(i)
+        barrier()
+        ms_e2e = timed_steps(step_e2e, K, flush)
+        barrier()
+        time.sleep(0.05)
     total_e2e = float(np.sum(ms_e2e))
     loss_val = float(host_loss.item())
 
@@ -256,7 +257,7 @@ def run_ours(args):
             k_fwd(i); k_bwd(0)(i)
         for i in range(3):
             mlp_only(i)
-        n_it = max(K // 2, 5)
+        n_it = min(max(K // 2, 5), 20)
         ms_fwd = float(np.mean(timed_steps(k_fwd, n_it, flush)))
         ms_dgrad = float(np.mean(timed_steps(k_bwd(1), n_it, flush)))
         ms_wg = float(np.mean(timed_steps(k_bwd(3), n_it, flush)))
@@ -323,6 +324,17 @@ def run_ours(args):
     render_rps = rh * rw / (float(np.mean(ms_r)) * 1e-3)
     render_tflops = render_rps * SAMPLES * FLOP_PER_POINT_FWD / 1e12
 
+    # ---- HEAD generation (fp32 FFMA path): render_image 200x200 x 64 fenceposts (63 intervals per ray) ----
+    from nerf_b200.head import HeadNeRF
+    torch.manual_seed(3)
+    hm = HeadNeRF().to(dev)
+    hh = 200
+    with torch.no_grad():
+        hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES)
+        ms_h = timed_steps(lambda i: hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES), 3, flush)
+    head_rps = hh * hh / (float(np.mean(ms_h)) * 1e-3)
+    head_tflops = head_rps * (SAMPLES - 1) * 601_088 / 1e12
+
     # max over ranks of the timed totals
     if world > 1:
         tt = torch.tensor([total_ms, total_e2e], device=dev, dtype=torch.float64)
@@ -358,6 +370,8 @@ def run_ours(args):
             "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},
             "kernels": kernels,
+            "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
+                            "mlp_tflops": head_tflops},
             "loss": loss_val,
         }
         if cpu:
@@ -370,8 +384,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
