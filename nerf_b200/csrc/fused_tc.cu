@@ -1,6 +1,7 @@
 // tcgen05 fused path: kernel body (roles) and the C entry points built on it.
 #include "tc_fused_kernel.cuh"
 #include <stdlib.h>
+#include <stdio.h>
 
 // CG = 1: one CTA per SM works alone (M=128 MMAs, both weight halves per K-slab).
 // CG = 2: CTA pairs (cluster of 2, cta_group::2): M=256 MMAs issued by the leader over both CTAs'
@@ -32,7 +33,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     const int cnt0 = (n_my + 1) >> 1, cnt1 = n_my >> 1;           // units of slot 0 / slot 1
     const int stages_per_slab = (CG == 2) ? 1 : 2;
 
-    for (int i = threadIdx.x; i < TC_VEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[i];
+    for (int i = threadIdx.x; i < TC_SMVEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[TC_VEC_HEADW + i];
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), (CG == 2 && leader) ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
         for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), CG == 2 ? 8 : 128); tc::mbar_init(acc_ready(x), 1); }
@@ -52,16 +53,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 for (int x = 0; x < 2; ++x) {
                     if (x == 1 && q >= cnt1) continue;
                     const int nk = a.nk[l];
+                    const bool blk = tc_unit_has_bias_block(l);
                     const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
                     for (int ks = 0; ks < nk; ++ks)
                         for (int h = 0; h < stages_per_slab; ++h, ++it) {
                             const int nh = (CG == 2) ? (int)rank : h;     // pair: this CTA owns one feature half
                             const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                            const bool with_blk = blk && ks == 0;         // the unit's bias block rides with its first stage
                             tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
                             if (tc::elect_one()) {
-                                tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
-                                tc::tma_load_1d(base + SM_RING + slot * TC_STAGE_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
+                                tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES + (with_blk ? TC_BIASBLK_BYTES : 0));
+                                tc::tma_load_1d(base + SM_RING + slot * TC_SLOT_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
                                                 TC_STAGE_BYTES, ring_full(slot));
+                                if (with_blk)
+                                    tc::tma_load_1d(base + SM_RING + slot * TC_SLOT_BYTES + TC_STAGE_BYTES,
+                                                    a.bias_blocks + (size_t)(l * 2 + nh) * TC_BIASBLK_BYTES, TC_BIASBLK_BYTES, ring_full(slot));
                             }
                             __syncwarp();
                         }
@@ -75,23 +81,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 for (int l = 0; l < 10; ++l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
+                        if (a.prof && blockIdx.x == 0 && q == 1 && lane == 0) a.prof[(l * 2 + x) * 8 + 0] = clock64();
                         tc::mbar_wait(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
                         tc::tcgen05_fence_after();
+                        if (a.prof && blockIdx.x == 0 && q == 1 && lane == 0) a.prof[(l * 2 + x) * 8 + 1] = clock64();
                         const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
                         const int nk = a.nk[l];
+                        const bool blk = tc_unit_has_bias_block(l);
                         for (int ks = 0; ks < nk; ++ks) {
                             const uint32_t a_addr = (l == 0 || ks >= 4) ? pe_addr : act_addr + ks * TC_SLAB_BYTES;
                             for (int h = 0; h < stages_per_slab; ++h, ++it) {
                                 const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
                                 tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
                                 tc::tcgen05_fence_after();
-                                const uint32_t b_addr = base + SM_RING + slot * TC_STAGE_BYTES;
+                                const uint32_t b_addr = base + SM_RING + slot * TC_SLOT_BYTES;
                                 const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
                                 if (tc::elect_one()) {
+                                    if (blk && ks == 0) {                 // acc = b': slab columns 48..63 (ones at 60..62) x bias block
+                                        const uint64_t ad = tc::umma_desc_sw128(pe_addr + 3 * 32);
+                                        const uint64_t bd = tc::umma_desc_k_noswz(b_addr + TC_STAGE_BYTES, TC_BIASBLK_LBO, TC_BIASBLK_SBO);
+                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, ad, bd, idesc, 0); else tc::umma_bf16(d_tmem, ad, bd, idesc, 0);
+                                    }
 #pragma unroll
                                     for (int kk = 0; kk < 4; ++kk) {
-                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
-                                        else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
+                                        const uint32_t acc = (blk || (ks | kk) != 0) ? 1u : 0u;
+                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, acc);
+                                        else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, acc);
                                     }
                                     if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
                                     if (ks == nk - 1 && h == stages_per_slab - 1) {
@@ -101,6 +116,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                                 __syncwarp();
                             }
                         }
+                        if (a.prof && blockIdx.x == 0 && q == 1 && lane == 0) a.prof[(l * 2 + x) * 8 + 2] = clock64();
                     }
         } else if (CG == 2 && lane == 0 && !leader) {
             // ===================== peer relay: "my weight half has landed" -> leader's full barrier =====================
@@ -142,8 +158,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
             }
             signal_act();
             for (int l = 0; l < 10; ++l) {
+                if (a.prof && blockIdx.x == 0 && q == 1 && threadIdx.x == 64 + x * 128) a.prof[(l * 2 + x) * 8 + 3] = clock64();
                 tc::mbar_wait(acc_ready(x), acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
+                if (a.prof && blockIdx.x == 0 && q == 1 && threadIdx.x == 64 + x * 128) a.prof[(l * 2 + x) * 8 + 4] = clock64();
                 if (TRAIN) {                                         // pending bulk stores must have read the slabs we overwrite
                     if (row == 0) tc::tma_store_wait_read0();
                     tc::named_bar_sync(1 + x, 128);
@@ -161,6 +179,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                         tc::tma_store_commit();
                     }
                 }
+                if (a.prof && blockIdx.x == 0 && q == 1 && threadIdx.x == 64 + x * 128) a.prof[(l * 2 + x) * 8 + 5] = clock64();
                 if (l < 9) signal_act();
             }
         }
@@ -177,7 +196,8 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;          // conditional inputs: fp32 path for now
     for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.stage_begin[l] = L.stage_begin[l]; }
     a.stages = (const uint8_t*)packed;
-    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
+    a.bias_blocks = (const uint8_t*)packed + tc_packed_biasblk_offset(L);
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
     static int cg = -1;
     if (cg < 0) {
@@ -187,6 +207,8 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
         NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
         NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
     }
+    a.prof = nullptr;
+    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 160 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 160 * sizeof(long long))); }
     const int sms = nerf_num_sms();
     if (cg == 2) {
         int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
@@ -203,6 +225,16 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
         else g1_fused_tc_kernel<1, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(a);
     }
     NERF_CUDA_CHECK_LAUNCH();
+    if (a.prof) {                                                 // debug: print the stamps relative to the first one
+        long long h[160];
+        NERF_CUDA(cudaStreamSynchronize(st));
+        NERF_CUDA(cudaMemcpy(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost));
+        long long t0 = h[0];
+        for (int i = 0; i < 20; ++i)
+            fprintf(stderr, "unit %d slot %d: mma wait %lld..%lld issued %lld | epi wait %lld..%lld done %lld\n", i / 2, i % 2,
+                    h[i * 8] - t0, h[i * 8 + 1] - t0, h[i * 8 + 2] - t0, h[i * 8 + 3] - t0, h[i * 8 + 4] - t0, h[i * 8 + 5] - t0);
+        cudaFree(a.prof);
+    }
     return NERF_OK;
 }
 

@@ -18,14 +18,16 @@
 #define TC_RING 3
 #define SM_ACT 0                                  // 2 x 64 KB
 #define SM_PE (2 * 65536)                         // 2 x 16 KB
-#define SM_RING (SM_PE + 2 * TC_SLAB_BYTES)       // TC_RING x 16 KB
-#define SM_VEC (SM_RING + TC_RING * TC_STAGE_BYTES)
-#define SM_BAR (SM_VEC + ((TC_VEC_FLOATS * 4 + 15) & ~15))
+#define TC_SLOT_BYTES (TC_STAGE_BYTES + TC_BIASBLK_BYTES)   // weight stage + the unit's bias block (first stage only)
+#define SM_RING (SM_PE + 2 * TC_SLAB_BYTES)       // TC_RING x 20 KB
+#define SM_VEC (SM_RING + TC_RING * TC_SLOT_BYTES)          // head weights [4][256] + head biases [4], fp32
+#define TC_SMVEC_FLOATS (TC_VEC_FLOATS - TC_VEC_HEADW)
+#define SM_BAR (SM_VEC + ((TC_SMVEC_FLOATS * 4 + 15) & ~15))
 #define SM_TOTAL (SM_BAR + 128)
 #define TC_SMEM_BYTES (SM_TOTAL + 1024)           // + slack for the manual 1024 B alignment
 
 struct FusedArgs {
-    const uint8_t* stages; const float* vec;
+    const uint8_t* stages; const float* vec; const uint8_t* bias_blocks;
     int nk[10]; int stage_begin[10];
     const float* rays_o; const float* rays_d;     // [B,3] or null -> camera
     const float* cam_o; const float* cam_r; int H, W; float focal; int64_t ray_begin;
@@ -39,6 +41,7 @@ struct FusedArgs {
     // training forward (TRAIN = true): slab images of every unit's normalised output and of the two
     // encodings, plus (rstd, -mean*rstd) per point and unit, for the backward and wgrad kernels
     uint8_t* tr_act; uint8_t* tr_pex; uint8_t* tr_ped; float2* tr_stats; int64_t P_pad; int tr_tiles;
+    long long* prof;                              // NERF_TC_PROF: clock64 stamps of CTA 0, second work unit
     uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
 };
 
@@ -69,6 +72,8 @@ __device__ __forceinline__ void write_pe_row(uint32_t slab_addr, uint32_t row, c
             w = w + w;                                       // exact octave doubling
         }
     }
+    static_assert(NV * 2 * L <= TC_ONES_COL, "the slab's ones columns must be free");
+    f[TC_ONES_COL] = f[TC_ONES_COL + 1] = f[TC_ONES_COL + 2] = 1.0f;     // x (bias hi, mid, lo) in the weights
 #pragma unroll
     for (int c16 = 0; c16 < 8; ++c16) {
         uint4 q = make_uint4(tc::pack_bf16x2(f[c16 * 8 + 0], f[c16 * 8 + 1]), tc::pack_bf16x2(f[c16 * 8 + 2], f[c16 * 8 + 3]),
@@ -135,13 +140,14 @@ __device__ __forceinline__ void encode_dir_row(const FusedArgs& a, uint32_t row,
     write_pe_row<3, NERF_PE_D_OCTAVES>(pe_addr, row, v);
 }
 
-// bias + ReLU + LayerNorm (no affine: folded into the consumer) for one unit of one tile slot.
+// ReLU + LayerNorm (no affine: folded into the consumer) for one unit of one tile slot; the
+// accumulator already holds z = W'x + b' (the bias comes through the slab's ones columns).
 // Two passes over the TMEM accumulator with packed f32x2 math and the next tcgen05.ld in
 // flight while the current 32 columns are processed:
-//   pass 1: z = acc + b, v = max(z, 0), sum v, sum v^2            (FADD2, FMNMX, FADD2, FFMA2)
-//   pass 2: n = max(acc*rstd + (b*rstd + shift), shift), shift = -mean*rstd  (rstd > 0, so this
-//           equals relu(z)*rstd + shift); the max is taken after the bf16 conversion
-//           (monotone rounding => identical result)              (FFMA2, FFMA2, F2FP, HMNMX2)
+//   pass 1: v = max(z, 0), sum v, sum v^2                          (FMNMX, FADD2, FFMA2)
+//   pass 2: n = max(z*rstd + shift, shift), shift = -mean*rstd  (rstd > 0, so this equals
+//           relu(z)*rstd + shift); the max is taken after the bf16 conversion
+//           (monotone rounding => identical result)              (FFMA2, F2FP, HMNMX2)
 __device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float2(__uint_as_float(a), __uint_as_float(b)); }
 
 // MODE: 0 = plain unit, 1 = unit 7 (+ density head), 2 = unit 9 (+ colour head, no activation
@@ -150,15 +156,12 @@ __device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float
 template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
                                            uint32_t row, uint32_t vec_addr, const RowState& st) {
-    const uint32_t bias_addr = vec_addr + (TC_VEC_BIAS + l * 256) * 4;
     uint32_t r0[32], r1[32];
     float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f);
     auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-            const float4 b = tc::lds128(bias_addr + (ch * 32 + j) * 4);
-            float2 z0 = __fadd2_rn(f2(rc[j], rc[j + 1]), make_float2(b.x, b.y));
-            float2 z1 = __fadd2_rn(f2(rc[j + 2], rc[j + 3]), make_float2(b.z, b.w));
+            float2 z0 = f2(rc[j], rc[j + 1]), z1 = f2(rc[j + 2], rc[j + 3]);
             z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
             s2 = __fadd2_rn(s2, z0); s2 = __fadd2_rn(s2, z1);
             q2 = __ffma2_rn(z0, z0, q2); q2 = __ffma2_rn(z1, z1, q2);
@@ -181,16 +184,13 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
     const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
     const __nv_bfloat162 shift_bf = __floats2bfloat162_rn(shift, shift);
     float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products
-    const uint32_t hw_addr = vec_addr + TC_VEC_HEADW * 4;
+    const uint32_t hw_addr = vec_addr;
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         uint32_t packed[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-            const float4 b = tc::lds128(bias_addr + (ch * 32 + j) * 4);
-            const float2 c0 = __ffma2_rn(make_float2(b.x, b.y), rstd2, shift2);
-            const float2 c1 = __ffma2_rn(make_float2(b.z, b.w), rstd2, shift2);
-            const float2 y0 = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, c0);
-            const float2 y1 = __ffma2_rn(f2(rc[j + 2], rc[j + 3]), rstd2, c1);
+            const float2 y0 = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, shift2);
+            const float2 y1 = __ffma2_rn(f2(rc[j + 2], rc[j + 3]), rstd2, shift2);
             __nv_bfloat162 p0 = __hmax2(__float22bfloat162_rn(y0), shift_bf);
             __nv_bfloat162 p1 = __hmax2(__float22bfloat162_rn(y1), shift_bf);
             packed[j / 2] = *reinterpret_cast<uint32_t*>(&p0); packed[j / 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);

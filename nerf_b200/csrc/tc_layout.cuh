@@ -9,6 +9,16 @@
 #define TC_VEC_HEADW (10 * 256)       //               head weights [4][256] (density, r, g, b) with gamma folded
 #define TC_VEC_HEADB (14 * 256)       //               head biases [4]
 #define TC_VEC_FLOATS (14 * 256 + 4)
+// Bias rides in the accumulator.  Every position/direction slab row carries 1.0 in columns 60..62;
+// units 0, 4, 8 (which read an encoding slab anyway) hold bias' as three bf16 parts (hi + mid + lo,
+// exact to ~2^-24) in those weight columns, the other units get one extra K=16 MMA of slab columns
+// 48..63 against a 4 KB "bias block": no-swizzle K-major [128 n x 16 k], k-core 0 zero, k-core 1 =
+// (0, 0, 0, 0, hi, mid, lo, 0).  Blocks follow the fp32 vector section: [10 units][2 n-halves].
+#define TC_ONES_COL 60
+#define TC_BIASBLK_BYTES 4096
+#define TC_BIASBLK_LBO 128            // between the two k-cores
+#define TC_BIASBLK_SBO 256            // between 8-row n groups
+#define TC_VEC_BYTES ((TC_VEC_FLOATS * 4 + 1023) & ~1023)
 
 struct PackLayout {
     int Dx, Dd, EX, ED;
@@ -38,6 +48,11 @@ static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
     L.off_head_w[0] = off[0]; L.off_head_b[0] = off[1]; L.off_head_w[1] = off[2]; L.off_head_b[1] = off[3];
     return NERF_OK;
 }
+
+__host__ __device__ static inline bool tc_unit_has_bias_block(int l) { return l != 0 && l != 4 && l != 8; }
+static inline int64_t tc_packed_vec_offset(const PackLayout& L) { return (int64_t)L.n_stages * TC_STAGE_BYTES; }
+static inline int64_t tc_packed_biasblk_offset(const PackLayout& L) { return tc_packed_vec_offset(L) + TC_VEC_BYTES; }
+static inline int64_t tc_packed_total(const PackLayout& L) { return tc_packed_biasblk_offset(L) + 20ll * TC_BIASBLK_BYTES; }
 
 // ---- workspace of the bf16 training step (tc_train.cu): byte offsets, all 1024-aligned ----
 #define TC_GW_LD 336                   // dW' row: 256 hidden + 64 encoding + 16 x (column sum of dz = db')

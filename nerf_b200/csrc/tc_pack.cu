@@ -8,7 +8,15 @@
 // (LN(x) = gamma n + beta, so W (gamma n + beta) + b = (W diag gamma) n + (W beta + b).)
 #include "tc_layout.cuh"
 
-__global__ void pack_stage_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
+// bias' -> three bf16 parts whose fp32 sum reproduces it to ~2^-24
+__device__ __forceinline__ void split_bias3(float b, float (&p)[3]) {
+    p[0] = __bfloat162float(__float2bfloat16_rn(b));
+    p[1] = __bfloat162float(__float2bfloat16_rn(b - p[0]));
+    p[2] = __bfloat162float(__float2bfloat16_rn(b - p[0] - p[1]));
+}
+
+__global__ void pack_stage_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ vec,
+                                  uint8_t* __restrict__ packed) {
     // one thread per (stage, row r in [0,128), 16-byte chunk c in [0,8))
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)L.n_stages * 128 * 8) return;
@@ -37,6 +45,9 @@ __global__ void pack_stage_kernel(const float* __restrict__ params, PackLayout L
                 int k2 = (ks - hid_slabs) * 64 + kk;      // index into the appended encoding columns
                 int kcol = (l == 0 ? 0 : 256) + k2;
                 if (kcol < Kt) w = W[(size_t)n * Kt + kcol];
+                else if (ks == L.nk[l] - 1 && kk >= TC_ONES_COL && kk < TC_ONES_COL + 3) {   // the slab's ones columns
+                    float p3[3]; split_bias3(vec[TC_VEC_BIAS + l * 256 + n], p3); w = p3[kk - TC_ONES_COL];
+                }
             }
             v[h] = w;
         }
@@ -76,10 +87,21 @@ __global__ void pack_vectors_kernel(const float* __restrict__ params, PackLayout
     }
 }
 
+// one thread per (unit, output feature): the 16-byte k-core-1 row of the unit's bias block
+__global__ void pack_bias_blocks_kernel(const float* __restrict__ vec, uint8_t* __restrict__ blocks) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 10 * 256) return;
+    const int l = i >> 8, n = i & 255, nh = n >> 7, r = n & 127;
+    float p3[3]; split_bias3(vec[TC_VEC_BIAS + i], p3);
+    uint8_t* row = blocks + (size_t)(l * 2 + nh) * TC_BIASBLK_BYTES + (r >> 3) * TC_BIASBLK_SBO + (r & 7) * 16;
+    *reinterpret_cast<uint4*>(row) = make_uint4(0u, 0u, 0u, 0u);                                        // k-core 0: slab columns 48..55
+    *reinterpret_cast<uint4*>(row + TC_BIASBLK_LBO) = make_uint4(0u, 0u, tc::pack_bf16x2(p3[0], p3[1]), tc::pack_bf16x2(p3[2], 0.f));
+}
+
 extern "C" int64_t nerf_g1_packed_bytes(int Dx, int Dd) {
     PackLayout L;
     if (make_pack_layout(Dx, Dd, L) != NERF_OK) return NERF_ERR_BAD_ARG;
-    return (int64_t)L.n_stages * TC_STAGE_BYTES + (int64_t)TC_VEC_FLOATS * sizeof(float);
+    return tc_packed_total(L);
 }
 
 extern "C" int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* packed, void* stream) {
@@ -87,12 +109,14 @@ extern "C" int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* p
     PackLayout L;
     int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    int64_t n = (int64_t)L.n_stages * 128 * 8;
-    pack_stage_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(params, L, (uint8_t*)packed);
-    NERF_CUDA_CHECK_LAUNCH();
-    float* vec = reinterpret_cast<float*>((uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
+    float* vec = reinterpret_cast<float*>((uint8_t*)packed + tc_packed_vec_offset(L));
     int warps = 10 * 256 + 4;
     pack_vectors_kernel<<<(warps * 32 + 255) / 256, 256, 0, st>>>(params, L, vec);
+    NERF_CUDA_CHECK_LAUNCH();
+    int64_t n = (int64_t)L.n_stages * 128 * 8;
+    pack_stage_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(params, L, vec, (uint8_t*)packed);
+    NERF_CUDA_CHECK_LAUNCH();
+    pack_bias_blocks_kernel<<<10, 256, 0, st>>>(vec, (uint8_t*)packed + tc_packed_biasblk_offset(L));
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
