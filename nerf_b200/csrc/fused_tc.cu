@@ -45,6 +45,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     tc::tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Role loops are latency chains of one warp (~6 cycles per dependent instruction, ~110 per mbarrier
+    // test, ~250 per bulk-copy issue, ~45 per MMA issue; scripts/mma_issue.cu, scripts/tma_bw.cu), and the
+    // tensor pipe only hides ~256 cycles of issue bubble: everything per stage is kept to a handful of
+    // 32-bit adds on precomputed descriptor words.
     if (warp == 0) {
         // ===================== TMA producer (whole warp converged; one elected lane issues) =====================
         uint32_t it = 0;
@@ -52,64 +56,68 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
             for (int l = 0; l < 10; ++l)
                 for (int x = 0; x < 2; ++x) {
                     if (x == 1 && q >= cnt1) continue;
+                    const int blk_kc = tc_unit_has_bias_block(l) ? TF_BIAS_KCORES : 0;
                     const int nk = a.nk[l];
-                    const bool blk = tc_unit_has_bias_block(l);
-                    const uint8_t* src = a.stages + (size_t)a.stage_begin[l] * TC_STAGE_BYTES;
-                    for (int ks = 0; ks < nk; ++ks)
-                        for (int h = 0; h < stages_per_slab; ++h, ++it) {
-                            const int nh = (CG == 2) ? (int)rank : h;     // pair: this CTA owns one feature half
+                    for (int h = 0; h < stages_per_slab; ++h) {           // CG=1 streams the two n-halves one after the other
+                        const int nh = (CG == 2) ? (int)rank : h;         // pair: this CTA owns one feature half
+                        const uint8_t* src = a.stages + a.unit_off[l] + (size_t)nh * a.half_kcores[l] * TF_KCORE_BYTES;
+                        for (int j = 0; j < nk; ++j, ++it) {
                             const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                            const bool with_blk = blk && ks == 0;         // the unit's bias block rides with its first stage
-                            tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
+                            const uint32_t bytes = TF_STAGE_BYTES + (j == 0 ? blk_kc * TF_KCORE_BYTES : 0);   // the bias block rides in front of stage 0
+                            tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
                             if (tc::elect_one()) {
-                                tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES + (with_blk ? TC_BIASBLK_BYTES : 0));
-                                tc::tma_load_1d(base + SM_RING + slot * TC_SLOT_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
-                                                TC_STAGE_BYTES, ring_full(slot));
-                                if (with_blk)
-                                    tc::tma_load_1d(base + SM_RING + slot * TC_SLOT_BYTES + TC_STAGE_BYTES,
-                                                    a.bias_blocks + (size_t)(l * 2 + nh) * TC_BIASBLK_BYTES, TC_BIASBLK_BYTES, ring_full(slot));
+                                tc::mbar_arrive_expect_tx(ring_full(slot), bytes);
+                                tc::tma_load_1d(base + SM_RING + slot * TF_SLOT_BYTES, src, bytes, ring_full(slot));
                             }
                             __syncwarp();
+                            src += bytes;
                         }
+                    }
                 }
     } else if (warp == 1) {
         if (leader) {
             // ===================== MMA issuer (whole warp converged; one elected lane issues) =====================
             const uint32_t idesc = (CG == 2) ? tc::umma_idesc_bf16(256, 256) : tc::umma_idesc_bf16(128, 128);
+            // descriptor words: hi = SBO | version | layout, lo = start address | LBO
+            constexpr uint32_t hi_a = (1024u >> 4) | (1u << 14) | (2u << 29);             // SW128 K-major slabs
+            constexpr uint32_t hi_b = (TF_B_SBO >> 4) | (1u << 14);                       // no-swizzle k-cores
+            auto lo_a = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
+            const uint32_t ring_lo = (((base + SM_RING) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
+            auto mma = [&](uint32_t d, uint32_t alo, uint32_t blo, uint32_t acc) {
+                const uint64_t ad = ((uint64_t)hi_a << 32) | alo, bd = ((uint64_t)hi_b << 32) | blo;
+                if (CG == 2) tc::umma_bf16_2cta(d, ad, bd, idesc, acc); else tc::umma_bf16(d, ad, bd, idesc, acc);
+            };
             uint32_t it = 0, act_it[2] = {0, 0};
             for (int q = 0; q < cnt0; ++q)
                 for (int l = 0; l < 10; ++l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
                         if (a.prof && blockIdx.x == 0 && q == 1 && lane == 0) a.prof[(l * 2 + x) * 8 + 0] = clock64();
-                        tc::mbar_wait(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
+                        tc::mbar_wait_spin(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
                         tc::tcgen05_fence_after();
                         if (a.prof && blockIdx.x == 0 && q == 1 && lane == 0) a.prof[(l * 2 + x) * 8 + 1] = clock64();
-                        const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
-                        const int nk = a.nk[l];
+                        const uint32_t act_lo = lo_a(base + SM_ACT + x * 65536), pe_lo = lo_a(base + SM_PE + x * TC_SLAB_BYTES);
                         const bool blk = tc_unit_has_bias_block(l);
-                        for (int ks = 0; ks < nk; ++ks) {
-                            const uint32_t a_addr = (l == 0 || ks >= 4) ? pe_addr : act_addr + ks * TC_SLAB_BYTES;
-                            for (int h = 0; h < stages_per_slab; ++h, ++it) {
+                        const int nk = a.nk[l];
+                        for (int h = 0; h < stages_per_slab; ++h) {
+                            const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
+                            for (int j = 0; j < nk; ++j, ++it) {
                                 const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                                tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
-                                tc::tcgen05_fence_after();
-                                const uint32_t b_addr = base + SM_RING + slot * TC_SLOT_BYTES;
-                                const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
+                                const uint32_t alo = (l == 0 || j >= 4) ? pe_lo : act_lo + j * (TC_SLAB_BYTES >> 4);
+                                uint32_t blo = ring_lo + slot * (TF_SLOT_BYTES >> 4);
+                                tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);   // TMA data -> MMA: both async proxy, no tcgen05 fence
                                 if (tc::elect_one()) {
-                                    if (blk && ks == 0) {                 // acc = b': slab columns 48..63 (ones at 60..62) x bias block
-                                        const uint64_t ad = tc::umma_desc_sw128(pe_addr + 3 * 32);
-                                        const uint64_t bd = tc::umma_desc_k_noswz(b_addr + TC_STAGE_BYTES, TC_BIASBLK_LBO, TC_BIASBLK_SBO);
-                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, ad, bd, idesc, 0); else tc::umma_bf16(d_tmem, ad, bd, idesc, 0);
+                                    if (blk && j == 0) {                  // acc = b': slab columns 48..63 (ones at 60..62) x bias block
+                                        mma(d_tmem, pe_lo + 3 * 2, blo, 0);
+                                        blo += (TF_BIAS_KCORES * TF_KCORE_BYTES) >> 4;
                                     }
-#pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk) {
-                                        const uint32_t acc = (blk || (ks | kk) != 0) ? 1u : 0u;
-                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, acc);
-                                        else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, acc);
-                                    }
+                                    const uint32_t acc0 = (blk || j != 0) ? 1u : 0u;
+                                    mma(d_tmem, alo, blo, acc0);
+                                    mma(d_tmem, alo + 2, blo + 1 * (2 * TF_KCORE_BYTES >> 4), 1);
+                                    mma(d_tmem, alo + 4, blo + 2 * (2 * TF_KCORE_BYTES >> 4), 1);
+                                    mma(d_tmem, alo + 6, blo + 3 * (2 * TF_KCORE_BYTES >> 4), 1);
                                     if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
-                                    if (ks == nk - 1 && h == stages_per_slab - 1) {
+                                    if (j == nk - 1 && h == stages_per_slab - 1) {
                                         if (CG == 2) tc::umma_commit_2cta(acc_ready(x)); else tc::umma_commit(acc_ready(x));
                                     }
                                 }
@@ -125,9 +133,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 for (int l = 0; l < 10; ++l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
-                        for (int ks = 0; ks < a.nk[l]; ++ks, ++it) {
+                        for (int j = 0; j < a.nk[l]; ++j, ++it) {
                             const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                            tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
+                            tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
                             tc::mbar_arrive_cluster(tc::mapa(ring_full(slot), 0));
                         }
                     }
@@ -194,10 +202,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
 static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaStream_t st, bool train = false) {
     PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
     if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;          // conditional inputs: fp32 path for now
-    for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.stage_begin[l] = L.stage_begin[l]; }
+    for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.unit_off[l] = L.unit_off[l]; }
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
-    a.bias_blocks = (const uint8_t*)packed + tc_packed_biasblk_offset(L);
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
     static int cg = -1;
     if (cg < 0) {
@@ -208,7 +215,7 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
         NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
     }
     a.prof = nullptr;
-    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 160 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 160 * sizeof(long long))); }
+    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
     const int sms = nerf_num_sms();
     if (cg == 2) {
         int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
@@ -226,7 +233,7 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     }
     NERF_CUDA_CHECK_LAUNCH();
     if (a.prof) {                                                 // debug: print the stamps relative to the first one
-        long long h[160];
+        long long h[192];
         NERF_CUDA(cudaStreamSynchronize(st));
         NERF_CUDA(cudaMemcpy(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost));
         long long t0 = h[0];

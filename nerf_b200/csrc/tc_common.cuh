@@ -43,6 +43,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_
     }
 }
 
+// The same wait without the iteration counter, for the one-warp role loops whose instruction count per
+// stage is the kernel's critical path (the protocol there is covered by the tests; the epilogue side keeps
+// the trapping version).
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity, uint32_t hint) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "WAIT_LOOP:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+                 "@p bra WAIT_DONE;\n\t"
+                 "bra WAIT_LOOP;\n\t"
+                 "WAIT_DONE:\n\t}"
+                 ::"r"(bar), "r"(parity), "r"(hint) : "memory");
+}
+
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));

@@ -1,8 +1,8 @@
 // Fused ray-gen + sample + encode + G1 MLP on tcgen05 (bf16 in, fp32 accumulate in TMEM).
 //
 // One persistent CTA per SM, 320 threads:
-//   warp 0      TMA producer: streams the packed weight stages (16 KB: 128 n x 64 k) through a ring
-//   warp 1      MMA issuer (one lane): tcgen05.mma M=128 N=128 K=16, accumulators in TMEM
+//   warp 0      TMA producer: streams the packed weight stages (16 KB: 128 n x 64 k, + 4 KB bias block) through a ring
+//   warp 1      MMA issuer (one elected lane): tcgen05.mma K=16, accumulators in TMEM
 //   warps 2-5   epilogue/encoder group of tile slot 0 (thread = point row = TMEM lane)
 //   warps 6-9   epilogue/encoder group of tile slot 1
 // Two 128-point tiles are in flight (slots), each with its own 256 TMEM columns, activation
@@ -18,17 +18,16 @@
 #define TC_RING 3
 #define SM_ACT 0                                  // 2 x 64 KB
 #define SM_PE (2 * 65536)                         // 2 x 16 KB
-#define TC_SLOT_BYTES (TC_STAGE_BYTES + TC_BIASBLK_BYTES)   // weight stage + the unit's bias block (first stage only)
 #define SM_RING (SM_PE + 2 * TC_SLAB_BYTES)       // TC_RING x 20 KB
-#define SM_VEC (SM_RING + TC_RING * TC_SLOT_BYTES)          // head weights [4][256] + head biases [4], fp32
+#define SM_VEC (SM_RING + TC_RING * TF_SLOT_BYTES)         // head weights [4][256] + head biases [4], fp32
 #define TC_SMVEC_FLOATS (TC_VEC_FLOATS - TC_VEC_HEADW)
 #define SM_BAR (SM_VEC + ((TC_SMVEC_FLOATS * 4 + 15) & ~15))
-#define SM_TOTAL (SM_BAR + 128)
+#define SM_TOTAL (SM_BAR + 256)
 #define TC_SMEM_BYTES (SM_TOTAL + 1024)           // + slack for the manual 1024 B alignment
 
 struct FusedArgs {
-    const uint8_t* stages; const float* vec; const uint8_t* bias_blocks;
-    int nk[10]; int stage_begin[10];
+    const uint8_t* stages; const float* vec;
+    int nk[10]; int half_kcores[10]; int64_t unit_off[10];
     const float* rays_o; const float* rays_d;     // [B,3] or null -> camera
     const float* cam_o; const float* cam_r; int H, W; float focal; int64_t ray_begin;
     float* ws_rays_o; float* ws_rays_d;           // written when rays come from the camera

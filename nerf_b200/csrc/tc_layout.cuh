@@ -9,15 +9,23 @@
 #define TC_VEC_HEADW (10 * 256)       //               head weights [4][256] (density, r, g, b) with gamma folded
 #define TC_VEC_HEADB (14 * 256)       //               head biases [4]
 #define TC_VEC_FLOATS (14 * 256 + 4)
+// Forward weights: bf16 B operand without swizzle, K-major, as a sequence of "k-cores" per (unit, n-half):
+// k-core = [128 n x 8 k] = 16 n-groups x (8 rows x 16 B) = 2 KB, so any run of k-cores is one contiguous
+// bulk copy and the ring stage size is a free choice (descriptor: LBO = 2 KB between k-cores, SBO = 128 B
+// between n-groups).  Small stages matter: the ring's round trip (MMA hold + refill latency) bounds the
+// MMA rate at bytes_in_flight / round_trip, and the hold part shrinks with the stage.
 // Bias rides in the accumulator.  Every position/direction slab row carries 1.0 in columns 60..62;
 // units 0, 4, 8 (which read an encoding slab anyway) hold bias' as three bf16 parts (hi + mid + lo,
-// exact to ~2^-24) in those weight columns, the other units get one extra K=16 MMA of slab columns
-// 48..63 against a 4 KB "bias block": no-swizzle K-major [128 n x 16 k], k-core 0 zero, k-core 1 =
-// (0, 0, 0, 0, hi, mid, lo, 0).  Blocks follow the fp32 vector section: [10 units][2 n-halves].
+// exact to ~2^-24) in those weight columns, the other units start with a two-k-core "bias block" that is
+// multiplied with slab columns 48..63: k-core 0 zero, k-core 1 = (0, 0, 0, 0, hi, mid, lo, 0).
 #define TC_ONES_COL 60
-#define TC_BIASBLK_BYTES 4096
-#define TC_BIASBLK_LBO 128            // between the two k-cores
-#define TC_BIASBLK_SBO 256            // between 8-row n groups
+#define TF_KCORE_BYTES 2048
+#define TF_STAGE_KCORES 8             // K = 64 per ring stage (four MMAs)
+#define TF_STAGE_BYTES (TF_STAGE_KCORES * TF_KCORE_BYTES)
+#define TF_BIAS_KCORES 2              // in front of the unit's first stage (same bulk copy, fifth MMA)
+#define TF_SLOT_BYTES (TF_STAGE_BYTES + TF_BIAS_KCORES * TF_KCORE_BYTES)
+#define TF_B_LBO 2048
+#define TF_B_SBO 128
 #define TC_VEC_BYTES ((TC_VEC_FLOATS * 4 + 1023) & ~1023)
 
 struct PackLayout {
@@ -26,6 +34,9 @@ struct PackLayout {
     int stage_begin[11];        // first 16 KB stage of each unit (2 stages per k-slab)
     int n_stages;
     int Kt[10];
+    int64_t unit_off[10];       // forward image: byte offset of the unit's [2 n-halves][k-cores] region
+    int half_kcores[10];        // k-cores per n-half: bias block (units without an encoding slab) + 8 per k-slab
+    int64_t weight_bytes;
     int64_t off_W[10], off_b[10], off_gamma[10], off_beta[10];
     int64_t off_head_w[2], off_head_b[2];
 };
@@ -45,14 +56,20 @@ static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
         L.off_gamma[l] = off[6 + 4 * l]; L.off_beta[l] = off[7 + 4 * l];
     }
     L.stage_begin[10] = s; L.n_stages = s;
+    int64_t wo = 0;
+    for (int l = 0; l < 10; ++l) {
+        const bool blk = (l != 0 && l != 4 && l != 8);
+        L.half_kcores[l] = (blk ? TF_BIAS_KCORES : 0) + 8 * L.nk[l];
+        L.unit_off[l] = wo; wo += 2ll * L.half_kcores[l] * TF_KCORE_BYTES;
+    }
+    L.weight_bytes = wo;
     L.off_head_w[0] = off[0]; L.off_head_b[0] = off[1]; L.off_head_w[1] = off[2]; L.off_head_b[1] = off[3];
     return NERF_OK;
 }
 
 __host__ __device__ static inline bool tc_unit_has_bias_block(int l) { return l != 0 && l != 4 && l != 8; }
-static inline int64_t tc_packed_vec_offset(const PackLayout& L) { return (int64_t)L.n_stages * TC_STAGE_BYTES; }
-static inline int64_t tc_packed_biasblk_offset(const PackLayout& L) { return tc_packed_vec_offset(L) + TC_VEC_BYTES; }
-static inline int64_t tc_packed_total(const PackLayout& L) { return tc_packed_biasblk_offset(L) + 20ll * TC_BIASBLK_BYTES; }
+static inline int64_t tc_packed_vec_offset(const PackLayout& L) { return L.weight_bytes; }
+static inline int64_t tc_packed_total(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES; }
 
 // ---- workspace of the bf16 training step (tc_train.cu): byte offsets, all 1024-aligned ----
 #define TC_GW_LD 336                   // dW' row: 256 hidden + 64 encoding + 16 x (column sum of dz = db')

@@ -174,7 +174,7 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     NERF_CUDA(cudaMemsetAsync(ws + T.zero_begin, 0, (size_t)T.zero_bytes, st));
     BwdArgs a{};
     a.stages = (const uint8_t*)packed_bwd;
-    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + (size_t)L.n_stages * TC_STAGE_BYTES);
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
     a.act = ws + T.off_act; a.stats = reinterpret_cast<const float2*>(ws + T.off_stats);
     a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz = ws + T.off_dz; a.dh = ws + T.off_dh;
     a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
