@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                         for (int h = 0; h < stages_per_slab; ++h, ++it) {
                             const int nh = (CG == 2) ? (int)rank : h;
                             const int slot = it % TB_RING; const uint32_t ph = (it / TB_RING) & 1;
-                            tc::mbar_wait(ring_empty(slot), ph ^ 1, a.wait_hint);
+                            tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
                             if (tc::elect_one()) {
                                 tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
                                 tc::tma_load_1d(base + TB_SM_RING + slot * TC_STAGE_BYTES, src + (size_t)(ks * 2 + nh) * TC_STAGE_BYTES,
@@ -190,29 +190,36 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
     } else if (warp == 1) {
         if (leader) {
             // ===================== MMA issuer: g_{l-1} = dz_l W'_l (whole warp converged; elected lane issues) =====================
+            // (per-stage work kept to a few 32-bit adds on precomputed descriptor words: the loop is a latency
+            // chain of one warp and the tensor pipe hides only ~256 cycles of issue bubble, see fused_tc.cu)
             const uint32_t idesc = (CG == 2) ? tc::umma_idesc_bf16(256, 256) : tc::umma_idesc_bf16(128, 128);
+            constexpr uint32_t hi_sw = (1024u >> 4) | (1u << 14) | (2u << 29);            // SW128 K-major: SBO, version, layout
+            auto lo_sw = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
+            const uint32_t ring_lo = lo_sw(base + TB_SM_RING);
+            auto mma = [&](uint32_t d, uint32_t alo, uint32_t blo, uint32_t acc) {
+                const uint64_t ad = ((uint64_t)hi_sw << 32) | alo, bd = ((uint64_t)hi_sw << 32) | blo;
+                if (CG == 2) tc::umma_bf16_2cta(d, ad, bd, idesc, acc); else tc::umma_bf16(d, ad, bd, idesc, acc);
+            };
             uint32_t it = 0, act_it[2] = {0, 0};
             for (int q = 0; q < cnt0; ++q)
                 for (int l = 9; l >= 1; --l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
-                        tc::mbar_wait(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
+                        tc::mbar_wait_spin(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
                         tc::tcgen05_fence_after();
-                        const uint32_t act_addr = base + TB_SM_ACT + x * 65536;
+                        const uint32_t act_lo = lo_sw(base + TB_SM_ACT + x * 65536);
                         for (int ks = 0; ks < 4; ++ks) {
-                            const uint32_t a_addr = act_addr + ks * TC_SLAB_BYTES;
+                            const uint32_t alo = act_lo + ks * (TC_SLAB_BYTES >> 4);
                             for (int h = 0; h < stages_per_slab; ++h, ++it) {
                                 const int slot = it % TB_RING; const uint32_t ph = (it / TB_RING) & 1;
-                                tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
-                                tc::tcgen05_fence_after();
-                                const uint32_t b_addr = base + TB_SM_RING + slot * TC_STAGE_BYTES;
+                                const uint32_t blo = ring_lo + slot * (TC_STAGE_BYTES >> 4);
                                 const uint32_t d_tmem = tmem_base + x * 256 + ((CG == 2) ? 0 : h * 128);
+                                tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);   // TMA data -> MMA: both async proxy, no tcgen05 fence
                                 if (tc::elect_one()) {
-#pragma unroll
-                                    for (int kk = 0; kk < 4; ++kk) {
-                                        if (CG == 2) tc::umma_bf16_2cta(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
-                                        else tc::umma_bf16(d_tmem, tc::umma_desc_sw128(a_addr + kk * 32), tc::umma_desc_sw128(b_addr + kk * 32), idesc, (ks | kk) != 0);
-                                    }
+                                    mma(d_tmem, alo, blo, ks != 0);
+                                    mma(d_tmem, alo + 2, blo + 2, 1);
+                                    mma(d_tmem, alo + 4, blo + 4, 1);
+                                    mma(d_tmem, alo + 6, blo + 6, 1);
                                     if (CG == 2) tc::umma_commit_2cta(ring_empty(slot)); else tc::umma_commit(ring_empty(slot));
                                     if (h == stages_per_slab - 1) {
                                         if (CG == 2) tc::umma_commit_2cta(slab_free(x, ks)); else tc::umma_commit(slab_free(x, ks));
@@ -232,7 +239,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                         if (x == 1 && q >= cnt1) continue;
                         for (int ks = 0; ks < 4; ++ks, ++it) {
                             const int slot = it % TB_RING; const uint32_t ph = (it / TB_RING) & 1;
-                            tc::mbar_wait(ring_full(slot), ph, a.wait_hint);
+                            tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
                             tc::mbar_arrive_cluster(tc::mapa(ring_full(slot), 0));
                         }
                     }

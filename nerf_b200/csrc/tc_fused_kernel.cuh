@@ -156,14 +156,14 @@ template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
                                            uint32_t row, uint32_t vec_addr, const RowState& st) {
     uint32_t r0[32], r1[32];
-    float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f);
+    float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f), s3 = s2, q3 = q2;   // two chains each: the adds are latency-bound
     auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
             float2 z0 = f2(rc[j], rc[j + 1]), z1 = f2(rc[j + 2], rc[j + 3]);
             z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
-            s2 = __fadd2_rn(s2, z0); s2 = __fadd2_rn(s2, z1);
-            q2 = __ffma2_rn(z0, z0, q2); q2 = __ffma2_rn(z1, z1, q2);
+            s2 = __fadd2_rn(s2, z0); s3 = __fadd2_rn(s3, z1);
+            q2 = __ffma2_rn(z0, z0, q2); q3 = __ffma2_rn(z1, z1, q3);
         }
     };
     tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
@@ -176,6 +176,7 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
         pass1(r1, 2 * c2 + 1);
         tc::tmem_ld_wait();
     }
+    s2 = __fadd2_rn(s2, s3); q2 = __fadd2_rn(q2, q3);
     const float mean = (s2.x + s2.y) * (1.0f / 256.f);
     const float var = fmaxf((q2.x + q2.y) * (1.0f / 256.f) - mean * mean, 0.f);
     const float rstd = rsqrtf(var + NERF_LN_EPS);
