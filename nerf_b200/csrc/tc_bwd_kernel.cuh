@@ -42,6 +42,8 @@ struct BwdArgs {
     float* hsum;                      // [4] += sum over points of (d_sigma, d_rgb)
     int64_t P, P_pad; int n_tiles, tr_tiles;
     uint32_t wait_hint;
+    long long* prof;                  // NERF_TC_PROF: clock64 stamps of CTA 0, second tile of each slot
+    int pf_dist, pf_next;             // L2 prefetch distance in units (0 = off), and whether to reach into the slot's next tile
 };
 
 __device__ __forceinline__ float bf_lo(uint32_t x) { return __uint_as_float(x << 16); }
@@ -57,7 +59,7 @@ __device__ __forceinline__ uint4 lds128u(uint32_t addr) {
 template <int SRC>
 __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr, uint32_t row, uint32_t hw_addr,
                                                float rstd, float shift, float ds, float dr, float dg, float db,
-                                               uint32_t nfull_base, uint32_t nf_parity, uint32_t wait_hint) {
+                                               uint32_t nfull_base, uint32_t nf_parity, uint32_t wait_hint, long long* pf = nullptr) {
     float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
     uint32_t r[32];
     // g for columns [ch*32 + j, +4)
@@ -82,7 +84,7 @@ __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr
 #pragma unroll 1
     for (int ch = 0; ch < 8; ++ch) {
         if (SRC != 2) tc::tmem_ld32(taddr + ch * 32, r);
-        if ((ch & 1) == 0) tc::mbar_wait(nfull_base + 8u * (ch >> 1), nf_parity, wait_hint);
+        if ((ch & 1) == 0) { tc::mbar_wait(nfull_base + 8u * (ch >> 1), nf_parity, wait_hint); if (pf) pf[ch >> 1] = clock64(); }
         if (SRC != 2) tc::tmem_ld_wait();
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
@@ -97,6 +99,7 @@ __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr
             s2 = __ffma2_rn(g3, make_float2(bf_lo(nv.w), bf_hi(nv.w)), s2);
         }
     }
+    if (pf) pf[4] = clock64();
     const float m1 = (s1.x + s1.y) * (1.0f / 256.f), m2 = (s2.x + s2.y) * (1.0f / 256.f);
     const float2 rs2 = make_float2(rstd, rstd);
     const float2 c0 = make_float2(-rstd * m1, -rstd * m1), c1 = make_float2(-rstd * m2, -rstd * m2);
@@ -205,8 +208,11 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                 for (int l = 9; l >= 1; --l)
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
+                        const bool pfm = a.prof && blockIdx.x == 0 && q == 1 && lane == 0;
+                        if (pfm) a.prof[(l * 2 + x) * 8 + 0] = clock64();
                         tc::mbar_wait_spin(act_ready(x), act_it[x] & 1, a.wait_hint); ++act_it[x];
                         tc::tcgen05_fence_after();
+                        if (pfm) a.prof[(l * 2 + x) * 8 + 1] = clock64();
                         const uint32_t act_lo = lo_sw(base + TB_SM_ACT + x * 65536);
                         for (int ks = 0; ks < 4; ++ks) {
                             const uint32_t alo = act_lo + ks * (TC_SLAB_BYTES >> 4);
@@ -229,6 +235,7 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                                 __syncwarp();
                             }
                         }
+                        if (pfm) a.prof[(l * 2 + x) * 8 + 2] = clock64();
                     }
         } else if (CG == 2 && lane == 0 && !leader) {
             // ===================== peer relay of weight arrivals =====================
@@ -278,14 +285,31 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                 *reinterpret_cast<uint4*>(o + 128) = make_uint4(0u, 0u, 0u, 0u);
             }
             for (int l = 9; l >= 0; --l) {
+                // n_{l-1} can only land in the slot once the MMA has consumed dz_l; pull it into L2 a whole unit ahead
+                if (io && a.pf_dist > 0) {
+                    const int d = a.pf_dist;
+                    if (l == 9) for (int e = 1; e < d; ++e) tc::tma_prefetch_l2(a.act + ((size_t)(9 - e) * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), 4 * TC_SLAB_BYTES);
+                    if (l >= d) tc::tma_prefetch_l2(a.act + ((size_t)(l - d) * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), 4 * TC_SLAB_BYTES);
+                    else if (a.pf_next && q + 1 < cnt) {             // n_9.. of this slot's next tile
+                        const int nunit = me + (2 * (q + 1) + x) * G;
+                        const int ntile = (CG == 2) ? 2 * nunit + (int)rank : nunit;
+                        tc::tma_prefetch_l2(a.act + ((size_t)(10 - d + l) * a.tr_tiles + ntile) * (4 * TC_SLAB_BYTES), 4 * TC_SLAB_BYTES);
+                    }
+                }
                 const float2 stt = a.stats[(int64_t)l * a.P_pad + p];
+                const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1;
+                if (pfe) a.prof[(l * 2 + x) * 8 + 3] = clock64();
                 if (l < 9) { tc::mbar_wait(acc_ready(x), acc_it & 1, a.wait_hint); ++acc_it; tc::tcgen05_fence_after(); }
+                if (pfe) a.prof[(l * 2 + x) * 8 + 4] = clock64();
                 if (l == 9) bwd_epilogue_unit<2>(taddr, act_addr, row, hw_addr, stt.x, stt.y, ds, dr, dg, db, n_full(x, 0), nf_it & 1, a.wait_hint);
                 else if (l == 7) bwd_epilogue_unit<1>(taddr, act_addr, row, hw_addr, stt.x, stt.y, ds, dr, dg, db, n_full(x, 0), nf_it & 1, a.wait_hint);
-                else bwd_epilogue_unit<0>(taddr, act_addr, row, hw_addr, stt.x, stt.y, ds, dr, dg, db, n_full(x, 0), nf_it & 1, a.wait_hint);
+                else bwd_epilogue_unit<0>(taddr, act_addr, row, hw_addr, stt.x, stt.y, ds, dr, dg, db, n_full(x, 0), nf_it & 1, a.wait_hint,
+                                          (pfe && l == 5) ? a.prof + 160 + x * 8 : nullptr);
                 ++nf_it;
+                if (pfe) a.prof[(l * 2 + x) * 8 + 5] = clock64();
                 tc::fence_proxy_async_smem();
                 tc::named_bar_sync(1 + x, 128);                      // dz_l complete in shared memory
+                if (pfe) a.prof[(l * 2 + x) * 8 + 6] = clock64();
                 if (io) {
                     tc::tma_store_1d(a.dz + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), act_addr, 4 * TC_SLAB_BYTES);
                     tc::tma_store_commit();
@@ -295,9 +319,14 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                     if (CG == 2) { __syncwarp(); if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
                     else tc::mbar_arrive(act_ready(x));
                     if (io) {                                        // refill each K-slab with n_{l-1} once the MMA has consumed it
+                        const bool pfi = a.prof && blockIdx.x == 0 && q == 1 && l == 6;
                         for (int ks = 0; ks < 4; ++ks) {
+                            if (pfi && ks == 0) a.prof[176 + x * 4] = clock64();
                             tc::mbar_wait(slab_free(x, ks), sf_it & 1, a.wait_hint);
+                            if (pfi && ks == 0) a.prof[177 + x * 4] = clock64();
                             if (ks == 0) tc::tma_store_wait_read0();
+                            if (pfi && ks == 0) a.prof[178 + x * 4] = clock64();
+                            if (pfi && ks == 3) a.prof[179 + x * 4] = clock64();
                             tc::mbar_arrive_expect_tx(n_full(x, ks), TC_SLAB_BYTES);
                             tc::tma_load_1d(act_addr + ks * TC_SLAB_BYTES,
                                             a.act + (((size_t)(l - 1) * a.tr_tiles + tile) * 4 + ks) * TC_SLAB_BYTES, TC_SLAB_BYTES, n_full(x, ks));

@@ -6,6 +6,7 @@
 // gradients w.r.t. the folded parameters (W' = W diag(gamma_prev), b' = b + W beta_prev) into the
 // gradients of the 44 state_dict tensors (reference: autograd of train_conditional_nerf.py:120-135).
 #include "tc_bwd_kernel.cuh"
+#include <stdio.h>
 #include <stdlib.h>
 
 struct WgradArgs;
@@ -126,6 +127,8 @@ __global__ void unfold_affine_kernel(const float* __restrict__ params, PackLayou
 
 template <int CG>
 static int launch_bwd(BwdArgs& a, cudaStream_t st) {
+    a.prof = nullptr;
+    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
     static bool init = false;
     if (!init) { NERF_CUDA(cudaFuncSetAttribute(g1_bwd_tc_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, TB_SMEM_BYTES)); init = true; }
     const int sms = nerf_num_sms();
@@ -142,6 +145,25 @@ static int launch_bwd(BwdArgs& a, cudaStream_t st) {
         g1_bwd_tc_kernel<CG><<<grid, TB_THREADS, TB_SMEM_BYTES, st>>>(a);
     }
     NERF_CUDA_CHECK_LAUNCH();
+    if (a.prof) {                                                 // debug: stamps relative to the first MMA wait of unit 9
+        long long h[192];
+        NERF_CUDA(cudaStreamSynchronize(st));
+        NERF_CUDA(cudaMemcpy(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost));
+        const long long t0 = h[9 * 2 * 8 + 3];
+        for (int x = 0; x < 2; ++x)
+            fprintf(stderr, "bwd unit 5 slot %d: n_full seen at %lld %lld %lld %lld, pass 1 done %lld\n", x, h[160 + x * 8] - t0, h[161 + x * 8] - t0,
+                    h[162 + x * 8] - t0, h[163 + x * 8] - t0, h[164 + x * 8] - t0);
+        for (int x = 0; x < 2; ++x)
+            fprintf(stderr, "bwd unit 6->5 slot %d io thread: refill loop entered %lld, slab 0 free %lld, dz store read out %lld, slab 3 free %lld\n", x,
+                    h[176 + x * 4] - t0, h[177 + x * 4] - t0, h[178 + x * 4] - t0, h[179 + x * 4] - t0);
+        for (int l = 9; l >= 0; --l)
+            for (int x = 0; x < 2; ++x) {
+                const long long* r = h + (l * 2 + x) * 8;
+                fprintf(stderr, "bwd unit %d slot %d: mma wait %lld..%lld issued %lld | epi wait %lld..%lld math done %lld synced %lld\n", l, x,
+                        r[0] - t0, r[1] - t0, r[2] - t0, r[3] - t0, r[4] - t0, r[5] - t0, r[6] - t0);
+            }
+        cudaFree(a.prof);
+    }
     return NERF_OK;
 }
 
@@ -180,6 +202,7 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
     a.P = T.P; a.P_pad = T.P_pad; a.n_tiles = T.n_tiles; a.tr_tiles = T.tr_tiles;
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
+    { const char* e = getenv("NERF_BWD_PF"); const int v = e ? atoi(e) : 11; a.pf_dist = v % 10; a.pf_next = v >= 10; }
     static int cg = -1;
     if (cg < 0) { const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2; }
     if (stage != 3) { rc = (cg == 2) ? launch_bwd<2>(a, st) : launch_bwd<1>(a, st); if (rc) return rc; }
