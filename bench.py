@@ -37,6 +37,19 @@ def load_peaks():
     return dict(hbm=6650.0, tensor_burst=1590.0, tensor_sustained=1400.0, src="fallback")
 
 
+def ncu_traffic():
+    """dram__bytes_read + dram__bytes_write per launch of the training kernels from the committed ncu --set full
+    summary (profiles/, written by scripts/ncu_summary.py at this workload size); {} when absent."""
+    path = os.path.join(ROOT, "profiles", "r01_train_tc_v5_ncu.json")
+    out = {}
+    if os.path.exists(path):
+        for k in json.load(open(path))["kernels"]:
+            for name in ("g1_fused_tc_kernel", "g1_bwd_tc_kernel", "g1_wgrad_tc_kernel"):
+                if name in k["kernel"] and "dram_bytes" in k:
+                    out[name] = k["dram_bytes"]
+    return out
+
+
 def nerf_pth_state_dict():
     z = np.load(os.path.join(ROOT, "tests", "golden", "nerf_pth.npz"))
     return {str(k): torch.from_numpy(z[str(k)]) for k in z["__keys__"]}
@@ -154,6 +167,16 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------ our arm -----
+def dominant_roofline(kernels, peaks):
+    """The contract's `roofline` object for the longest kernel of the step, against the resource that binds it."""
+    name, k = max(kernels.items(), key=lambda kv: kv[1]["ms"])
+    r = k[k["bound"]]
+    return {"bound": k["bound"], "kernel": name, "achieved": r["achieved"], "unit": r["unit"], "frac": r["frac"],
+            "peak": peaks["hbm"] if k["bound"] == "hbm" else peaks["tensor_sustained"],
+            "peak_source": peaks["src"] + (" HBM copy" if k["bound"] == "hbm" else " bf16 sustained"),
+            "traffic": k["traffic"], "ms": k["ms"], "algorithmic_bytes": k["hbm"]["bytes"]}
+
+
 def timed_steps(fn, steps, flush):
     """Each step bracketed by its own CUDA events on the current stream; L2 is flushed
     (a 256 MiB write) between steps, outside the timed brackets."""
@@ -264,13 +287,21 @@ def run_ours(args):
         ms_mlp = float(np.mean(timed_steps(mlp_only, n_it, flush)))
         n_tiles = (b * s + 127) // 128
         wgrad_bytes = n_tiles * ((10 + 9 + 2) * 65536 + 3 * 16384 + 2 * 4096)     # dz + unit inputs + head inputs + encodings + dh
+        act_bytes = n_tiles * 65536                                                # one unit's [128 x 256] bf16 slabs, all tiles
+        fwd_bytes = 10 * act_bytes + 2 * n_tiles * 16384 + 10 * n_tiles * 128 * 8 + b * s * 20   # activations, encodings, stats, t/sigma/rgb
+        dgrad_bytes = 20 * act_bytes + 10 * n_tiles * 128 * 8 + n_tiles * 4096 + b * s * 16      # n_l in, dz_l out, stats, dh image, d_sigma/d_rgb
+        traffic = ncu_traffic()
+
+        def kern(name, ms, flop, nbytes):
+            tf, gbs = flop / ms / 1e9, nbytes / ms / 1e6
+            ft, fh = tf / peaks["tensor_sustained"], gbs / peaks["hbm"]
+            return {"ms": ms, "bound": "tensor" if ft >= fh else "hbm", "frac": max(ft, fh),
+                    "tensor": {"achieved": tf, "unit": "TFLOP/s", "frac": ft}, "hbm": {"achieved": gbs, "unit": "GB/s", "frac": fh, "bytes": nbytes},
+                    "traffic": traffic.get(name)}
         kernels = {
-            "g1_fused_tc_kernel<2,train>": {"ms": ms_fwd, "bound": "tensor", "achieved": FLOP_PER_POINT_FWD * b * s / ms_fwd / 1e9,
-                                            "unit": "TFLOP/s", "frac": FLOP_PER_POINT_FWD * b * s / ms_fwd / 1e9 / peaks["tensor_sustained"]},
-            "g1_bwd_tc_kernel<2>": {"ms": ms_dgrad, "bound": "tensor", "achieved": 2 * 9 * 65536 * b * s / ms_dgrad / 1e9,
-                                    "unit": "TFLOP/s", "frac": 2 * 9 * 65536 * b * s / ms_dgrad / 1e9 / peaks["tensor_sustained"]},
-            "g1_wgrad_tc_kernel": {"ms": ms_wg, "bound": "hbm", "achieved": wgrad_bytes / ms_wg / 1e6,
-                                   "unit": "GB/s", "frac": wgrad_bytes / ms_wg / 1e6 / peaks["hbm"], "bytes": wgrad_bytes},
+            "g1_fused_tc_kernel<2,train>": kern("g1_fused_tc_kernel", ms_fwd, FLOP_PER_POINT_FWD * b * s, fwd_bytes),
+            "g1_bwd_tc_kernel<2>": kern("g1_bwd_tc_kernel", ms_dgrad, 2 * 9 * 65536 * b * s, dgrad_bytes),
+            "g1_wgrad_tc_kernel": kern("g1_wgrad_tc_kernel", ms_wg, 2 * (9 * 65536 + 3 * 16384 + 10 * 256 + 2 * 1024) * b * s, wgrad_bytes),
         }
         mlp_kernel_name = "G1 MLP fwd+bwd on tcgen05 (g1_fused_tc_kernel<train> + g1_bwd_tc_kernel + g1_wgrad_tc_kernel + unfold)"
     else:
@@ -360,10 +391,11 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": RAYS * 9 * 4, "d2h_bytes_per_step": 4},
             "gpu_launches": trainer.kernel_launches * K,
             "clocks": clk.summary(),
-            "roofline": {"bound": "tensor", "kernel": mlp_kernel_name,
-                         "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
-                         "frac": mlp_tflops / tensor_peak, "traffic": None, "peak_source": peaks["src"] + " bf16 sustained",
-                         "ms": ms_mlp},
+            "roofline": dominant_roofline(kernels, peaks) if kernels else
+                        {"bound": "tensor", "kernel": mlp_kernel_name, "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
+                         "frac": mlp_tflops / tensor_peak, "traffic": None, "peak_source": peaks["src"] + " bf16 sustained", "ms": ms_mlp},
+            "roofline_mlp_step": {"bound": "tensor", "kernel": mlp_kernel_name, "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
+                                  "frac": mlp_tflops / tensor_peak, "ms": ms_mlp},
             "roofline_hbm": {"composite_fwd": {"achieved": comp_fwd_gbs, "frac": comp_fwd_gbs / peaks["hbm"], "ms": ms_cf},
                              "composite_bwd": {"achieved": comp_bwd_gbs, "frac": comp_bwd_gbs / peaks["hbm"], "ms": ms_cb},
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
