@@ -354,6 +354,16 @@ def run_ours(args):
                                                         rfocal, NEAR, FAR, SAMPLES), 3, flush)
     render_rps = rh * rw / (float(np.mean(ms_r)) * 1e-3)
     render_tflops = render_rps * SAMPLES * FLOP_PER_POINT_FWD / 1e12
+    # D3: 64 coarse + 128 fine samples (hierarchical inverse-CDF pass, 192-point fine evaluation)
+    d3 = None
+    if args.precision == "bf16":
+        with torch.no_grad():
+            model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES, num_fine=128)
+            ms_d3 = timed_steps(lambda i: model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw,
+                                                             rfocal, NEAR, FAR, SAMPLES, num_fine=128), 2, flush)
+        d3_rps = rh * rw / (float(np.mean(ms_d3)) * 1e-3)
+        d3 = {"value": d3_rps, "unit": "rays/s", "workload": f"{rh}x{rw}, 64 coarse + 128 fine samples (256 MLP evaluations per ray)",
+              "mlp_tflops": d3_rps * 256 * FLOP_PER_POINT_FWD / 1e12, "frac_tensor": d3_rps * 256 * FLOP_PER_POINT_FWD / 1e12 / peaks["tensor_sustained"]}
 
     # ---- HEAD generation (fp32 FFMA path): render_image 200x200 x 64 fenceposts (63 intervals per ray) ----
     from nerf_b200.head import HeadNeRF
@@ -401,6 +411,7 @@ def run_ours(args):
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
             "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},
+            "render_d3": d3,
             "kernels": kernels,
             "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
                             "mlp_tflops": head_tflops},

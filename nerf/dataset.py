@@ -1,2 +1,2 @@
-"""`from nerf.dataset import PixelRayDataset` -- the reference's import path."""
-from nerf_b200.dataset import PixelRayDataset  # noqa: F401
+"""`from nerf.dataset import PixelRayDataset, ImageRayDataset` -- the reference's import path."""
+from nerf_b200.dataset import ImageRayDataset, PixelRayDataset  # noqa: F401

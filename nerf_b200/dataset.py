@@ -109,3 +109,62 @@ class PixelRayDataset(data.Dataset):
             if drop_last and sel.numel() < batch_size:
                 break
             yield self.gather(sel)
+
+
+class ImageRayDataset(data.Dataset):
+    """The reference's block-stratified dataset (nerf/dataset.py:6-172): every item draws
+    `num_samples_per_block` pixels from each cell of a `num_vertical_blocks x num_horizontal_blocks`
+    grid over ONE image and returns them as [num_samples_per_block, blocks, ...] tensors with the
+    reference's keys.  The index arithmetic (:134-153) is a handful of integer ops on a
+    [samples, blocks] grid and stays in torch; pixels, poses and world-space rays of the whole item come
+    from ONE launch of the batched gather kernel (`nerf_gather_pixel_rays`) when the images live on the
+    GPU.  `block_ray_idx` may be passed in (tests, reproducible runs); by default it is drawn like the
+    reference does (`torch.multinomial` over uniform weights, with replacement)."""
+
+    def __init__(self, images, poses, states, focal_length, num_vertical_blocks=8, num_horizontal_blocks=8,
+                 num_samples_per_block=2):
+        self.images, self.poses, self.states = images, poses, states
+        self.focal_length = float(focal_length)
+        self.num_vertical_blocks, self.num_horizontal_blocks = num_vertical_blocks, num_horizontal_blocks
+        self.num_samples_per_block = num_samples_per_block
+        self.horizontal_block_size = images.shape[2] // num_horizontal_blocks      # :70-73
+        self.vertical_block_size = images.shape[1] // num_vertical_blocks
+        self.total_block_area = self.horizontal_block_size * self.vertical_block_size
+        self._rays = None
+
+    rays = PixelRayDataset.rays
+
+    def __len__(self):
+        return (self.images.shape[0] * self.total_block_area) // self.num_samples_per_block     # :93-94
+
+    def block_pixels(self, idx, block_ray_idx=None, generator=None):
+        """(image_bi, image_hi, image_wi), each [samples, blocks] int64 -- nerf/dataset.py:134-158."""
+        dev = self.images.device
+        blocks = self.num_vertical_blocks * self.num_horizontal_blocks
+        if block_ray_idx is None:
+            block_ray_idx = torch.multinomial(torch.ones(self.num_samples_per_block, self.total_block_area), blocks,
+                                              replacement=True, generator=generator)
+        block_ray_idx = block_ray_idx.to(dev)
+        block_idx = torch.arange(blocks, device=dev).unsqueeze(0)
+        image_wi = block_ray_idx % self.horizontal_block_size + (block_idx % self.num_horizontal_blocks) * self.horizontal_block_size
+        image_hi = block_ray_idx // self.horizontal_block_size + (block_idx // self.num_horizontal_blocks) * self.vertical_block_size
+        image_bi = torch.full_like(image_hi, int(idx) // self.total_block_area)
+        return image_bi, image_hi, image_wi
+
+    def __getitem__(self, idx, block_ray_idx=None, generator=None):
+        bi, hi, wi = self.block_pixels(idx, block_ray_idx, generator)
+        shape = hi.shape
+        h, w = self.images.shape[1], self.images.shape[2]
+        pose = self.poses[bi]
+        pose_o, pose_d = pose[..., :3, 3], pose[..., :3, :3]
+        if self.images.is_cuda:
+            flat = ((bi * h + hi) * w + wi).reshape(-1)
+            o, d, px, _, _ = ops.gather_pixel_rays(self.images, self.poses, self.focal_length, flat)
+            pixel, rays_o, rays_d = px.view(*shape, -1), o.view(*shape, 3), d.view(*shape, 3)
+            ray = self.rays[hi, wi]
+        else:                                                       # host tensors: the reference's own indexing
+            pixel = self.images[bi, hi, wi]
+            ray = self.rays[hi, wi]
+            rays_o, rays_d = pose_o, (pose_d * ray.unsqueeze(-2)).sum(dim=-1)
+        return dict(image_bi=bi, image_hi=hi, image_wi=wi, pixels=pixel, states=self.states[bi], rays=ray,
+                    pose_o=pose_o, pose_d=pose_d, rays_o=rays_o, rays_d=rays_d)

@@ -1,6 +1,8 @@
 """GPU parity: every kernel behind the C ABI against the CPU oracle / golden vectors.
 Tolerances: bit-exact for indices and sample bins; <=1e-3 max-abs on composited pixels
 in fp32 mode (north star), much tighter where the arithmetic allows."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -289,6 +291,25 @@ def test_gather_pixel_rays():
         assert torch.equal(o[i].cpu(), poses[bi, :3, 3])
         _, wd = g1.rays_to_world_coordinates(rays[hi, wi], poses[bi, :3, 3], poses[bi, :3, :3])
         np.testing.assert_allclose(d[i].cpu().numpy(), wd.numpy(), rtol=0, atol=1e-6)
+
+
+def test_image_ray_dataset_gpu_items():
+    """ImageRayDataset on CUDA tensors (one gather-kernel launch per item) against the reference fixture."""
+    from nerf.dataset import ImageRayDataset
+    from test_host import _image_ray_inputs, GOLDEN
+    z = np.load(os.path.join(GOLDEN, "image_ray_dataset.npz"))
+    images, poses, states = (t.cuda() for t in _image_ray_inputs())
+    ds = ImageRayDataset(images, poses, states, 20.0, num_vertical_blocks=4, num_horizontal_blocks=4, num_samples_per_block=2)
+    for idx in (0, 17, 35):
+        torch.manual_seed(100 + idx)
+        item = ds[idx]
+        for k in (k.split("/", 1)[1] for k in z.files if k.startswith(f"{idx}/")):
+            want = z[f"{idx}/{k}"]
+            assert item[k].is_cuda and tuple(item[k].shape) == want.shape, k
+            if want.dtype.kind == "i":
+                assert np.array_equal(item[k].cpu().numpy(), want), k
+            else:
+                np.testing.assert_allclose(item[k].cpu().numpy(), want, rtol=0, atol=1e-6, err_msg=k)
 
 
 def test_fused_adam_vs_torch():

@@ -10,6 +10,7 @@ import pytest
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
 def test_library_exports_every_declared_symbol():
@@ -187,3 +188,33 @@ def test_gloo_world_size_2():
     for p in procs:
         p.join(timeout=60)
     assert len(res) == 2 and all(all(r[1:]) for r in res), res
+
+
+def _image_ray_inputs():
+    g = torch.Generator().manual_seed(11)            # same construction as tests/golden/make_image_ray_dataset.py
+    images = torch.rand(3, 16, 24, 3, generator=g)
+    poses = torch.eye(4).repeat(3, 1, 1); poses[:, :3, :] = torch.randn(3, 3, 4, generator=g)
+    states = torch.randn(3, 5, generator=g)
+    return images, poses, states
+
+
+def test_image_ray_dataset_matches_reference_items():
+    """Block-stratified items against the UNMODIFIED reference class (fixture generated from it):
+    same length, same keys, same indices (global-generator draw included), same tensors."""
+    from nerf.dataset import ImageRayDataset
+    z = np.load(os.path.join(GOLDEN, "image_ray_dataset.npz"))
+    images, poses, states = _image_ray_inputs()
+    ds = ImageRayDataset(images, poses, states, 20.0, num_vertical_blocks=4, num_horizontal_blocks=4, num_samples_per_block=2)
+    assert len(ds) == int(z["len"])
+    for idx in (0, 17, 35):
+        torch.manual_seed(100 + idx)
+        item = ds[idx]
+        keys = sorted(k.split("/", 1)[1] for k in z.files if k.startswith(f"{idx}/"))
+        assert sorted(item.keys()) == keys
+        for k in keys:
+            want = z[f"{idx}/{k}"]
+            assert tuple(item[k].shape) == want.shape, k
+            if want.dtype.kind == "i":
+                assert np.array_equal(item[k].numpy(), want), k
+            else:
+                np.testing.assert_allclose(item[k].numpy(), want, rtol=0, atol=1e-6, err_msg=k)
