@@ -253,6 +253,18 @@ int64_t nerf_head_mlp_workspace_bytes(int64_t P);
 int nerf_head_mlp_fwd(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
                       float* out, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* bf16 tensor-core (tcgen05) form of NeRF.forward for the HEAD generation (nerf/model.py:553-594):
+ * integrated_pe + prediction_heads in one persistent kernel, activations on chip.
+ *   nerf_head_pack_weights: the 22 state_dict tensors (HOST array of DEVICE pointers, as for
+ *     nerf_head_mlp_fwd) -> operand image of nerf_head_packed_bytes() bytes; n_in = 3*encoding_size.
+ *   nerf_head_fwd_tc: rays [B,3], fenceposts t [B,S] -> out [B,S-1,n_out] (density | colour |
+ *     segmentation rows, fp32) and mean_out [B,S-1,3] (the Gaussian means nerf_head_composite takes as
+ *     points).  Built for encoding_size = 32 (n_deg = 16) and n_out <= 64. */
+int64_t nerf_head_packed_bytes(void);
+int nerf_head_pack_weights(const float* const* params_host, int n_in, int n_out, void* packed, void* stream);
+int nerf_head_fwd_tc(const void* packed, const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
+                     float base_radius, int min_deg, int n_deg, int n_out, float* out, float* mean_out, void* stream);
+
 /* Colour + segmentation composite of NeRF.render_rays (nerf/model.py:652-663) on the trunk's
  * interleaved rows out [B,S,n_out] = [density | colour(3) | segmentation(n_seg)], n_out = 4+n_seg,
  * n_seg <= 64; points [B,S,3] are the Gaussian means.  noise [B,S] (or NULL) * noise_std is added

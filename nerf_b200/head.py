@@ -22,8 +22,13 @@ class HeadNeRF(nn.Module):
 
     def __init__(self, color_outputs=3, segmentation_outputs=50, hidden_size=256, encoding_size=32,
                  focal_length=112.0, min_x=-20.0, min_y=-20.0, min_z=-20.0,
-                 max_x=20.0, max_y=20.0, max_z=20.0, max_chunk_rays=65536):
+                 max_x=20.0, max_y=20.0, max_z=20.0, max_chunk_rays=65536, precision="fp32"):
         super().__init__()
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if precision == "bf16" and (encoding_size != 32 or 1 + color_outputs + segmentation_outputs > 64):
+            raise ValueError("the tcgen05 HEAD kernel is built for encoding_size=32 and at most 64 outputs")
+        self.precision = precision
         if hidden_size != 256:
             raise ValueError("the sm_100a kernels are built for hidden_size=256")
         if color_outputs != 3 or not (0 <= segmentation_outputs <= 64):
@@ -92,6 +97,19 @@ class HeadNeRF(nn.Module):
               "nerf_head_encode")
         return (mean.view(*batch, s - 1, 3), cov.view(*batch, s - 1, 3), feat.view(*batch, s - 1, 6 * n_deg))
 
+    def _fwd_tc(self, o, d, t):
+        """Encoder + trunk + output head on tcgen05 (csrc/head_tc.cu) -> (means [B,S-1,3], out [B,S-1,n_out])."""
+        b, s = t.shape
+        n_out = 1 + self.color_outputs + self.segmentation_outputs
+        ptrs, keep = self._param_pointers()
+        packed = torch.empty(lib().nerf_head_packed_bytes(), dtype=torch.uint8, device=t.device)
+        check(lib().nerf_head_pack_weights(ptrs, 3 * self.encoding_size, n_out, ptr(packed), stream()), "nerf_head_pack_weights")
+        out = torch.empty(b, s - 1, n_out, device=t.device); mean = torch.empty(b, s - 1, 3, device=t.device)
+        r = 1.0 / (math.sqrt(3) * self.focal_length)
+        check(lib().nerf_head_fwd_tc(ptr(packed), ptr(o), ptr(d), ptr(t), b, s, r, -4, self.encoding_size // 2, n_out,
+                                     ptr(out), ptr(mean), stream()), "nerf_head_fwd_tc")
+        return mean, out
+
     def _trunk(self, feat2d):
         p, n_in = feat2d.shape
         n_out = 1 + self.color_outputs + self.segmentation_outputs
@@ -106,8 +124,13 @@ class HeadNeRF(nn.Module):
     @torch.no_grad()
     def forward(self, rays_o, rays_d, samples, states_x=None, states_d=None):
         """nerf/model.py:553-594 -> (mean, density [..,1], color [..,3], segmentation [..,n_seg])."""
-        mean, _, feat = self.integrated_pe(rays_o, rays_d, samples)
-        out = self._trunk(feat.reshape(-1, feat.shape[-1])).view(*feat.shape[:-1], -1)
+        if self.precision == "bf16":
+            batch = samples.shape[:-1]; s = samples.shape[-1]
+            mean, out = self._fwd_tc(ops._f32c(rays_o.reshape(-1, 3)), ops._f32c(rays_d.reshape(-1, 3)), ops._f32c(samples.reshape(-1, s)))
+            mean, out = mean.view(*batch, s - 1, 3), out.view(*batch, s - 1, -1)
+        else:
+            mean, _, feat = self.integrated_pe(rays_o, rays_d, samples)
+            out = self._trunk(feat.reshape(-1, feat.shape[-1])).view(*feat.shape[:-1], -1)
         density, color, seg = out.split([1, self.color_outputs, self.segmentation_outputs], dim=-1)
         return mean, density, color, seg
 
@@ -118,9 +141,13 @@ class HeadNeRF(nn.Module):
         o = ops._f32c(rays_o.reshape(-1, 3)); d = ops._f32c(rays_d.reshape(-1, 3))
         b = o.shape[0]
         t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)
-        mean, _, feat = self.integrated_pe(o, d, t)
         s1 = num_samples - 1
-        out = self._trunk(feat.view(b * s1, -1))
+        if self.precision == "bf16":
+            mean, out = self._fwd_tc(o, d, t)
+            out = out.view(b * s1, -1)
+        else:
+            mean, _, feat = self.integrated_pe(o, d, t)
+            out = self._trunk(feat.view(b * s1, -1))
         if noise is None and density_noise_std != 0.0:           # the reference draws torch.randn here (:652)
             noise = torch.randn(b, s1, device=o.device)
         img = torch.empty(b, 3, device=o.device); seg = torch.empty(b, self.segmentation_outputs, device=o.device)

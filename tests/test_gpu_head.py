@@ -97,3 +97,56 @@ def test_head_vs_oracle_large(head_model, head_ref):
     assert np.abs(gi.cpu().numpy() - wi.numpy()).max() <= 1e-3
     np.testing.assert_allclose(gi.cpu().numpy(), wi.numpy(), rtol=0, atol=2e-5)
     np.testing.assert_allclose(gs.cpu().numpy(), ws.numpy(), rtol=1e-4, atol=1e-3)
+
+
+# ------------------------------------------------------------ bf16 tensor-core path ----
+@pytest.fixture(scope="module")
+def head_model_bf16(head_ref):
+    from nerf.model import NeRF
+    m = NeRF(encoding_size=32, precision="bf16").cuda()
+    m.load_state_dict({str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]}, strict=True)
+    return m
+
+
+def test_head_tc_forward_vs_reference(head_model_bf16, head_ref):
+    """tcgen05 encoder + trunk (bf16 operands, fp32 accumulate) against the unmodified reference's outputs:
+    Gaussian means in fp32, trunk outputs to bf16 accuracy (activations are O(1) after LayerNorm, six
+    chained bf16 GEMMs)."""
+    o, d, t = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"]), _cuda(head_ref["head_t_rand"])
+    mean, dens, col, seg = head_model_bf16(o, d, t)
+    assert dens.shape == (6, 15, 1) and col.shape == (6, 15, 3) and seg.shape == (6, 15, 50)
+    np.testing.assert_allclose(mean.cpu().numpy(), head_ref["head_ipe_mean"], rtol=1e-5, atol=1e-5)
+    for got, key in ((dens, "head_fwd_density"), (col, "head_fwd_color"), (seg, "head_fwd_seg")):
+        want = head_ref[key]
+        err = np.abs(got.cpu().numpy() - want).max()
+        print(key, "max|diff|", err, "scale", np.abs(want).max())
+        assert err <= 3e-2 * max(1.0, np.abs(want).max())
+
+
+def test_head_tc_render_vs_fp32(head_model, head_model_bf16):
+    """Rendered pixels and segmentation of the bf16 path against the fp32 path (itself pinned to the reference at
+    1e-5) on ragged sizes: several tiles, rays straddling tiles, a partial last tile."""
+    g = torch.Generator().manual_seed(31)
+    o = (torch.randn(301, 3, generator=g) * 2).cuda(); d = torch.randn(301, 3, generator=g).cuda()
+    u = torch.rand(301, 48, generator=g).cuda()
+    wi, ws = head_model.render_rays(o, d, 48, u=u)
+    gi, gs = head_model_bf16.render_rays(o, d, 48, u=u)
+    assert gi.shape == wi.shape and gs.shape == ws.shape
+    err = (gi - wi).abs().max().item()
+    mse = ((gi - wi) ** 2).mean().item()
+    print("HEAD bf16 vs fp32 pixels: max|diff|", err, "PSNR", -10 * np.log10(max(mse, 1e-20)))
+    assert err <= 2e-2 and -10 * np.log10(max(mse, 1e-20)) >= 45.0
+    assert (gs - ws).abs().max().item() <= 0.15                      # log-probabilities of 50 classes
+
+
+def test_head_tc_render_image_shards(head_model_bf16):
+    """render_image through the bf16 path: shapes, determinism, and a ray shard equals the slice of the full frame."""
+    from oracle.g1 import pose_spherical
+    pose = pose_spherical(40.0, -30.0, 4.0).cuda()
+    co, cr = pose[None, :3, 3].contiguous(), pose[None, :3, :3].contiguous()
+    img, seg = head_model_bf16.render_image(co, cr, 20, 24, 30.0, 33)
+    assert img.shape == (1, 20, 24, 3) and seg.shape == (1, 20, 24, 50) and torch.isfinite(img).all() and torch.isfinite(seg).all()
+    img2, _ = head_model_bf16.render_image(co, cr, 20, 24, 30.0, 33)
+    assert torch.equal(img, img2)
+    part, _ = head_model_bf16.render_image(co, cr, 20, 24, 30.0, 33, ray_begin=100, ray_end=333)
+    assert torch.allclose(part, img.reshape(-1, 3)[100:333], atol=1e-6)
