@@ -375,6 +375,15 @@ def run_ours(args):
         ms_h = timed_steps(lambda i: hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES), 3, flush)
     head_rps = hh * hh / (float(np.mean(ms_h)) * 1e-3)
     head_tflops = head_rps * (SAMPLES - 1) * 601_088 / 1e12
+    # ... and its tcgen05 bf16 path (head_tc.cu): 800x800
+    torch.manual_seed(3)
+    hb = HeadNeRF(precision="bf16").to(dev)
+    hbh = 800
+    with torch.no_grad():
+        hb.render_image(pose[None, :3, 3], pose[None, :3, :3], hbh, hbh, 896.0, SAMPLES)
+        ms_hb = timed_steps(lambda i: hb.render_image(pose[None, :3, 3], pose[None, :3, :3], hbh, hbh, 896.0, SAMPLES), 3, flush)
+    headb_rps = hbh * hbh / (float(np.mean(ms_hb)) * 1e-3)
+    headb_tflops = headb_rps * (SAMPLES - 1) * 601_088 / 1e12
 
     # max over ranks of the timed totals
     if world > 1:
@@ -415,6 +424,8 @@ def run_ours(args):
             "kernels": kernels,
             "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
                             "mlp_tflops": head_tflops},
+            "head_render_bf16": {"value": headb_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hbh}x{hbh} x {SAMPLES} fenceposts render_image, tcgen05 bf16 (head_tc_kernel)",
+                                 "mlp_tflops": headb_tflops, "frac_tensor": headb_tflops / tensor_peak},
             "loss": loss_val,
         }
         if cpu:

@@ -259,19 +259,22 @@ int nerf_head_mlp_fwd(const float* const* params_host, const float* feat, int64_
  *     nerf_head_mlp_fwd) -> operand image of nerf_head_packed_bytes() bytes; n_in = 3*encoding_size.
  *   nerf_head_fwd_tc: rays [B,3], fenceposts t [B,S] -> out [B,S-1,n_out] (density | colour |
  *     segmentation rows, fp32) and mean_out [B,S-1,3] (the Gaussian means nerf_head_composite takes as
- *     points).  Built for encoding_size = 32 (n_deg = 16) and n_out <= 64. */
+ *     points).  log_softmax_seg != 0: the segmentation columns hold log_softmax(logits) (model.py:662),
+ *     to be composited with seg_is_log_softmax = 1.  Built for encoding_size = 32 (n_deg = 16), n_out <= 64. */
 int64_t nerf_head_packed_bytes(void);
 int nerf_head_pack_weights(const float* const* params_host, int n_in, int n_out, void* packed, void* stream);
 int nerf_head_fwd_tc(const void* packed, const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
-                     float base_radius, int min_deg, int n_deg, int n_out, float* out, float* mean_out, void* stream);
+                     float base_radius, int min_deg, int n_deg, int n_out, int log_softmax_seg, float* out, float* mean_out,
+                     void* stream);
 
 /* Colour + segmentation composite of NeRF.render_rays (nerf/model.py:652-663) on the trunk's
  * interleaved rows out [B,S,n_out] = [density | colour(3) | segmentation(n_seg)], n_out = 4+n_seg,
  * n_seg <= 64; points [B,S,3] are the Gaussian means.  noise [B,S] (or NULL) * noise_std is added
- * to the density.  pixels [B,3], seg_out [B,n_seg], weights [B,S] (optional). */
+ * to the density.  pixels [B,3], seg_out [B,n_seg], weights [B,S] (optional).  seg_is_log_softmax: the
+ * segmentation columns already went through log_softmax (nerf_head_fwd_tc can emit them that way). */
 int nerf_head_composite(const float* out, int n_out, int n_seg, const float* points, const float* noise,
                         float noise_std, int64_t B, int S, float* pixels, float* seg_out, float* weights,
-                        void* stream);
+                        int seg_is_log_softmax, void* stream);
 
 /* -------------------------------------------------------------- optimiser --- */
 

@@ -115,7 +115,7 @@ __device__ __forceinline__ float warp_max(float v) {
 __global__ void __launch_bounds__(256) head_composite_kernel(
         const float* __restrict__ out, int n_out, int n_seg, const float* __restrict__ points,
         const float* __restrict__ noise, float noise_std, int64_t B, int S,
-        float* __restrict__ pixels, float* __restrict__ seg_out, float* __restrict__ weights) {
+        float* __restrict__ pixels, float* __restrict__ seg_out, float* __restrict__ weights, int seg_is_log_softmax) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < B; ray += warps) {
@@ -157,8 +157,11 @@ __global__ void __launch_bounds__(256) head_composite_kernel(
                     const float* row = out + (base + s0 + kk) * n_out + 4;
                     const float x0 = lane < n_seg ? row[lane] : -INFINITY;
                     const float x1 = lane + 32 < n_seg ? row[lane + 32] : -INFINITY;
-                    const float m = warp_max(fmaxf(x0, x1));
-                    const float lse = m + logf(warp_sum(expf(x0 - m) + expf(x1 - m)));
+                    float lse = 0.f;
+                    if (!seg_is_log_softmax) {
+                        const float m = warp_max(fmaxf(x0, x1));
+                        lse = m + logf(warp_sum(expf(x0 - m) + expf(x1 - m)));
+                    }
                     const float v0 = lw + (x0 - lse), v1 = lw + (x1 - lse);
                     if (lane < n_seg) { const float mn = fmaxf(M0, v0); S0 = S0 * expf(M0 - mn) + expf(v0 - mn); M0 = mn; }
                     if (lane + 32 < n_seg) { const float mn = fmaxf(M1, v1); S1 = S1 * expf(M1 - mn) + expf(v1 - mn); M1 = mn; }
@@ -176,12 +179,12 @@ __global__ void __launch_bounds__(256) head_composite_kernel(
 
 extern "C" int nerf_head_composite(const float* out, int n_out, int n_seg, const float* points, const float* noise,
                                    float noise_std, int64_t B, int S, float* pixels, float* seg_out, float* weights,
-                                   void* stream) {
+                                   int seg_is_log_softmax, void* stream) {
     if (!out || !points || B < 0 || S <= 0 || n_seg < 0 || n_seg > 64 || n_out != 4 + n_seg) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
     int64_t blocks = (B + 7) / 8, cap = (int64_t)nerf_num_sms() * 32;
     head_composite_kernel<<<(unsigned)(blocks < cap ? blocks : cap), 256, 0, (cudaStream_t)stream>>>(
-        out, n_out, n_seg, points, noise, noise_std, B, S, pixels, n_seg ? seg_out : nullptr, weights);
+        out, n_out, n_seg, points, noise, noise_std, B, S, pixels, n_seg ? seg_out : nullptr, weights, seg_is_log_softmax);
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }

@@ -10,7 +10,8 @@
 //     which is free at that point -- no separate encoding slab;
 //   * every unit's bias rides in the accumulator through a constant [128 x 16] "ones" A block and a
 //     4 KB bias block (bias as hi+mid+lo bf16 parts) in front of the unit's first weight stage;
-//   * the output head is the sixth unit (N padded to 256), its epilogue writes rows of n_out floats.
+//   * the output head is the sixth unit with N = 64 (k-cores of 32 rows per CTA, 512 B), its epilogue
+//     writes rows of n_out floats.
 // SURVEY 8(a) rows a5-H, a6-H, a7 (nerf/model.py:24-163, 525-594).
 #include "tc_layout.cuh"
 #include <stdlib.h>
@@ -28,24 +29,27 @@
 #define HT_ONES_LBO 128
 #define HT_ONES_SBO 256
 
-struct HeadTcLayout { int nk[HT_UNITS]; int half_kcores[HT_UNITS]; int64_t unit_off[HT_UNITS]; int64_t weight_bytes, vec_off, total; };
+#define HT_OUT_N 64                                        // MMA N of the output head (n_out <= 64)
+struct HeadTcLayout { int nk[HT_UNITS]; int half_kcores[HT_UNITS]; int kcore_bytes[HT_UNITS]; int64_t unit_off[HT_UNITS]; int64_t weight_bytes, vec_off, total; };
 static inline void make_head_tc_layout(HeadTcLayout& L) {
     int64_t o = 0;
     for (int l = 0; l < HT_UNITS; ++l) {
         L.nk[l] = l == 0 ? 2 : 4;
         L.half_kcores[l] = TF_BIAS_KCORES + 8 * L.nk[l];
-        L.unit_off[l] = o; o += 2ll * L.half_kcores[l] * TF_KCORE_BYTES;
+        L.kcore_bytes[l] = (l < 5 ? 128 : HT_OUT_N / 2) * 16;       // rows per CTA half x 16 B
+        L.unit_off[l] = o; o += 2ll * L.half_kcores[l] * L.kcore_bytes[l];
     }
     L.weight_bytes = o; L.vec_off = o; L.total = o + 10 * 256 * 4;
 }
 
 struct HeadTcArgs {
     const uint8_t* stages; const float* vec;
-    int nk[HT_UNITS]; int half_kcores[HT_UNITS]; int64_t unit_off[HT_UNITS];
+    int nk[HT_UNITS]; int half_kcores[HT_UNITS]; int kcore_bytes[HT_UNITS]; int64_t unit_off[HT_UNITS];
     const float* rays_o; const float* rays_d; const float* t;     // [B,3], [B,3], fenceposts [B,S]
     int64_t B; int S; int64_t P; int n_tiles;                     // P = B (S-1) intervals
     float base_radius; int min_deg;
     float* out; int n_out; float* mean_out;                       // [P,n_out], [P,3]
+    int log_softmax_seg;                                          // segmentation columns leave as log_softmax
     uint32_t wait_hint;
 };
 
@@ -61,11 +65,11 @@ struct HeadParams { const float* p[22]; };                        // state_dict 
 // one thread per 16-byte row of a k-core: (unit, n-half, k-core, n)
 __global__ void head_pack_kernel(HeadParams hp, HeadTcLayout L, int n_in, int n_out, uint8_t* __restrict__ packed) {
     const int l = blockIdx.y;
-    const int hk = L.half_kcores[l];
+    const int hk = L.half_kcores[l], rows = L.kcore_bytes[l] / 16;     // output features per CTA half
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * hk * 128) return;
-    const int r = i & 127, kc = (i >> 7) % hk, nh = (i >> 7) / hk;
-    const int n = nh * 128 + r;
+    if (i >= 2 * hk * rows) return;
+    const int r = i % rows, kc = (i / rows) % hk, nh = (i / rows) / hk;
+    const int n = nh * rows + r;
     const float* W = hp.p[l < 5 ? 4 * l : 20]; const float* bias = hp.p[l < 5 ? 4 * l + 1 : 21];
     const int K = l == 0 ? n_in : 256, N = l < 5 ? 256 : n_out;
     float v[8];
@@ -78,7 +82,7 @@ __global__ void head_pack_kernel(HeadParams hp, HeadTcLayout L, int n_in, int n_
             for (int j = 0; j < 8; ++j) { const int k = (kc - TF_BIAS_KCORES) * 8 + j; if (k < K) v[j] = W[(size_t)n * K + k]; }
         }
     }
-    uint8_t* dst = packed + L.unit_off[l] + ((size_t)(nh * hk + kc)) * TF_KCORE_BYTES + (r >> 3) * TF_B_SBO + (r & 7) * 16;
+    uint8_t* dst = packed + L.unit_off[l] + ((size_t)(nh * hk + kc)) * L.kcore_bytes[l] + (r >> 3) * TF_B_SBO + (r & 7) * 16;
     *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_bf16x2(v[0], v[1]), tc::pack_bf16x2(v[2], v[3]),
                                                 tc::pack_bf16x2(v[4], v[5]), tc::pack_bf16x2(v[6], v[7]));
 }
@@ -93,7 +97,7 @@ __global__ void head_pack_vec_kernel(HeadParams hp, float* __restrict__ vec) {
 extern "C" int64_t nerf_head_packed_bytes(void) { HeadTcLayout L; make_head_tc_layout(L); return L.total; }
 
 extern "C" int nerf_head_pack_weights(const float* const* params_host, int n_in, int n_out, void* packed, void* stream) {
-    if (!params_host || !packed || n_in <= 0 || n_in > 125 || n_out <= 0 || n_out > 256) return NERF_ERR_BAD_ARG;
+    if (!params_host || !packed || n_in <= 0 || n_in > 128 || n_out <= 0 || n_out > HT_OUT_N) return NERF_ERR_BAD_ARG;
     HeadTcLayout L; make_head_tc_layout(L);
     HeadParams hp; for (int i = 0; i < 22; ++i) { if (!params_host[i]) return NERF_ERR_BAD_ARG; hp.p[i] = params_host[i]; }
     cudaStream_t st = (cudaStream_t)stream;
@@ -233,18 +237,43 @@ __device__ __noinline__ void ht_epilogue_ln(uint32_t taddr, uint32_t act_addr, u
     }
 }
 
-// output head: the accumulator row already holds W5 n + b5; n_out (<= 64 here) floats per interval
+// output head: the accumulator row already holds W5 n + b5; n_out (<= 64) floats per interval.  With
+// log_softmax_seg the n_out - 4 segmentation logits leave as log_softmax (nerf/model.py:662): the row is in
+// this thread's registers, so the normaliser costs ~2 instructions per class here and saves the compositing
+// kernel two warp reductions per sample.
 __device__ __noinline__ void ht_epilogue_out(const HeadTcArgs& a, uint32_t taddr, int64_t p, bool valid) {
-    uint32_t r[32];
-    for (int ch = 0; ch * 32 < a.n_out; ++ch) {
-        tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait();
-        if (valid) {
-            float* o = a.out + p * a.n_out + ch * 32;
+    uint32_t r0[32], r1[32];
+    tc::tmem_ld32(taddr, r0);
+    tc::tmem_ld32(taddr + 32, r1);
+    tc::tmem_ld_wait();
+    if (!valid) return;
+    const int n1 = a.n_out - 32;                              // columns held in r1
+    float lse = 0.f;
+    if (a.log_softmax_seg) {
+        float m = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < 32; j += 2)
-                if (ch * 32 + j + 1 < a.n_out) *reinterpret_cast<float2*>(o + j) = make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
-                else if (ch * 32 + j < a.n_out) o[j] = __uint_as_float(r[j]);
-        }
+        for (int j = 4; j < 32; ++j) if (j < a.n_out) m = fmaxf(m, __uint_as_float(r0[j]));
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < n1) m = fmaxf(m, __uint_as_float(r1[j]));
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 4; j < 32; ++j) if (j < a.n_out) sum += __expf(__uint_as_float(r0[j]) - m);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j < n1) sum += __expf(__uint_as_float(r1[j]) - m);
+        lse = m + __logf(sum);
+    }
+    float* o = a.out + p * a.n_out;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+        const float v0 = __uint_as_float(r0[j]) - (j >= 4 ? lse : 0.f), v1 = __uint_as_float(r0[j + 1]) - (j >= 4 ? lse : 0.f);
+        if (j + 1 < a.n_out) *reinterpret_cast<float2*>(o + j) = make_float2(v0, v1);
+        else if (j < a.n_out) o[j] = v0;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+        const float v0 = __uint_as_float(r1[j]) - lse, v1 = __uint_as_float(r1[j + 1]) - lse;
+        if (j + 1 < n1) *reinterpret_cast<float2*>(o + 32 + j) = make_float2(v0, v1);
+        else if (j < n1) o[32 + j] = v0;
     }
 }
 
@@ -292,10 +321,11 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
             for (int l = 0; l < HT_UNITS; ++l)
                 for (int x = 0; x < 2; ++x) {
                     if (x == 1 && q >= cnt1) continue;
-                    const uint8_t* src = a.stages + a.unit_off[l] + (size_t)rank * a.half_kcores[l] * TF_KCORE_BYTES;
+                    const uint32_t kcb = a.kcore_bytes[l];
+                    const uint8_t* src = a.stages + a.unit_off[l] + (size_t)rank * a.half_kcores[l] * kcb;
                     for (int j = 0; j < a.nk[l]; ++j, ++it) {
                         const int slot = it % HT_RING; const uint32_t ph = (it / HT_RING) & 1;
-                        const uint32_t bytes = TF_STAGE_BYTES + (j == 0 ? TF_BIAS_KCORES * TF_KCORE_BYTES : 0);
+                        const uint32_t bytes = (TF_STAGE_KCORES + (j == 0 ? TF_BIAS_KCORES : 0)) * kcb;
                         tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
                         if (tc::elect_one()) {
                             tc::mbar_arrive_expect_tx(ring_full(slot), bytes);
@@ -308,12 +338,13 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
     } else if (warp == 1) {
         if (leader) {
             // ===================== MMA issuer =====================
-            const uint32_t idesc = tc::umma_idesc_bf16(256, 256);
+            constexpr uint32_t idesc_hid = tc::umma_idesc_bf16(256, 256), idesc_out = tc::umma_idesc_bf16(256, HT_OUT_N);
             constexpr uint32_t hi_a = (1024u >> 4) | (1u << 14) | (2u << 29);             // SW128 K-major slabs
             constexpr uint32_t hi_b = (TF_B_SBO >> 4) | (1u << 14);                       // no-swizzle k-cores
             constexpr uint32_t hi_ones = (HT_ONES_SBO >> 4) | (1u << 14);
-            const uint32_t ring_lo = (((base + HT_SM_RING) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
+            const uint32_t ring_addr = ((base + HT_SM_RING) & 0x3FFFFu) >> 4;
             const uint32_t ones_lo = (((base + HT_SM_ONES) & 0x3FFFFu) >> 4) | ((HT_ONES_LBO >> 4) << 16);
+            uint32_t idesc = idesc_hid;
             auto mma = [&](uint32_t d, uint32_t ahi, uint32_t alo, uint32_t blo, uint32_t acc) {
                 tc::umma_bf16_2cta(d, ((uint64_t)ahi << 32) | alo, ((uint64_t)hi_b << 32) | blo, idesc, acc);
             };
@@ -327,6 +358,9 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
                         const uint32_t act_lo = (((base + HT_SM_ACT + x * 65536) & 0x3FFFFu) >> 4) | (1u << 16);
                         const uint32_t d_tmem = tmem_base + x * 256;
                         const int nk = a.nk[l];
+                        const uint32_t kstep = (2u * a.kcore_bytes[l]) >> 4;                 // one K=16 step = two k-cores
+                        const uint32_t ring_lo = ring_addr | ((uint32_t)(a.kcore_bytes[l] >> 4) << 16);   // LBO = k-core stride
+                        idesc = l < 5 ? idesc_hid : idesc_out;
                         for (int j = 0; j < nk; ++j, ++it) {
                             const int slot = it % HT_RING; const uint32_t ph = (it / HT_RING) & 1;
                             const uint32_t alo = act_lo + j * (TC_SLAB_BYTES >> 4);
@@ -335,12 +369,12 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
                             if (tc::elect_one()) {
                                 if (j == 0) {                                // acc = bias: ones block x bias block
                                     mma(d_tmem, hi_ones, ones_lo, blo, 0);
-                                    blo += (TF_BIAS_KCORES * TF_KCORE_BYTES) >> 4;
+                                    blo += kstep;
                                 }
                                 mma(d_tmem, hi_a, alo, blo, 1);
-                                mma(d_tmem, hi_a, alo + 2, blo + 1 * (2 * TF_KCORE_BYTES >> 4), 1);
-                                mma(d_tmem, hi_a, alo + 4, blo + 2 * (2 * TF_KCORE_BYTES >> 4), 1);
-                                mma(d_tmem, hi_a, alo + 6, blo + 3 * (2 * TF_KCORE_BYTES >> 4), 1);
+                                mma(d_tmem, hi_a, alo + 2, blo + kstep, 1);
+                                mma(d_tmem, hi_a, alo + 4, blo + 2 * kstep, 1);
+                                mma(d_tmem, hi_a, alo + 6, blo + 3 * kstep, 1);
                                 tc::umma_commit_2cta(ring_empty(slot));
                                 if (j == nk - 1) tc::umma_commit_2cta(acc_ready(x));
                             }
@@ -399,16 +433,17 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
 // Encoder + trunk + output head for B rays x (S-1) intervals: out [B (S-1), n_out] fp32 rows
 // (density | colour | segmentation) and the Gaussian means [B (S-1), 3] that nerf_head_composite takes as points.
 extern "C" int nerf_head_fwd_tc(const void* packed, const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
-                                float base_radius, int min_deg, int n_deg, int n_out, float* out, float* mean_out, void* stream) {
+                                float base_radius, int min_deg, int n_deg, int n_out, int log_softmax_seg, float* out, float* mean_out,
+                                void* stream) {
     if (!packed || !rays_o || !rays_d || !t || !out || !mean_out || B < 0 || S < 2) return NERF_ERR_BAD_ARG;
-    if (n_deg != 16 || n_out <= 0 || n_out > 64) return NERF_ERR_UNSUPPORTED;     // encoding_size = 32, 1+3+<=60 outputs
+    if (n_deg != 16 || n_out <= 0 || n_out > HT_OUT_N) return NERF_ERR_UNSUPPORTED;     // encoding_size = 32, 1+3+<=60 outputs
     if (B == 0) return NERF_OK;
     HeadTcLayout L; make_head_tc_layout(L);
     HeadTcArgs a{};
     a.stages = (const uint8_t*)packed; a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + L.vec_off);
-    for (int l = 0; l < HT_UNITS; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.unit_off[l] = L.unit_off[l]; }
+    for (int l = 0; l < HT_UNITS; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.kcore_bytes[l] = L.kcore_bytes[l]; a.unit_off[l] = L.unit_off[l]; }
     a.rays_o = rays_o; a.rays_d = rays_d; a.t = t; a.B = B; a.S = S; a.P = B * (int64_t)(S - 1); a.n_tiles = (int)((a.P + 127) / 128);
-    a.base_radius = base_radius; a.min_deg = min_deg; a.out = out; a.n_out = n_out; a.mean_out = mean_out;
+    a.base_radius = base_radius; a.min_deg = min_deg; a.out = out; a.n_out = n_out; a.mean_out = mean_out; a.log_softmax_seg = log_softmax_seg;
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
     static bool attr = false;
     if (!attr) { NERF_CUDA(cudaFuncSetAttribute(head_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM_BYTES)); attr = true; }

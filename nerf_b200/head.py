@@ -97,7 +97,7 @@ class HeadNeRF(nn.Module):
               "nerf_head_encode")
         return (mean.view(*batch, s - 1, 3), cov.view(*batch, s - 1, 3), feat.view(*batch, s - 1, 6 * n_deg))
 
-    def _fwd_tc(self, o, d, t):
+    def _fwd_tc(self, o, d, t, log_softmax_seg=False):
         """Encoder + trunk + output head on tcgen05 (csrc/head_tc.cu) -> (means [B,S-1,3], out [B,S-1,n_out])."""
         b, s = t.shape
         n_out = 1 + self.color_outputs + self.segmentation_outputs
@@ -107,7 +107,7 @@ class HeadNeRF(nn.Module):
         out = torch.empty(b, s - 1, n_out, device=t.device); mean = torch.empty(b, s - 1, 3, device=t.device)
         r = 1.0 / (math.sqrt(3) * self.focal_length)
         check(lib().nerf_head_fwd_tc(ptr(packed), ptr(o), ptr(d), ptr(t), b, s, r, -4, self.encoding_size // 2, n_out,
-                                     ptr(out), ptr(mean), stream()), "nerf_head_fwd_tc")
+                                     int(log_softmax_seg), ptr(out), ptr(mean), stream()), "nerf_head_fwd_tc")
         return mean, out
 
     def _trunk(self, feat2d):
@@ -143,7 +143,7 @@ class HeadNeRF(nn.Module):
         t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)
         s1 = num_samples - 1
         if self.precision == "bf16":
-            mean, out = self._fwd_tc(o, d, t)
+            mean, out = self._fwd_tc(o, d, t, log_softmax_seg=True)      # :662 fused into the output head's epilogue
             out = out.view(b * s1, -1)
         else:
             mean, _, feat = self.integrated_pe(o, d, t)
@@ -153,7 +153,8 @@ class HeadNeRF(nn.Module):
         img = torch.empty(b, 3, device=o.device); seg = torch.empty(b, self.segmentation_outputs, device=o.device)
         nz = ops._f32c(noise.reshape(b, s1)) if noise is not None else None
         check(lib().nerf_head_composite(ptr(out), out.shape[1], self.segmentation_outputs, ptr(mean.view(b, s1, 3).contiguous()),
-                                        ptr(nz), float(density_noise_std), b, s1, ptr(img), ptr(seg), None, stream()),
+                                        ptr(nz), float(density_noise_std), b, s1, ptr(img), ptr(seg), None,
+                                        int(self.precision == "bf16"), stream()),
               "nerf_head_composite")
         return img.unsqueeze(-2), seg.unsqueeze(-2)
 
