@@ -268,7 +268,7 @@ def run_ours(args):
 
         def k_fwd(i):
             _lib.check(L.nerf_g1_train_fwd_tc(P(z["packed"]), 3, 3, P(o), P(d), b, s, NEAR, FAR, P(ladder), None, None, 1, 1, 0,
-                                              6.0, 1, P(z["t"]), P(z["sigma"]), P(z["rgb"]), P(z["ws"]), z["n"], _lib.stream()), "fwd")
+                                              6.0, 1, None, P(z["t"]), P(z["sigma"]), P(z["rgb"]), P(z["ws"]), z["n"], _lib.stream()), "fwd")
 
         def k_bwd(stage):
             def f(i):

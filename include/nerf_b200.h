@@ -215,8 +215,11 @@ int nerf_tc_wgrad_debug(const void* dz, const void* xmain, const void* xenc, con
 
 /* bf16 training step of the G1 model = autograd of the loop body train_conditional_nerf.py:120-135
  * / example.ipynb cell 8 on tcgen05.  The caller owns one workspace of
- * nerf_g1_train_workspace_bytes(B, S) bytes shared by the forward and backward calls. */
-int64_t nerf_g1_train_workspace_bytes(int64_t B, int S);
+ * nerf_g1_train_workspace_bytes(B, S, Dx) bytes shared by the forward and backward calls.
+ * Conditional models (train_conditional_nerf.py:97-104, Dx = 3 + Sx): states_x [B, Sx] are per-ray
+ * constants, so their share of units 0 and 4 is added as a per-ray bias (one small fp32 GEMM per step)
+ * and their weight gradients come from per-ray sums of dz; Dd must be 3 (states_d: fp32 path). */
+int64_t nerf_g1_train_workspace_bytes(int64_t B, int S, int Dx);
 /* transposed bf16 weight stages (gamma folded) for the data-gradient MMAs */
 int64_t nerf_g1_packed_bwd_bytes(int Dx, int Dd);
 int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, void* packed_bwd, void* stream);
@@ -225,7 +228,7 @@ int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, void* packed_b
 int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
                          int64_t B, int S, float near_plane, float far_plane, const float* t_base,
                          const float* t_in, const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
-                         float normalize_position, int normalize_direction,
+                         float normalize_position, int normalize_direction, const float* states_x,
                          float* out_t, float* out_sigma, float* out_rgb,
                          void* workspace, int64_t workspace_bytes, void* stream);
 /* backward: d_sigma [B,S], d_rgb [B,S,3] (from nerf_composite_bwd) -> grads (flat fp32, state_dict

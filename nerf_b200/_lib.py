@@ -41,11 +41,11 @@ SIGNATURES = {
                                    c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_p]),
     "nerf_g1_mlp_tc_debug": (c_i, [c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_i, c_p, c_p, c_p, c_p, c_i, c_p]),
     "nerf_tc_wgrad_debug": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_p]),
-    "nerf_g1_train_workspace_bytes": (c_l, [c_l, c_i]),
+    "nerf_g1_train_workspace_bytes": (c_l, [c_l, c_i, c_i]),
     "nerf_g1_packed_bwd_bytes": (c_l, [c_i, c_i]),
     "nerf_g1_pack_weights_bwd": (c_i, [c_p, c_i, c_i, c_p, c_p]),
     "nerf_g1_train_fwd_tc": (c_i, [c_p, c_i, c_i, c_p, c_p, c_l, c_i, c_f, c_f, c_p, c_p, c_p, c_i, c_u64, c_l,
-                                   c_f, c_i, c_p, c_p, c_p, c_p, c_l, c_p]),
+                                   c_f, c_i, c_p, c_p, c_p, c_p, c_p, c_l, c_p]),
     "nerf_g1_train_bwd_tc": (c_i, [c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_l, c_i, c_p, c_p, c_l, c_i, c_p]),
     "nerf_head_encode": (c_i, [c_p, c_p, c_p, c_l, c_i, c_f, c_i, c_i, c_p, c_p, c_p, c_p]),
     "nerf_head_mlp_workspace_bytes": (c_l, [c_l]),

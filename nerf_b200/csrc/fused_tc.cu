@@ -177,6 +177,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 if (!TRAIN && a.dbg && a.dbg_layer == l) epilogue_unit<3, false>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 else if (l == 7) epilogue_unit<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 else if (l == 9) epilogue_unit<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (a.ray_bias && (l == 0 || l == 4))
+                    epilogue_unit<0, TRAIN, true>(a, l, taddr, act_addr, row, base + SM_VEC, st,
+                                                  a.ray_bias + ((size_t)(l ? 1 : 0) * a.B + (st.valid ? st.p / a.S : 0)) * 256);
                 else epilogue_unit<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
                 if (TRAIN) {                                         // normalised output of unit l (and the direction slab) -> HBM
@@ -201,7 +204,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
 // ------------------------------------------------------------------ host side ----
 static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaStream_t st, bool train = false) {
     PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
-    if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;          // conditional inputs: fp32 path for now
+    if (Dd != 3 || (Dx != 3 && !a.ray_bias)) return NERF_ERR_UNSUPPORTED;   // states_x need the per-ray bias; states_d: fp32 path
     for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.unit_off[l] = L.unit_off[l]; }
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
@@ -320,6 +323,7 @@ int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, 
                        uint64_t seed, int64_t ray_id_base, float norm, int normalize_dir,
                        float* out_t, float* out_sigma, float* out_rgb, uint8_t* ws, const TrainLayout& T, cudaStream_t st) {
     FusedArgs a{};
+    a.ray_bias = T.EXs ? reinterpret_cast<const float*>(ws + T.off_rb) : nullptr;
     a.rays_o = rays_o; a.rays_d = rays_d; a.B = B; a.S = S; a.P = T.P; a.n_tiles = T.n_tiles;
     a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
     a.near_plane = near_plane; a.far_plane = far_plane; a.norm = norm; a.normalize_dir = normalize_dir;

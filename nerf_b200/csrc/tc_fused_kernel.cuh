@@ -40,6 +40,7 @@ struct FusedArgs {
     // training forward (TRAIN = true): slab images of every unit's normalised output and of the two
     // encodings, plus (rstd, -mean*rstd) per point and unit, for the backward and wgrad kernels
     uint8_t* tr_act; uint8_t* tr_pex; uint8_t* tr_ped; float2* tr_stats; int64_t P_pad; int tr_tiles;
+    const float* ray_bias;                        // conditional inputs: [2 (units 0, 4)][B][256] fp32 per-ray bias, or null
     long long* prof;                              // NERF_TC_PROF: clock64 stamps of CTA 0, second work unit
     uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
 };
@@ -152,15 +153,21 @@ __device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float
 // MODE: 0 = plain unit, 1 = unit 7 (+ density head), 2 = unit 9 (+ colour head, no activation
 // store), 3 = debug dump of the normalised row.  Chunk loops are unrolled by two only (static
 // register double-buffer) to keep the kernel inside the instruction cache.
-template <int MODE, bool TRAIN>
+// RB (units 0 and 4 of a conditional model): the row's ray contributes a bias vector rb[256] (the states'
+// share of the unit, tc_layout.cuh), added to z in both passes.
+template <int MODE, bool TRAIN, bool RB = false>
 __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
-                                           uint32_t row, uint32_t vec_addr, const RowState& st) {
+                                           uint32_t row, uint32_t vec_addr, const RowState& st, const float* rb = nullptr) {
     uint32_t r0[32], r1[32];
     float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f), s3 = s2, q3 = q2;   // two chains each: the adds are latency-bound
     auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
             float2 z0 = f2(rc[j], rc[j + 1]), z1 = f2(rc[j + 2], rc[j + 3]);
+            if (RB) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(rb + ch * 32 + j));
+                z0 = __fadd2_rn(z0, make_float2(b.x, b.y)); z1 = __fadd2_rn(z1, make_float2(b.z, b.w));
+            }
             z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
             s2 = __fadd2_rn(s2, z0); s3 = __fadd2_rn(s3, z1);
             q2 = __ffma2_rn(z0, z0, q2); q3 = __ffma2_rn(z1, z1, q3);
@@ -189,8 +196,13 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
         uint32_t packed[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-            const float2 y0 = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, shift2);
-            const float2 y1 = __ffma2_rn(f2(rc[j + 2], rc[j + 3]), rstd2, shift2);
+            float2 c0 = shift2, c1 = shift2;
+            if (RB) {
+                const float4 b = __ldg(reinterpret_cast<const float4*>(rb + ch * 32 + j));
+                c0 = __ffma2_rn(make_float2(b.x, b.y), rstd2, shift2); c1 = __ffma2_rn(make_float2(b.z, b.w), rstd2, shift2);
+            }
+            const float2 y0 = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, c0);
+            const float2 y1 = __ffma2_rn(f2(rc[j + 2], rc[j + 3]), rstd2, c1);
             __nv_bfloat162 p0 = __hmax2(__float22bfloat162_rn(y0), shift_bf);
             __nv_bfloat162 p1 = __hmax2(__float22bfloat162_rn(y1), shift_bf);
             packed[j / 2] = *reinterpret_cast<uint32_t*>(&p0); packed[j / 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);

@@ -28,8 +28,14 @@
 #define TF_B_SBO 128
 #define TC_VEC_BYTES ((TC_VEC_FLOATS * 4 + 1023) & ~1023)
 
+// Conditional inputs (G2: states_x appended to the normalised position before the encoding, Dx = 3 + Sx):
+// the states are per-RAY constants, so their share of units 0 and 4, W[:, state columns] . PE(states), is a
+// per-ray bias vector [256].  The slab and the weight image keep the 60 position columns only; the state
+// weights travel as an fp32 section behind the vectors ([2 units][256][20 Sx]) for the per-ray bias GEMM.
 struct PackLayout {
     int Dx, Dd, EX, ED;
+    int EXs;                    // encoding columns of the states (20 per state), 0 for G1
+    int64_t state_w_off;        // byte offset of the fp32 state weights in the packed image
     int nk[10];                 // k-slabs (of 64) per unit
     int stage_begin[11];        // first 16 KB stage of each unit (2 stages per k-slab)
     int n_stages;
@@ -46,7 +52,8 @@ static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
     int64_t off[44];
     nerf_g1_param_layout(Dx, Dd, off);
     L.Dx = Dx; L.Dd = Dd; L.EX = 2 * NERF_PE_X_OCTAVES * Dx; L.ED = 2 * NERF_PE_D_OCTAVES * Dd;
-    const int nkx = (L.EX + 63) / 64, nkd = (L.ED + 63) / 64;
+    L.EXs = 2 * NERF_PE_X_OCTAVES * (Dx - 3);
+    const int nkx = (2 * NERF_PE_X_OCTAVES * 3 + 63) / 64, nkd = (L.ED + 63) / 64;   // the slab holds the position columns
     int s = 0;
     for (int l = 0; l < 10; ++l) {
         L.nk[l] = (l == 0) ? nkx : (l == 4 ? 4 + nkx : (l == 8 ? 4 + nkd : 4));
@@ -69,16 +76,20 @@ static inline int make_pack_layout(int Dx, int Dd, PackLayout& L) {
 
 __host__ __device__ static inline bool tc_unit_has_bias_block(int l) { return l != 0 && l != 4 && l != 8; }
 static inline int64_t tc_packed_vec_offset(const PackLayout& L) { return L.weight_bytes; }
-static inline int64_t tc_packed_total(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES; }
+static inline int64_t tc_packed_state_w_offset(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES; }
+static inline int64_t tc_packed_total(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES + ((2ll * 256 * L.EXs * 4 + 1023) & ~1023ll); }
 
 // ---- workspace of the bf16 training step (tc_train.cu): byte offsets, all 1024-aligned ----
 #define TC_GW_LD 336                   // dW' row: 256 hidden + 64 encoding + 16 x (column sum of dz = db')
 struct TrainLayout {
     int64_t P, P_pad; int n_tiles, tr_tiles;
     int64_t off_pex, off_ped, off_act, off_dz, off_stats, off_dh, off_gw, off_gh, off_hsum, total;
-    int64_t zero_begin, zero_bytes;    // [gw | gh | hsum]: accumulated with atomics, cleared every step
+    int64_t zero_begin, zero_bytes;    // [gw | gh | hsum | gs]: accumulated with atomics, cleared every step
+    // conditional inputs (EXs > 0): PE(states) [B][EXs], per-ray bias [2][B][256], per-ray sums of dz [2][B][256],
+    // state-weight gradients [2][256][EXs] (all fp32)
+    int EXs; int64_t off_pes, off_rb, off_rsum, off_gs;
 };
-static inline void make_train_layout(int64_t B, int S, TrainLayout& T) {
+static inline void make_train_layout(int64_t B, int S, TrainLayout& T, int Dx = 3) {
     auto up = [](int64_t x) { return (x + 1023) & ~(int64_t)1023; };
     T.P = B * S; T.n_tiles = (int)((T.P + 127) / 128); T.tr_tiles = (T.n_tiles + 1) & ~1; T.P_pad = (int64_t)T.tr_tiles * 128;
     int64_t o = 0;
@@ -91,6 +102,11 @@ static inline void make_train_layout(int64_t B, int S, TrainLayout& T) {
     T.off_gw = o; T.zero_begin = o; o += up(10ll * 256 * TC_GW_LD * 4);
     T.off_gh = o; o += up(2ll * 256 * 16 * 4);
     T.off_hsum = o; o += 1024;
+    T.EXs = 2 * NERF_PE_X_OCTAVES * (Dx - 3);
+    T.off_gs = o; o += up(2ll * 256 * T.EXs * 4);
     T.zero_bytes = o - T.zero_begin;
+    T.off_pes = o; o += up(B * (int64_t)T.EXs * 4);
+    T.off_rb = o; o += T.EXs ? up(2ll * B * 256 * 4) : 0;
+    T.off_rsum = o; o += T.EXs ? up(2ll * B * 256 * 4) : 0;
     T.total = o;
 }

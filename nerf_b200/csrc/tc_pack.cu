@@ -46,7 +46,8 @@ __global__ void pack_stage_kernel(const float* __restrict__ params, PackLayout L
             for (int j = 0; j < 8; ++j) {
                 const int k2 = (c - hid_cores) * 8 + j;   // index into the appended encoding columns
                 const int kcol = (l == 0 ? 0 : 256) + k2;
-                if (kcol < Kt) v[j] = W[(size_t)n * Kt + kcol];
+                const int n_enc = (l == 8) ? L.ED : 2 * NERF_PE_X_OCTAVES * 3;       // position columns only (states: per-ray bias)
+                if (k2 < n_enc) v[j] = W[(size_t)n * Kt + kcol];
                 else if (k2 >= nenc_cores * 8 - 64 + TC_ONES_COL && k2 < nenc_cores * 8 - 64 + TC_ONES_COL + 3) {   // the last slab's ones columns
                     float p3[3]; split_bias3(vec[TC_VEC_BIAS + l * 256 + n], p3); v[j] = p3[k2 - (nenc_cores * 8 - 64 + TC_ONES_COL)];
                 }
@@ -88,6 +89,15 @@ __global__ void pack_vectors_kernel(const float* __restrict__ params, PackLayout
     }
 }
 
+// fp32 copy of the state columns of units 0 and 4: sw[u][n][k] = W_u[n, (u ? 256 : 0) + 60 + k]
+__global__ void pack_state_weights_kernel(const float* __restrict__ params, PackLayout L, float* __restrict__ sw) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * 256 * L.EXs) return;
+    const int k = i % L.EXs, n = (i / L.EXs) & 255, u = i / (L.EXs * 256);
+    const int l = u ? 4 : 0;
+    sw[i] = params[L.off_W[l] + (size_t)n * L.Kt[l] + (u ? 256 : 0) + 2 * NERF_PE_X_OCTAVES * 3 + k];
+}
+
 extern "C" int64_t nerf_g1_packed_bytes(int Dx, int Dd) {
     PackLayout L;
     if (make_pack_layout(Dx, Dd, L) != NERF_OK) return NERF_ERR_BAD_ARG;
@@ -107,5 +117,10 @@ extern "C" int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* p
     for (int l = 0; l < 10; ++l) max_hk = L.half_kcores[l] > max_hk ? L.half_kcores[l] : max_hk;
     pack_stage_kernel<<<dim3((2 * max_hk * 128 + 255) / 256, 10), 256, 0, st>>>(params, L, vec, (uint8_t*)packed);
     NERF_CUDA_CHECK_LAUNCH();
+    if (L.EXs) {
+        pack_state_weights_kernel<<<(2 * 256 * L.EXs + 255) / 256, 256, 0, st>>>(
+            params, L, reinterpret_cast<float*>((uint8_t*)packed + tc_packed_state_w_offset(L)));
+        NERF_CUDA_CHECK_LAUNCH();
+    }
     return NERF_OK;
 }

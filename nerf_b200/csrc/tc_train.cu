@@ -51,10 +51,55 @@ extern "C" int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, voi
     return NERF_OK;
 }
 
-extern "C" int64_t nerf_g1_train_workspace_bytes(int64_t B, int S) {
-    if (B <= 0 || S <= 0) return NERF_ERR_BAD_ARG;
-    TrainLayout T; make_train_layout(B, S, T);
+extern "C" int64_t nerf_g1_train_workspace_bytes(int64_t B, int S, int Dx) {
+    if (B <= 0 || S <= 0 || Dx < 3 || Dx > 16) return NERF_ERR_BAD_ARG;
+    TrainLayout T; make_train_layout(B, S, T, Dx);
     return T.total;
+}
+
+// ---- conditional inputs: the states' share of units 0 and 4 as a per-ray bias (tc_layout.cuh) ----
+// pes[ray][c*20 + j] = sin(pi 2^j s_c), [c*20 + 10 + j] = cos(pi 2^j s_c): the layout of nerf_encode_g1 for c >= 3
+__global__ void pe_states_kernel(const float* __restrict__ states, int64_t B, int Sx, float* __restrict__ pes) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * Sx * NERF_PE_X_OCTAVES) return;
+    const int j = (int)(i % NERF_PE_X_OCTAVES); const int64_t rc = i / NERF_PE_X_OCTAVES;
+    const int c = (int)(rc % Sx); const int64_t ray = rc / Sx;
+    float s, co; sincospif(ldexpf(states[ray * Sx + c], j), &s, &co);
+    float* o = pes + ray * (2 * NERF_PE_X_OCTAVES * Sx) + c * 2 * NERF_PE_X_OCTAVES;
+    o[j] = s; o[NERF_PE_X_OCTAVES + j] = co;
+}
+// rb[u][ray][n] = sum_k sw[u][n][k] pes[ray][k]   (block = ray, thread = n)
+__global__ void __launch_bounds__(256) ray_bias_kernel(const float* __restrict__ sw, const float* __restrict__ pes, int64_t B, int EXs,
+                                                      float* __restrict__ rb) {
+    __shared__ float pe_s[2 * NERF_PE_X_OCTAVES * 13];
+    const int64_t ray = blockIdx.x; const int u = blockIdx.y, n = threadIdx.x;
+    for (int k = threadIdx.x; k < EXs; k += 256) pe_s[k] = pes[ray * EXs + k];
+    __syncthreads();
+    const float* w = sw + ((size_t)u * 256 + n) * EXs;
+    float acc = 0.f;
+    for (int k = 0; k < EXs; ++k) acc = fmaf(w[k], pe_s[k], acc);
+    rb[((size_t)u * B + ray) * 256 + n] = acc;
+}
+// rsum[u][ray][n] = sum over the ray's S points of dz_l[p][n], l = 0 (u = 0) or 4 (u = 1), read from the slab image
+__global__ void __launch_bounds__(256) dz_ray_sum_kernel(const uint8_t* __restrict__ dz, int tr_tiles, int64_t B, int S, float* __restrict__ rsum) {
+    const int64_t ray = blockIdx.x; const int u = blockIdx.y, n = threadIdx.x;
+    const uint8_t* img = dz + (size_t)(u ? 4 : 0) * tr_tiles * (4 * TC_SLAB_BYTES);
+    float acc = 0.f;
+    for (int k = 0; k < S; ++k) {
+        const int64_t p = ray * S + k; const int64_t tile = p >> 7; const uint32_t row = (uint32_t)(p & 127);
+        const uint8_t* q = img + (size_t)tile * (4 * TC_SLAB_BYTES) + (size_t)(n >> 6) * TC_SLAB_BYTES + tc::sw128_offset(row, (n & 63) >> 3) + (n & 7) * 2;
+        acc += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(q));
+    }
+    rsum[((size_t)u * B + ray) * 256 + n] = acc;
+}
+// gs[u][n][k] += sum_ray rsum[u][ray][n] pes[ray][k]   (grid: k, u, ray chunk; thread = n)
+__global__ void __launch_bounds__(256) state_grad_kernel(const float* __restrict__ rsum, const float* __restrict__ pes, int64_t B, int EXs,
+                                                        float* __restrict__ gs) {
+    const int k = blockIdx.x, u = blockIdx.y, n = threadIdx.x;
+    const int64_t r0 = (int64_t)blockIdx.z * 256, r1 = r0 + 256 < B ? r0 + 256 : B;
+    float acc = 0.f;
+    for (int64_t ray = r0; ray < r1; ++ray) acc = fmaf(rsum[((size_t)u * B + ray) * 256 + n], pes[ray * EXs + k], acc);
+    atomicAdd(gs + ((size_t)u * 256 + n) * EXs + k, acc);
 }
 
 // ---- unfold: gradients of folded parameters -> gradients of the state_dict tensors ----
@@ -63,8 +108,10 @@ extern "C" int64_t nerf_g1_train_workspace_bytes(int64_t B, int S) {
 // hsum [4]:          sum_p (d_sigma, d_rgb)
 //   dW_l[i,k] = G_l[i,k] gamma_{l-1}[k] + c_l[i] beta_{l-1}[k]  (hidden k);  = G_l[i, 256+k2]  (encoding)
 //   db_l = c_l;  heads: dw[k] = gamma[k] H[k] + beta[k] s,  db = s
+//   conditional inputs: the state columns of units 0 and 4 come from gs (state_grad_kernel)
 __global__ void unfold_weights_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
-                                      const float* __restrict__ gh, const float* __restrict__ hsum, float* __restrict__ grads) {
+                                      const float* __restrict__ gh, const float* __restrict__ hsum, const float* __restrict__ gs,
+                                      float* __restrict__ grads) {
     const int l = blockIdx.y;
     if (l < 10) {
         const int Kt = L.Kt[l], hid = (l == 0) ? 0 : 256;
@@ -75,6 +122,7 @@ __global__ void unfold_weights_kernel(const float* __restrict__ params, PackLayo
             if (k == Kt) { grads[L.off_b[l] + i] = c; continue; }
             float v;
             if (k < hid) v = fmaf(G[(size_t)i * TC_GW_LD + k], params[L.off_gamma[l - 1] + k], c * params[L.off_beta[l - 1] + k]);
+            else if (l != 8 && k - hid >= 2 * NERF_PE_X_OCTAVES * 3) v = gs[((size_t)(l ? 1 : 0) * 256 + i) * L.EXs + (k - hid - 2 * NERF_PE_X_OCTAVES * 3)];
             else v = G[(size_t)i * TC_GW_LD + 256 + (k - hid)];
             grads[L.off_W[l] + (size_t)i * Kt + k] = v;
         }
@@ -170,12 +218,27 @@ static int launch_bwd(BwdArgs& a, cudaStream_t st) {
 extern "C" int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
                                     int64_t B, int S, float near_plane, float far_plane, const float* t_base,
                                     const float* t_in, const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
-                                    float normalize_position, int normalize_direction,
+                                    float normalize_position, int normalize_direction, const float* states_x,
                                     float* out_t, float* out_sigma, float* out_rgb,
                                     void* workspace, int64_t workspace_bytes, void* stream) {
     if (!packed || !rays_o || !rays_d || !out_t || !out_sigma || !out_rgb || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
-    TrainLayout T; make_train_layout(B, S, T);
+    if (Dx < 3 || Dx > 16 || (Dx > 3 && !states_x)) return NERF_ERR_BAD_ARG;
+    if (Dd != 3) return NERF_ERR_UNSUPPORTED;
+    PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
+    TrainLayout T; make_train_layout(B, S, T, Dx);
     if (!workspace || workspace_bytes < T.total) return NERF_ERR_WORKSPACE;
+    if (T.EXs) {                                                  // states -> PE -> per-ray bias of units 0 and 4
+        cudaStream_t st = (cudaStream_t)stream;
+        uint8_t* ws = (uint8_t*)workspace;
+        float* pes = reinterpret_cast<float*>(ws + T.off_pes);
+        const int64_t n = B * (Dx - 3) * NERF_PE_X_OCTAVES;
+        pe_states_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(states_x, B, Dx - 3, pes);
+        NERF_CUDA_CHECK_LAUNCH();
+        ray_bias_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(
+            reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_state_w_offset(L)), pes, B, T.EXs,
+            reinterpret_cast<float*>(ws + T.off_rb));
+        NERF_CUDA_CHECK_LAUNCH();
+    }
     return launch_fused_train(packed, Dx, Dd, rays_o, rays_d, B, S, near_plane, far_plane, t_base, t_in, u, jitter, seed,
                               ray_id_base, normalize_position, normalize_direction, out_t, out_sigma, out_rgb,
                               (uint8_t*)workspace, T, (cudaStream_t)stream);
@@ -187,9 +250,9 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
                                     const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
                                     void* workspace, int64_t workspace_bytes, int stage, void* stream) {
     if (!packed || !packed_bwd || !params || !d_sigma || !d_rgb || !grads || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
-    if (Dx != 3 || Dd != 3) return NERF_ERR_UNSUPPORTED;
+    if (Dd != 3) return NERF_ERR_UNSUPPORTED;
     PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
-    TrainLayout T; make_train_layout(B, S, T);
+    TrainLayout T; make_train_layout(B, S, T, Dx);
     if (!workspace || workspace_bytes < T.total) return NERF_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t* ws = (uint8_t*)workspace;
@@ -212,7 +275,16 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     const float* gw = reinterpret_cast<const float*>(ws + T.off_gw);
     const float* gh = reinterpret_cast<const float*>(ws + T.off_gh);
     const float* hsum = reinterpret_cast<const float*>(ws + T.off_hsum);
-    unfold_weights_kernel<<<dim3(80, 11), 256, 0, st>>>(params, L, gw, gh, hsum, grads);
+    const float* gs = reinterpret_cast<const float*>(ws + T.off_gs);
+    if (T.EXs) {                                                  // weight gradients of the state columns (forward must have run on this workspace)
+        float* rsum = reinterpret_cast<float*>(ws + T.off_rsum);
+        dz_ray_sum_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(ws + T.off_dz, T.tr_tiles, B, S, rsum);
+        NERF_CUDA_CHECK_LAUNCH();
+        state_grad_kernel<<<dim3(T.EXs, 2, (unsigned)((B + 255) / 256)), 256, 0, st>>>(
+            rsum, reinterpret_cast<const float*>(ws + T.off_pes), B, T.EXs, reinterpret_cast<float*>(ws + T.off_gs));
+        NERF_CUDA_CHECK_LAUNCH();
+    }
+    unfold_weights_kernel<<<dim3(80, 11), 256, 0, st>>>(params, L, gw, gh, hsum, gs, grads);
     NERF_CUDA_CHECK_LAUNCH();
     unfold_affine_kernel<<<10, 1024, 0, st>>>(params, L, gw, gh, hsum, grads);
     NERF_CUDA_CHECK_LAUNCH();

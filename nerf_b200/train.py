@@ -41,20 +41,21 @@ class Trainer:
 
     # ------------------------------------------------------------ bf16 (tcgen05) step ------
     def _tc_buffers(self, b, s, dev):
+        dx = self.model.density_inputs
         if self._tc is None or self._tc["key"] != (b, s):
             L = lib()
-            n = L.nerf_g1_train_workspace_bytes(b, s)
+            n = L.nerf_g1_train_workspace_bytes(b, s, dx)
             e = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
             self._tc = {
                 "key": (b, s), "n": n, "ws": torch.empty(n, dtype=torch.uint8, device=dev),
-                "packed": torch.empty(L.nerf_g1_packed_bytes(3, 3), dtype=torch.uint8, device=dev),
-                "packed_bwd": torch.empty(L.nerf_g1_packed_bwd_bytes(3, 3), dtype=torch.uint8, device=dev),
+                "packed": torch.empty(L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev),
+                "packed_bwd": torch.empty(L.nerf_g1_packed_bwd_bytes(dx, 3), dtype=torch.uint8, device=dev),
                 "t": e(b, s), "sigma": e(b, s), "rgb": e(b, s, 3), "d_sigma": e(b, s), "d_rgb": e(b, s, 3),
                 "pixels": e(b, 3), "g_pixels": e(b, 3), "loss": e(1),
             }
         return self._tc
 
-    def _step_bf16(self, rays_o, rays_d, target, u, noise, apply_update):
+    def _step_bf16(self, rays_o, rays_d, target, u, noise, apply_update, states_x=None):
         """sample+encode+MLP forward (one tcgen05 kernel, activations kept as bf16 slab images) ->
         noise -> composite -> MSE -> composite backward -> tcgen05 data-gradient kernel ->
         tcgen05 weight-gradient GEMM -> unfold -> [all-reduce] -> Adam.  fp32 master weights."""
@@ -66,15 +67,17 @@ class Trainer:
         z = self._tc_buffers(b, s, dev)
         st = stream()
         ray_base = self.rays_seen * self.world + self.rank * b
-        check(L.nerf_g1_pack_weights(ptr(flat), 3, 3, ptr(z["packed"]), st), "nerf_g1_pack_weights")
-        check(L.nerf_g1_pack_weights_bwd(ptr(flat), 3, 3, ptr(z["packed_bwd"]), st), "nerf_g1_pack_weights_bwd")
-        check(L.nerf_g1_train_fwd_tc(ptr(z["packed"]), 3, 3, ptr(rays_o), ptr(rays_d), b, s, self.near, self.far,
+        dx = m.density_inputs
+        sx = ops._f32c(states_x) if dx > 3 else None
+        check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(z["packed"]), st), "nerf_g1_pack_weights")
+        check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(z["packed_bwd"]), st), "nerf_g1_pack_weights_bwd")
+        check(L.nerf_g1_train_fwd_tc(ptr(z["packed"]), dx, 3, ptr(rays_o), ptr(rays_d), b, s, self.near, self.far,
                                      ptr(m._ladder(self.near, self.far, s, dev)), None, ptr(u),
                                      int(self.jitter and u is None), self.seed, ray_base,
-                                     float(m.normalize_position), int(m.normalize_direction),
+                                     float(m.normalize_position), int(m.normalize_direction), ptr(sx),
                                      ptr(z["t"]), ptr(z["sigma"]), ptr(z["rgb"]), ptr(z["ws"]), z["n"], st),
               "nerf_g1_train_fwd_tc")
-        launches = 4
+        launches = 4 + (5 if dx > 3 else 0)     # conditional: state weights, PE(states), ray bias; dz ray sums, state gradients
         if noise is not None:
             z["sigma"] += noise.view(b, s)
         elif self.noise_std != 0.0:
@@ -86,7 +89,7 @@ class Trainer:
                                    ptr(z["g_pixels"]), None, None, None, ptr(z["pixels"]), None, None,
                                    ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
               "nerf_composite_bwd")
-        check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), 3, 3, ptr(z["d_sigma"]),
+        check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), dx, 3, ptr(z["d_sigma"]),
                                      ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
               "nerf_g1_train_bwd_tc")
         launches += 3 + 4                                           # + bwd, wgrad, 2 unfold (memset not counted)
@@ -107,9 +110,10 @@ class Trainer:
         """One optimisation step on a ray batch resident on the device.  Returns the loss
         (1-element device tensor; reading it is the caller's device->host sync)."""
         m = self.model
-        if (self.precision == ops.PREC_BF16 and states_x is None and states_d is None
-                and m.density_inputs == 3 and m.color_inputs == 3 and self.num_samples >= 32):
-            return self._step_bf16(rays_o.contiguous(), rays_d.contiguous(), target.contiguous(), u, noise, apply_update)
+        if (self.precision == ops.PREC_BF16 and states_d is None and m.color_inputs == 3 and self.num_samples >= 32
+                and (m.density_inputs == 3 or states_x is not None)):
+            return self._step_bf16(rays_o.contiguous(), rays_d.contiguous(), target.contiguous(), u, noise, apply_update,
+                                   states_x=states_x)
         flat = m.flat_parameters()
         b, s = rays_o.shape[0], self.num_samples
         dx, dd = m.density_inputs, m.color_inputs

@@ -32,7 +32,7 @@ def main():
     ladder = m._ladder(2.0, 6.0, s, dev)
     calls = {
         "pack": lambda: (L.nerf_g1_pack_weights(P(flat), 3, 3, P(z["packed"]), st()), L.nerf_g1_pack_weights_bwd(P(flat), 3, 3, P(z["packed_bwd"]), st())),
-        "fwd": lambda: L.nerf_g1_train_fwd_tc(P(z["packed"]), 3, 3, P(o), P(d), b, s, 2.0, 6.0, P(ladder), None, None, 1, 1, 0, 6.0, 1,
+        "fwd": lambda: L.nerf_g1_train_fwd_tc(P(z["packed"]), 3, 3, P(o), P(d), b, s, 2.0, 6.0, P(ladder), None, None, 1, 1, 0, 6.0, 1, None,
                                                P(z["t"]), P(z["sigma"]), P(z["rgb"]), P(z["ws"]), z["n"], st()),
         "composite_fwd": lambda: L.nerf_composite_fwd(P(z["sigma"]), P(z["rgb"]), None, P(o), P(d), P(z["t"]), b, s, P(z["pixels"]), None, None, None, st()),
         "mse": lambda: L.nerf_mse_loss(P(z["pixels"]), P(tgt), b * 3, P(z["loss"]), P(z["g_pixels"]), st()),
