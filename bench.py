@@ -385,11 +385,30 @@ def run_ours(args):
     headb_rps = hbh * hbh / (float(np.mean(ms_hb)) * 1e-3)
     headb_tflops = headb_rps * (SAMPLES - 1) * 601_088 / 1e12
 
+    # ---- C4 / D4: the same step with latent-coded inputs (8 scenes, states_x in [-1,1]^4 => density_inputs 7) ----
+    c4_ms = None
+    if args.precision == "bf16":
+        torch.manual_seed(5)
+        cm = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").to(dev)
+        ctr = Trainer(cm, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=4321)
+        g4 = torch.Generator().manual_seed(4)
+        scenes = torch.rand(8, 4, generator=g4) * 2 - 1
+        c4_pool = [scenes[torch.randint(0, 8, (RAYS,), generator=g4)].to(dev) for _ in range(n_pool)]
+
+        def step_c4(i):
+            o_, d_, tgt_ = pool_d[i % n_pool]
+            return ctr.step(o_, d_, tgt_, states_x=c4_pool[i % n_pool])
+        for i in range(3):
+            step_c4(i)
+        barrier()
+        c4_ms = float(np.sum(timed_steps(step_c4, min(K, 50), flush))) / min(K, 50)
+
     # max over ranks of the timed totals
     if world > 1:
-        tt = torch.tensor([total_ms, total_e2e], device=dev, dtype=torch.float64)
+        tt = torch.tensor([total_ms, total_e2e, c4_ms or 0.0], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        total_ms, total_e2e = tt.tolist()
+        total_ms, total_e2e, c4_max = tt.tolist()
+        c4_ms = c4_max if c4_ms is not None else None
     value = world * RAYS * K / (total_ms * 1e-3)
     e2e = world * RAYS * K / (total_e2e * 1e-3)
 
@@ -420,6 +439,9 @@ def run_ours(args):
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
             "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},
+            "train_c4": None if c4_ms is None else {
+                "value": world * RAYS / (c4_ms * 1e-3), "unit": "rays/s", "ms_per_step": c4_ms,
+                "workload": "conditional train step (8 scenes, 4 latents per ray: block_0.0.weight [256,140]), 4096 rays x 64 samples per GPU"},
             "render_d3": d3,
             "kernels": kernels,
             "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",

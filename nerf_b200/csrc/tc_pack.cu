@@ -89,11 +89,12 @@ __global__ void pack_vectors_kernel(const float* __restrict__ params, PackLayout
     }
 }
 
-// fp32 copy of the state columns of units 0 and 4: sw[u][n][k] = W_u[n, (u ? 256 : 0) + 60 + k]
+// fp32 copy of the state columns of units 0 and 4, transposed so that the per-ray bias GEMM reads it coalesced:
+// sw[u][k][n] = W_u[n, (u ? 256 : 0) + 60 + k]
 __global__ void pack_state_weights_kernel(const float* __restrict__ params, PackLayout L, float* __restrict__ sw) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= 2 * 256 * L.EXs) return;
-    const int k = i % L.EXs, n = (i / L.EXs) & 255, u = i / (L.EXs * 256);
+    const int n = i & 255, k = (i >> 8) % L.EXs, u = i / (L.EXs * 256);
     const int l = u ? 4 : 0;
     sw[i] = params[L.off_W[l] + (size_t)n * L.Kt[l] + (u ? 256 : 0) + 2 * NERF_PE_X_OCTAVES * 3 + k];
 }

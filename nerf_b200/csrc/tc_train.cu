@@ -68,40 +68,64 @@ __global__ void pe_states_kernel(const float* __restrict__ states, int64_t B, in
     float* o = pes + ray * (2 * NERF_PE_X_OCTAVES * Sx) + c * 2 * NERF_PE_X_OCTAVES;
     o[j] = s; o[NERF_PE_X_OCTAVES + j] = co;
 }
-// rb[u][ray][n] = sum_k sw[u][n][k] pes[ray][k]   (block = ray, thread = n)
+// rb[u][ray][n] = sum_k sw[u][k][n] pes[ray][k]   (block = ray, thread = n)
 __global__ void __launch_bounds__(256) ray_bias_kernel(const float* __restrict__ sw, const float* __restrict__ pes, int64_t B, int EXs,
                                                       float* __restrict__ rb) {
     __shared__ float pe_s[2 * NERF_PE_X_OCTAVES * 13];
     const int64_t ray = blockIdx.x; const int u = blockIdx.y, n = threadIdx.x;
     for (int k = threadIdx.x; k < EXs; k += 256) pe_s[k] = pes[ray * EXs + k];
     __syncthreads();
-    const float* w = sw + ((size_t)u * 256 + n) * EXs;
+    const float* w = sw + (size_t)u * EXs * 256 + n;
     float acc = 0.f;
-    for (int k = 0; k < EXs; ++k) acc = fmaf(w[k], pe_s[k], acc);
+    for (int k = 0; k < EXs; ++k) acc = fmaf(w[(size_t)k * 256], pe_s[k], acc);
     rb[((size_t)u * B + ray) * 256 + n] = acc;
 }
-// rsum[u][ray][n] = sum over the ray's S points of dz_l[p][n], l = 0 (u = 0) or 4 (u = 1), read from the slab image
+// rsum[u][ray][n] = sum over the ray's S points of dz_l[p][n], l = 0 (u = 0) or 4 (u = 1), read from the slab image.
+// Block = ray; thread = (point group pg of 8, 16-byte chunk c of the row's 32): 128-byte segments per warp-load.
 __global__ void __launch_bounds__(256) dz_ray_sum_kernel(const uint8_t* __restrict__ dz, int tr_tiles, int64_t B, int S, float* __restrict__ rsum) {
-    const int64_t ray = blockIdx.x; const int u = blockIdx.y, n = threadIdx.x;
+    __shared__ float part[8][256];
+    const int64_t ray = blockIdx.x; const int u = blockIdx.y;
+    const int pg = threadIdx.x >> 5, c = threadIdx.x & 31;
     const uint8_t* img = dz + (size_t)(u ? 4 : 0) * tr_tiles * (4 * TC_SLAB_BYTES);
-    float acc = 0.f;
-    for (int k = 0; k < S; ++k) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int k = pg; k < S; k += 8) {
         const int64_t p = ray * S + k; const int64_t tile = p >> 7; const uint32_t row = (uint32_t)(p & 127);
-        const uint8_t* q = img + (size_t)tile * (4 * TC_SLAB_BYTES) + (size_t)(n >> 6) * TC_SLAB_BYTES + tc::sw128_offset(row, (n & 63) >> 3) + (n & 7) * 2;
-        acc += __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(q));
+        const uint4 v = *reinterpret_cast<const uint4*>(img + (size_t)tile * (4 * TC_SLAB_BYTES) + (size_t)(c >> 3) * TC_SLAB_BYTES + tc::sw128_offset(row, c & 7));
+        acc[0] += bf_lo(v.x); acc[1] += bf_hi(v.x); acc[2] += bf_lo(v.y); acc[3] += bf_hi(v.y);
+        acc[4] += bf_lo(v.z); acc[5] += bf_hi(v.z); acc[6] += bf_lo(v.w); acc[7] += bf_hi(v.w);
     }
-    rsum[((size_t)u * B + ray) * 256 + n] = acc;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) part[pg][c * 8 + j] = acc[j];
+    __syncthreads();
+    const int n = threadIdx.x;
+    float t = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) t += part[g][n];
+    rsum[((size_t)u * B + ray) * 256 + n] = t;
 }
-// gs[u][n][k] += sum_ray rsum[u][ray][n] pes[ray][k]   (grid: k, u, ray chunk; thread = n)
+// gs[u][n][k] += sum_ray rsum[u][ray][n] pes[ray][k]: block = (chunk of 64 rays, u), thread = n holding the EXs
+// partial sums of its output feature in registers (one coalesced load + EXs FMAs per ray), EXs <= 20 * 13
+template <int KC>
 __global__ void __launch_bounds__(256) state_grad_kernel(const float* __restrict__ rsum, const float* __restrict__ pes, int64_t B, int EXs,
                                                         float* __restrict__ gs) {
-    const int k = blockIdx.x, u = blockIdx.y, n = threadIdx.x;
-    const int64_t r0 = (int64_t)blockIdx.z * 256, r1 = r0 + 256 < B ? r0 + 256 : B;
-    float acc = 0.f;
-    for (int64_t ray = r0; ray < r1; ++ray) acc = fmaf(rsum[((size_t)u * B + ray) * 256 + n], pes[ray * EXs + k], acc);
-    atomicAdd(gs + ((size_t)u * 256 + n) * EXs + k, acc);
+    __shared__ float pe_s[64][KC];
+    const int u = blockIdx.y, n = threadIdx.x, k0 = blockIdx.z * KC;
+    const int64_t r0 = (int64_t)blockIdx.x * 64; const int nr = (int)(B - r0 < 64 ? B - r0 : 64);
+    for (int i = threadIdx.x; i < nr * KC; i += 256) { const int r = i / KC, k = i % KC; pe_s[r][k] = k0 + k < EXs ? pes[(r0 + r) * EXs + k0 + k] : 0.f; }
+    __syncthreads();
+    float acc[KC];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) acc[k] = 0.f;
+    for (int r = 0; r < nr; ++r) {
+        const float v = rsum[((size_t)u * B + r0 + r) * 256 + n];
+#pragma unroll
+        for (int k = 0; k < KC; ++k) acc[k] = fmaf(v, pe_s[r][k], acc[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k) if (k0 + k < EXs) atomicAdd(gs + ((size_t)u * 256 + n) * EXs + k0 + k, acc[k]);
 }
-
 // ---- unfold: gradients of folded parameters -> gradients of the state_dict tensors ----
 // gw [10][256][336]: G_l = dL/dW'_l (cols 0..255 hidden, 256..319 encoding), col 320 = c_l = dL/db'_l
 // gh [2][256][16]:   gh[0][k][0] = sum_p d_sigma n_7[k];  gh[1][k][1+c] = sum_p d_rgb_c n_9[k]
@@ -280,7 +304,7 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
         float* rsum = reinterpret_cast<float*>(ws + T.off_rsum);
         dz_ray_sum_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(ws + T.off_dz, T.tr_tiles, B, S, rsum);
         NERF_CUDA_CHECK_LAUNCH();
-        state_grad_kernel<<<dim3(T.EXs, 2, (unsigned)((B + 255) / 256)), 256, 0, st>>>(
+        state_grad_kernel<40><<<dim3((unsigned)((B + 63) / 64), 2, (T.EXs + 39) / 40), 256, 0, st>>>(
             rsum, reinterpret_cast<const float*>(ws + T.off_pes), B, T.EXs, reinterpret_cast<float*>(ws + T.off_gs));
         NERF_CUDA_CHECK_LAUNCH();
     }
