@@ -157,6 +157,7 @@ extern "C" int nerf_composite_fwd(const float* sigma, const float* rgb, const fl
                                   const float* rays_o, const float* rays_d, const float* t,
                                   int64_t B, int S, float* pixels, float* depth, float* acc,
                                   float* weights, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
     if (!sigma || B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
     if (!points && (!rays_o || !rays_d || !t)) return NERF_ERR_BAD_ARG;
     if (depth && !t) return NERF_ERR_BAD_ARG;
@@ -181,6 +182,7 @@ extern "C" int nerf_composite_bwd(const float* sigma, const float* rgb, const fl
                                   const float* g_acc, const float* g_weights,
                                   const float* saved_pixels, const float* saved_depth, const float* saved_acc,
                                   float* d_sigma, float* d_rgb, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
     if (!sigma || !rgb || !d_sigma || !d_rgb || B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
     if (!points && (!rays_o || !rays_d || !t)) return NERF_ERR_BAD_ARG;
     if (g_depth && !t) return NERF_ERR_BAD_ARG;

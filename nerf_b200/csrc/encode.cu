@@ -67,6 +67,7 @@ extern "C" int nerf_encode_g1(const float* rays_o, const float* rays_d, const fl
                               const float* states_x, int Sx, const float* states_d, int Sd,
                               int64_t B, int S, float normalize_position, int normalize_direction,
                               float* ex, float* ed, float* points_out, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
     if (!rays_o || !rays_d || B < 0 || S <= 0 || Sx < 0 || Sd < 0) return NERF_ERR_BAD_ARG;
     if ((Sx > 0 && !states_x) || (Sd > 0 && !states_d)) return NERF_ERR_BAD_ARG;
     if ((ex || points_out) && !t) return NERF_ERR_BAD_ARG;
@@ -158,6 +159,7 @@ __global__ void __launch_bounds__(128) sample_pdf_merge_kernel(
 
 extern "C" int nerf_sample_pdf_merge(const float* t, const float* weights, int S, int n_fine,
                                      const float* u_fine, int64_t B, float* t_out, void* stream) {
+    if (B == 0 && S >= 3 && n_fine >= 1) return NERF_OK;
     if (!t || !weights || !t_out || S < 3 || S > PDF_MAX_S || n_fine < 1 || n_fine > PDF_MAX_F || B < 0) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
     sample_pdf_merge_kernel<<<(unsigned)((B + 3) / 4), 128, 0, (cudaStream_t)stream>>>(t, weights, S, n_fine, u_fine, B, t_out);

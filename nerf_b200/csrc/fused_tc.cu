@@ -271,9 +271,9 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                                     void* workspace, int64_t workspace_bytes, void* stream) {
     if (!packed || B < 0 || S < 32 || S > 4096) return (S > 0 && S < 32) ? NERF_ERR_UNSUPPORTED : NERF_ERR_BAD_ARG;
     if (!rays_o != !rays_d) return NERF_ERR_BAD_ARG;
+    if (B == 0) return NERF_OK;                                   // zero rays: nothing to do (empty tensors carry null pointers)
     if (!rays_o && (!cam_o || !cam_r || n_cams <= 0 || H <= 0 || W <= 0 || ray_begin < 0 ||
                     ray_begin + B > (int64_t)n_cams * H * W)) return NERF_ERR_BAD_ARG;
-    if (B == 0) return NERF_OK;
     if (!workspace || workspace_bytes < nerf_g1_render_workspace_bytes(B, S)) return NERF_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t P = B * S;

@@ -56,6 +56,7 @@ __global__ void head_encode_kernel(const float* __restrict__ rays_o, const float
 extern "C" int nerf_head_encode(const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
                                 float base_radius, int min_deg, int n_deg, float* mean_out, float* cov_out,
                                 float* feat_out, void* stream) {
+    if (B == 0 && S >= 2 && n_deg > 0) return NERF_OK;
     if (!rays_o || !rays_d || !t || !feat_out || B < 0 || S < 2 || n_deg <= 0 || n_deg > 32) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
     const int64_t n = B * (int64_t)(S - 1) * n_deg;
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(256) head_composite_kernel(
 extern "C" int nerf_head_composite(const float* out, int n_out, int n_seg, const float* points, const float* noise,
                                    float noise_std, int64_t B, int S, float* pixels, float* seg_out, float* weights,
                                    int seg_is_log_softmax, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
     if (!out || !points || B < 0 || S <= 0 || n_seg < 0 || n_seg > 64 || n_out != 4 + n_seg) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
     int64_t blocks = (B + 7) / 8, cap = (int64_t)nerf_num_sms() * 32;

@@ -435,6 +435,7 @@ __global__ void __launch_bounds__(HT_THREADS, 1) head_tc_kernel(const HeadTcArgs
 extern "C" int nerf_head_fwd_tc(const void* packed, const float* rays_o, const float* rays_d, const float* t, int64_t B, int S,
                                 float base_radius, int min_deg, int n_deg, int n_out, int log_softmax_seg, float* out, float* mean_out,
                                 void* stream) {
+    if (B == 0 && packed && S >= 2) return NERF_OK;
     if (!packed || !rays_o || !rays_d || !t || !out || !mean_out || B < 0 || S < 2) return NERF_ERR_BAD_ARG;
     if (n_deg != 16 || n_out <= 0 || n_out > HT_OUT_N) return NERF_ERR_UNSUPPORTED;     // encoding_size = 32, 1+3+<=60 outputs
     if (B == 0) return NERF_OK;

@@ -10,6 +10,7 @@ extern "C" int nerf_g1_mlp_fwd(const float* params, const float* ex, const float
                                int Dx, int Dd, int precision, int save_for_backward,
                                float* sigma, float* rgb, void* workspace, int64_t workspace_bytes,
                                void* stream) {
+    if (P == 0 && params && S > 0) return NERF_OK;
     if (!params || !ex || !ed || !sigma || !rgb || P < 0 || S <= 0 || (P % S) != 0) return NERF_ERR_BAD_ARG;
     if (P == 0) return NERF_OK;
     if (!workspace) return NERF_ERR_WORKSPACE;
@@ -22,6 +23,7 @@ extern "C" int nerf_g1_mlp_fwd(const float* params, const float* ex, const float
 extern "C" int nerf_g1_mlp_bwd(const float* params, const float* ex, const float* ed, int64_t P, int S,
                                int Dx, int Dd, int precision, const float* d_sigma, const float* d_rgb,
                                float* grads, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (P == 0 && params && grads && S > 0) return NERF_OK;
     if (!params || !ex || !ed || !d_sigma || !d_rgb || !grads || P < 0 || S <= 0 || (P % S) != 0) return NERF_ERR_BAD_ARG;
     if (P == 0) return NERF_OK;
     if (!workspace) return NERF_ERR_WORKSPACE;

@@ -151,6 +151,7 @@ __global__ void sample_stratified_kernel(const float* __restrict__ t_base, int m
 
 static int launch_sampler(const float* t_base, int mode, float a, float b, float scale, int S, int64_t B,
                           const float* u, int jitter, uint64_t seed, int64_t ray_id_base, float* t_out, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;                       // zero rays: nothing to do (empty tensors carry null pointers)
     if (S <= 0 || B < 0 || !t_out) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;
     int64_t groups = (B * (int64_t)S + 3) / 4;
@@ -198,6 +199,7 @@ __global__ void density_noise_kernel(float* __restrict__ sigma, int S, int64_t B
 
 extern "C" int nerf_add_density_noise(float* sigma, int S, int64_t B, float std, uint64_t seed,
                                       int64_t ray_id_base, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
     if (!sigma || S <= 0 || B < 0) return NERF_ERR_BAD_ARG;
     if (B == 0 || std == 0.0f) return NERF_OK;
     int64_t n = B * ((S + 3) / 4);

@@ -179,7 +179,7 @@ class NeRF(nn.Module):
                                     self.normalize_direction, want_points=True)
         b, s = samples.shape
         flat = self.flat_parameters()
-        sigma, rgb = ops.g1_mlp(ex.view(b * s, -1), ed, s, self.density_inputs, self.color_inputs,
+        sigma, rgb = ops.g1_mlp(ex.view(b * s, ex.shape[-1]), ed, s, self.density_inputs, self.color_inputs,
                                 ops.PREC_FP32, flat, list(self.parameters()))
         return pts, sigma.view(b, s, 1), rgb.view(b, s, 3)
 
