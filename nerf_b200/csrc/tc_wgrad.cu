@@ -56,8 +56,15 @@ struct WgradArgs {
     int dbg;                         // experiments: bit 0 = no MMAs, bit 1 = no loads
     long long* prof;                 // NERF_WG_PROF: per-CTA cycle counters [8]
 };
-__host__ __device__ inline int wg_cost(const WgradArgs& a, int l) {      // quarter slabs the leader CTA loads per tile
-    return 8 + (a.xmain[l] ? 8 : 0) + (a.xenc[l] ? 4 : 0) + (a.xsmall[l] ? 1 : 0);
+// Relative time per tile of a unit, for the equal-cost cut of the work list over the CTA pairs.  Bytes alone
+// (8 quarter-slabs of dZ + 8 of X + 4 of the encoding + 1 small) mispredict: a stage costs its producer thread
+// ~250 cycles per bulk copy whatever the size, so the units with small stages (unit 0, the two head pseudo-units)
+// run at the producer's rate, not at HBM's.  Measured on B200 (clock64 span of every pair, NERF_WG_PROF):
+// cycles per tile 2254 (hidden), 2361 (hidden + encoding), 1838 (unit 0), 1875 (heads) -- with the byte costs the
+// head pairs finished 45 % after the average pair.
+__host__ __device__ inline int wg_cost(const WgradArgs& a, int l) {
+    if (a.xmain[l]) return a.xenc[l] ? 126 : 120;
+    return a.xenc[l] ? 98 : 100;
 }
 
 namespace tc {
