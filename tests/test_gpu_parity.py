@@ -357,10 +357,12 @@ def test_api_compat_g1_g2(nerf_pth_state_dict):
     assert img.shape == (1, 4, 5, 3)
 
 
-@pytest.mark.parametrize("b,s", [(1, 16), (130, 32), (300, 64), (77, 128), (5, 256)])
+@pytest.mark.parametrize("b,s", [(1, 16), (130, 32), (300, 64), (77, 128), (5, 256),
+                                 (32769, 16), (32898, 32), (33068, 64), (32845, 128), (32773, 256)])
 @pytest.mark.parametrize("saved", [True, False])
 def test_composite_tile_kernels_vs_autograd(b, s, saved):
-    """The thread-per-ray tile kernels (S % 16 == 0, ray geometry): forward outputs and the
+    """Ray-geometry compositing at S % 16 == 0: the thread-per-ray tile kernels (taken from 2^14 rays forward,
+    2^15 rays backward; ragged last tile) and the warp-per-ray kernels below that: forward outputs and the
     backward in both modes (suffix sums from the saved forward outputs / from a first sweep)."""
     from oracle import g1
     from nerf_b200 import _lib
