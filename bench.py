@@ -387,9 +387,18 @@ def run_ours(args):
 
     # ---- C4 / D4: the same step with latent-coded inputs (8 scenes, states_x in [-1,1]^4 => density_inputs 7) ----
     c4_ms = None
+    c4_render = None
     if args.precision == "bf16":
         torch.manual_seed(5)
         cm = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").to(dev)
+        sx1 = torch.tensor([[0.3, -0.2, 0.7, -0.9]], device=dev)         # validation render of train_conditional_nerf.py:141-153
+        with torch.no_grad():
+            cm.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES, states_x=sx1)
+            ms_c4r = timed_steps(lambda i: cm.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES,
+                                                           states_x=sx1), 3, flush)
+        c4_rps = rh * rw / (float(np.mean(ms_c4r)) * 1e-3)
+        c4_render = {"value": c4_rps, "unit": "rays/s", "workload": f"conditional {rh}x{rw} x {SAMPLES} samples render_image(states_x=[1,4])",
+                     "mlp_tflops": c4_rps * SAMPLES * 1_343_488 / 1e12}        # G1 + 4 latents: 671 744 MAC per point
         ctr = Trainer(cm, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=4321)
         g4 = torch.Generator().manual_seed(4)
         scenes = torch.rand(8, 4, generator=g4) * 2 - 1
@@ -443,6 +452,7 @@ def run_ours(args):
                 "value": world * RAYS / (c4_ms * 1e-3), "unit": "rays/s", "ms_per_step": c4_ms,
                 "workload": "conditional train step (8 scenes, 4 latents per ray: block_0.0.weight [256,140]), 4096 rays x 64 samples per GPU"},
             "render_d3": d3,
+            "render_c4": c4_render,
             "kernels": kernels,
             "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
                             "mlp_tflops": head_tflops},

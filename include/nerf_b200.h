@@ -163,8 +163,9 @@ int64_t nerf_g1_packed_bytes(int Dx, int Dd);
  * the previous LayerNorm's affine folded in, plus fp32 bias/head vectors. */
 int nerf_g1_pack_weights(const float* params, int Dx, int Dd, void* packed, void* stream);
 
-/* Workspace of nerf_g1_render_fused: t, sigma, rgb per point and rays per ray. */
-int64_t nerf_g1_render_workspace_bytes(int64_t B, int S);
+/* Workspace of nerf_g1_render_fused: t, sigma, rgb per point and rays per ray; with conditional
+ * inputs (Dx > 3) also the encoded states and their bias rows (2 KB per state row). */
+int64_t nerf_g1_render_workspace_bytes(int64_t B, int S, int Dx, int64_t n_states);
 
 /* Fused render (tcgen05 path): ray-gen (or explicit rays) -> stratified sample -> encode ->
  * MLP, one persistent kernel whose activations never leave the SM, then the compositing
@@ -176,6 +177,11 @@ int64_t nerf_g1_render_workspace_bytes(int64_t B, int S);
  * computed in-kernel) with jitter from u [B,S] or, when u == NULL and jitter != 0, from
  * Philox keyed by (seed, ray_id_base + ray, sample).
  * Density noise: noise_std != 0 adds Philox N(0,1)*std to sigma before compositing.
+ * Conditional inputs (G2, train_conditional_nerf.py:120-153; Dx = 3 + Sx): states_x [n_states,Sx];
+ * ray r of this call (camera mode: flattened id ray_begin + r) reads row r / rays_per_state --
+ * rays_per_state = 1 with one row per ray (render_rays), H*W with one row per camera
+ * (render_image).  The states' share of the two layers that see the position encoding is applied
+ * as a per-row bias computed in fp32 (csrc/tc_layout.cuh).  Dx == 3: states_x is ignored.
  * Outputs (each optional): out_pixels [B,3], out_depth/out_acc [B], out_weights [B,S],
  * out_t [B,S], out_sigma [B,S] (after noise), out_rgb [B,S,3].  Needs S >= 32. */
 int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
@@ -186,6 +192,7 @@ int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                          const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
                          const float* noise, float noise_std,
                          float normalize_position, int normalize_direction,
+                         const float* states_x, int64_t n_states, int64_t rays_per_state,
                          float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
                          float* out_t, float* out_sigma, float* out_rgb,
                          void* workspace, int64_t workspace_bytes, void* stream);

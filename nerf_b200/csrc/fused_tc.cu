@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 else if (l == 9) epilogue_unit<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 else if (a.ray_bias && (l == 0 || l == 4))
                     epilogue_unit<0, TRAIN, true>(a, l, taddr, act_addr, row, base + SM_VEC, st,
-                                                  a.ray_bias + ((size_t)(l ? 1 : 0) * a.B + (st.valid ? st.p / a.S : 0)) * 256);
+                                                  a.ray_bias + ((size_t)(l ? 1 : 0) * a.rb_rows + (st.valid ? (a.rb_ray0 + st.p / a.S) / a.rb_div : 0)) * 256);
                 else epilogue_unit<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
                 if (TRAIN) {                                         // normalised output of unit l (and the direction slab) -> HBM
@@ -252,10 +252,14 @@ extern "C" int nerf_add_density_noise(float*, int, int64_t, float, uint64_t, int
 
 static inline int64_t a256(int64_t x) { return (x + 255) & ~(int64_t)255; }
 
-extern "C" int64_t nerf_g1_render_workspace_bytes(int64_t B, int S) {
-    if (B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
+int launch_state_bias(const void* packed, int Dx, int Dd, const float* states, int64_t n_states, float* pes, float* rb, cudaStream_t st);   // tc_train.cu
+
+extern "C" int64_t nerf_g1_render_workspace_bytes(int64_t B, int S, int Dx, int64_t n_states) {
+    if (B < 0 || S <= 0 || Dx < 3 || Dx > 16 || n_states < 0) return NERF_ERR_BAD_ARG;
     int64_t P = B * S;
-    return a256(P * 4) * 2 + a256(P * 12) + 2 * a256(B * 12);      // t, sigma, rgb, rays_o, rays_d
+    int64_t n = a256(P * 4) * 2 + a256(P * 12) + 2 * a256(B * 12);   // t, sigma, rgb, rays_o, rays_d
+    if (Dx > 3) n += a256(n_states * (Dx - 3) * 2 * NERF_PE_X_OCTAVES * 4) + a256(n_states * 2 * 256 * 4);   // PE(states), bias rows of units 0 and 4
+    return n;
 }
 
 extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
@@ -266,15 +270,19 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                                     const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
                                     const float* noise, float noise_std,
                                     float normalize_position, int normalize_direction,
+                                    const float* states_x, int64_t n_states, int64_t rays_per_state,
                                     float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
                                     float* out_t, float* out_sigma, float* out_rgb,
                                     void* workspace, int64_t workspace_bytes, void* stream) {
     if (!packed || B < 0 || S < 32 || S > 4096) return (S > 0 && S < 32) ? NERF_ERR_UNSUPPORTED : NERF_ERR_BAD_ARG;
-    if (!rays_o != !rays_d) return NERF_ERR_BAD_ARG;
+    if (!rays_o != !rays_d || Dx < 3 || Dx > 16) return NERF_ERR_BAD_ARG;
     if (B == 0) return NERF_OK;                                   // zero rays: nothing to do (empty tensors carry null pointers)
+    if (Dx == 3) n_states = 0;
+    else if (!states_x || n_states <= 0 || rays_per_state <= 0 ||
+             ((rays_o ? 0 : ray_begin) + B - 1) / rays_per_state >= n_states) return NERF_ERR_BAD_ARG;
     if (!rays_o && (!cam_o || !cam_r || n_cams <= 0 || H <= 0 || W <= 0 || ray_begin < 0 ||
                     ray_begin + B > (int64_t)n_cams * H * W)) return NERF_ERR_BAD_ARG;
-    if (!workspace || workspace_bytes < nerf_g1_render_workspace_bytes(B, S)) return NERF_ERR_WORKSPACE;
+    if (!workspace || workspace_bytes < nerf_g1_render_workspace_bytes(B, S, Dx, n_states)) return NERF_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t P = B * S;
     uint8_t* w = (uint8_t*)workspace;
@@ -282,8 +290,14 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
     float* ws_sigma = (float*)w; w += a256(P * 4);
     float* ws_rgb = (float*)w; w += a256(P * 12);
     float* ws_o = (float*)w; w += a256(B * 12);
-    float* ws_d = (float*)w;
+    float* ws_d = (float*)w; w += a256(B * 12);
     FusedArgs a{};
+    if (Dx > 3) {                                                 // states -> PE -> bias rows of units 0 and 4 (tc_layout.cuh)
+        float* pes = (float*)w; w += a256(n_states * (Dx - 3) * 2 * NERF_PE_X_OCTAVES * 4);
+        float* rb = (float*)w;
+        int rc = launch_state_bias(packed, Dx, Dd, states_x, n_states, pes, rb, st); if (rc) return rc;
+        a.ray_bias = rb; a.rb_rows = n_states; a.rb_ray0 = rays_o ? 0 : ray_begin; a.rb_div = rays_per_state;
+    }
     a.rays_o = rays_o; a.rays_d = rays_d; a.cam_o = cam_o; a.cam_r = cam_r; a.H = H; a.W = W; a.focal = focal;
     a.ray_begin = ray_begin; a.ws_rays_o = ws_o; a.ws_rays_d = ws_d;
     a.B = B; a.S = S; a.P = P; a.n_tiles = (int)((P + 127) / 128);
@@ -324,6 +338,7 @@ int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, 
                        float* out_t, float* out_sigma, float* out_rgb, uint8_t* ws, const TrainLayout& T, cudaStream_t st) {
     FusedArgs a{};
     a.ray_bias = T.EXs ? reinterpret_cast<const float*>(ws + T.off_rb) : nullptr;
+    a.rb_rows = B; a.rb_ray0 = 0; a.rb_div = 1;
     a.rays_o = rays_o; a.rays_d = rays_d; a.B = B; a.S = S; a.P = T.P; a.n_tiles = T.n_tiles;
     a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
     a.near_plane = near_plane; a.far_plane = far_plane; a.norm = norm; a.normalize_dir = normalize_dir;

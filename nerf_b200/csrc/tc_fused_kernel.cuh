@@ -40,7 +40,8 @@ struct FusedArgs {
     // training forward (TRAIN = true): slab images of every unit's normalised output and of the two
     // encodings, plus (rstd, -mean*rstd) per point and unit, for the backward and wgrad kernels
     uint8_t* tr_act; uint8_t* tr_pex; uint8_t* tr_ped; float2* tr_stats; int64_t P_pad; int tr_tiles;
-    const float* ray_bias;                        // conditional inputs: [2 (units 0, 4)][B][256] fp32 per-ray bias, or null
+    const float* ray_bias;                        // conditional inputs: [2 (units 0, 4)][rb_rows][256] fp32 bias rows, or null;
+    int64_t rb_rows, rb_ray0, rb_div;             //   ray r of this launch uses row (rb_ray0 + r) / rb_div (one row per ray, or per camera)
     long long* prof;                              // NERF_TC_PROF: clock64 stamps of CTA 0, second work unit
     uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
 };

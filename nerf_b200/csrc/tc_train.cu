@@ -239,6 +239,19 @@ static int launch_bwd(BwdArgs& a, cudaStream_t st) {
     return NERF_OK;
 }
 
+// pes [n_states][EXs] <- PE(states [n_states][Dx-3]); rb [2][n_states][256] <- state weight columns of units 0, 4 x pes
+int launch_state_bias(const void* packed, int Dx, int Dd, const float* states, int64_t n_states, float* pes, float* rb, cudaStream_t st) {
+    PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
+    const int Sx = Dx - 3;
+    const int64_t n = n_states * Sx * NERF_PE_X_OCTAVES;
+    pe_states_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(states, n_states, Sx, pes);
+    NERF_CUDA_CHECK_LAUNCH();
+    ray_bias_kernel<<<dim3((unsigned)n_states, 2), 256, 0, st>>>(
+        reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_state_w_offset(L)), pes, n_states, L.EXs, rb);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
 extern "C" int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
                                     int64_t B, int S, float near_plane, float far_plane, const float* t_base,
                                     const float* t_in, const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
@@ -252,16 +265,10 @@ extern "C" int nerf_g1_train_fwd_tc(const void* packed, int Dx, int Dd, const fl
     TrainLayout T; make_train_layout(B, S, T, Dx);
     if (!workspace || workspace_bytes < T.total) return NERF_ERR_WORKSPACE;
     if (T.EXs) {                                                  // states -> PE -> per-ray bias of units 0 and 4
-        cudaStream_t st = (cudaStream_t)stream;
         uint8_t* ws = (uint8_t*)workspace;
-        float* pes = reinterpret_cast<float*>(ws + T.off_pes);
-        const int64_t n = B * (Dx - 3) * NERF_PE_X_OCTAVES;
-        pe_states_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(states_x, B, Dx - 3, pes);
-        NERF_CUDA_CHECK_LAUNCH();
-        ray_bias_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(
-            reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_state_w_offset(L)), pes, B, T.EXs,
-            reinterpret_cast<float*>(ws + T.off_rb));
-        NERF_CUDA_CHECK_LAUNCH();
+        rc = launch_state_bias(packed, Dx, Dd, states_x, B, reinterpret_cast<float*>(ws + T.off_pes),
+                               reinterpret_cast<float*>(ws + T.off_rb), (cudaStream_t)stream);
+        if (rc) return rc;
     }
     return launch_fused_train(packed, Dx, Dd, rays_o, rays_d, B, S, near_plane, far_plane, t_base, t_in, u, jitter, seed,
                               ray_id_base, normalize_position, normalize_direction, out_t, out_sigma, out_rgb,

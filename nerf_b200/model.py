@@ -201,11 +201,18 @@ class NeRF(nn.Module):
         b = rays_o.shape[0]
         if self._fused_ok(num_samples, states_x, states_d) and noise is None:
             # tcgen05 path: one persistent kernel for sample+encode+MLP, then the compositing kernel
-            packed = ops.g1_pack_weights(self.flat_parameters())
-            out = ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position, self.normalize_direction,
-                                      rays_o=rays_o, rays_d=rays_d, t_in=t, u=u,
-                                      t_base=self._ladder(near, far, num_samples, rays_o.device),
-                                      want=("pixels", "depth", "acc", "weights", "t", "sigma", "rgb"))
+            packed = ops.g1_pack_weights(self.flat_parameters(), self.density_inputs, 3)
+            sl = lambda x, i, j: None if x is None else x[i:j]
+            step = max(b, 1) if states_x is None else 1 << 17      # conditional: 2 KB of bias rows per ray in the workspace
+            outs = []
+            for i in range(0, max(b, 1), step):
+                j = min(i + step, b)
+                outs.append(ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position, self.normalize_direction,
+                                                rays_o=rays_o[i:j], rays_d=rays_d[i:j], t_in=sl(t, i, j), u=sl(u, i, j),
+                                                t_base=self._ladder(near, far, num_samples, rays_o.device),
+                                                want=("pixels", "depth", "acc", "weights", "t", "sigma", "rgb"),
+                                                states_x=sl(states_x, i, j)))
+            out = outs[0] if len(outs) == 1 else {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
             out["density"] = out.pop("sigma").unsqueeze(-1); out["color"] = out.pop("rgb")
             return out
         if b <= self.max_chunk_rays:
@@ -218,9 +225,11 @@ class NeRF(nn.Module):
         return {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
 
     def _fused_ok(self, num_samples, states_x, states_d):
-        """bf16 tcgen05 path: inference only for now (training uses the fp32 kernels)."""
+        """bf16 tcgen05 render path (training on tensor cores goes through train.Trainer): position-side
+        conditional inputs are supported, direction-side ones take the fp32 kernels."""
+        sx = 0 if states_x is None else states_x.shape[-1]
         return (self.precision == "bf16" and not torch.is_grad_enabled() and num_samples >= 32
-                and self.density_inputs == 3 and self.color_inputs == 3 and states_x is None and states_d is None)
+                and self.density_inputs == 3 + sx and self.color_inputs == 3 and states_d is None)
 
     def render_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
                     randomly_sample=False, density_noise_std=0.0):
@@ -258,7 +267,9 @@ class NeRF(nn.Module):
         chunk = self.max_chunk_rays if max_chunk_size is None else int(max_chunk_size)
         outs = []
         if self._fused_ok(num_samples, states_x, states_d) and num_fine == 0:
-            packed = ops.g1_pack_weights(self.flat_parameters())
+            packed = ops.g1_pack_weights(self.flat_parameters(), self.density_inputs, 3)
+            if states_x is not None:                        # one state row per camera (train_conditional_nerf.py:141-153)
+                states_x = states_x.float().reshape(-1, states_x.shape[-1]).expand(bc, -1).contiguous()
             big = 1 << 20                                   # rays per launch (bounds the t/sigma/rgb workspace)
             for i in range(ray_begin, ray_end, big):
                 j = min(i + big, ray_end)
@@ -266,7 +277,8 @@ class NeRF(nn.Module):
                                         self.normalize_direction,
                                         camera=(camera_o, camera_r, image_h, image_w, focal_length),
                                         ray_begin=i, num_rays=j - i,
-                                        t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",))
+                                        t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",),
+                                        states_x=states_x, rays_per_state=image_h * image_w)
                 outs.append(r["pixels"])
             img = torch.cat(outs, dim=0)
             return img.reshape(bc, image_h, image_w, 3) if full else img

@@ -249,8 +249,10 @@ def g1_mlp_tc_debug(packed, rays_o, rays_d, t, normalize_position, normalize_dir
 def g1_render_fused(packed, num_samples, near, far, normalize_position, normalize_direction=True,
                     rays_o=None, rays_d=None, camera=None, ray_begin=0, num_rays=None,
                     t_base=None, t_in=None, u=None, jitter=False, seed=0, ray_id_base=0, noise_std=0.0,
-                    want=("pixels", "depth", "acc", "weights", "t")):
-    """One fused pass.  camera = (cam_o [n,3], cam_r [n,3,3], H, W, focal) when rays are not given."""
+                    want=("pixels", "depth", "acc", "weights", "t"), states_x=None, rays_per_state=1):
+    """One fused pass.  camera = (cam_o [n,3], cam_r [n,3,3], H, W, focal) when rays are not given.
+    states_x [n,Sx] (conditional model, `packed` built with density_inputs = 3 + Sx): one row per
+    `rays_per_state` consecutive rays (camera mode: flattened ray ids)."""
     if rays_o is not None:
         rays_o, rays_d = _f32c(rays_o), _f32c(rays_d)
         b = rays_o.shape[0]; dev = rays_o.device
@@ -264,13 +266,16 @@ def g1_render_fused(packed, num_samples, near, far, normalize_position, normaliz
     alloc = {"pixels": (b, 3), "depth": (b,), "acc": (b,), "weights": (b, s), "t": (b, s), "sigma": (b, s), "rgb": (b, s, 3)}
     for k in want:
         out[k] = torch.empty(*alloc[k], device=dev, dtype=torch.float32)
-    nbytes = lib().nerf_g1_render_workspace_bytes(b, s)
+    states_x = _f32c(states_x)
+    n_states, dx = (0, 3) if states_x is None else (states_x.shape[0], 3 + states_x.shape[1])
+    nbytes = lib().nerf_g1_render_workspace_bytes(b, s, dx, n_states)
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
     g = lambda k: ptr(out.get(k))
-    check(lib().nerf_g1_render_fused(ptr(packed), 3, 3, ptr(rays_o), ptr(rays_d), ptr(cam_o), ptr(cam_r), n_cams, h, w,
+    check(lib().nerf_g1_render_fused(ptr(packed), dx, 3, ptr(rays_o), ptr(rays_d), ptr(cam_o), ptr(cam_r), n_cams, h, w,
                                      float(focal), ray_begin, b, s, float(near), float(far), ptr(t_base), ptr(_f32c(t_in)),
                                      ptr(_f32c(u)), int(jitter), seed, ray_id_base, None, float(noise_std),
                                      float(normalize_position), int(normalize_direction),
+                                     ptr(states_x), n_states, int(rays_per_state),
                                      g("pixels"), g("depth"), g("acc"), g("weights"), g("t"), g("sigma"), g("rgb"),
                                      ptr(ws), nbytes, stream()), "nerf_g1_render_fused")
     return out

@@ -25,14 +25,41 @@ def packed(nerf_pth_state_dict):
 def _render_args(P, packed, o, d, b, s, ws, nbytes, pixels):
     from nerf_b200 import _lib
     return (P(packed), 3, 3, P(o), P(d), None, None, 0, 0, 0, 1.0, 0, b, s, 2.0, 6.0, None, None, None, 0, 0, 0, None, 0.0,
-            6.0, 1, P(pixels), None, None, None, None, None, None, P(ws), nbytes, _lib.stream())
+            6.0, 1, None, 0, 1, P(pixels), None, None, None, None, None, None, P(ws), nbytes, _lib.stream())
+
+
+def test_render_fused_conditional_status_codes(L):
+    """Dx > 3 needs states_x with enough rows for every ray of the call; the workspace grows by the bias rows."""
+    from nerf_b200 import _lib, ops
+    from nerf_b200.model import NeRF
+    P = _lib.ptr
+    torch.manual_seed(0)
+    m = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").cuda()
+    pk = ops.g1_pack_weights(m.flat_parameters(), 7, 3)
+    o = torch.randn(8, 3, device="cuda"); d = torch.randn(8, 3, device="cuda"); px = torch.empty(8, 3, device="cuda")
+    sx = torch.rand(8, 4, device="cuda")
+    n = L.nerf_g1_render_workspace_bytes(8, 64, 7, 8)
+    assert n > L.nerf_g1_render_workspace_bytes(8, 64, 3, 0) > 0
+    assert L.nerf_g1_render_workspace_bytes(8, 64, 2, 0) == BAD_ARG
+    ws = torch.empty(n, dtype=torch.uint8, device="cuda")
+    def call(states, n_states, per, nbytes=n):
+        return L.nerf_g1_render_fused(P(pk), 7, 3, P(o), P(d), None, None, 0, 0, 0, 1.0, 0, 8, 64, 2.0, 6.0, None, None, None, 0, 0, 0,
+                                      None, 0.0, 6.0, 1, P(states), n_states, per, P(px), None, None, None, None, None, None,
+                                      P(ws), nbytes, _lib.stream())
+    assert call(sx, 8, 1) == 0
+    assert call(sx, 2, 4) == 0                                   # 4 rays per state row
+    assert call(None, 8, 1) == BAD_ARG                           # conditional model without states
+    assert call(sx, 4, 1) == BAD_ARG                             # rays 4..7 have no row
+    assert call(sx, 8, 0) == BAD_ARG
+    assert call(sx, 8, 1, L.nerf_g1_render_workspace_bytes(8, 64, 3, 0)) == WORKSPACE
+    torch.cuda.synchronize()
 
 
 def test_render_fused_status_codes(L, packed):
     from nerf_b200 import _lib
     P = _lib.ptr
     o = torch.randn(8, 3, device="cuda"); d = torch.randn(8, 3, device="cuda"); px = torch.empty(8, 3, device="cuda")
-    n = L.nerf_g1_render_workspace_bytes(8, 64)
+    n = L.nerf_g1_render_workspace_bytes(8, 64, 3, 0)
     ws = torch.empty(n, dtype=torch.uint8, device="cuda")
     assert L.nerf_g1_render_fused(*_render_args(P, packed, o, d, 8, 64, ws, n, px)) == 0
     assert L.nerf_g1_render_fused(*_render_args(P, packed, o, d, 0, 64, ws, n, px)) == 0            # zero rays: no-op

@@ -473,3 +473,54 @@ def test_tc_train_conditional_d4_vs_fp32():
         c = torch.nn.functional.cosine_similarity(a.flatten(), w.flatten(), dim=0).item()
         print(f"{key} state columns: cosine {c:.5f}, |grad| {w.norm().item():.3e}")
         assert c >= 0.99, (key, c)                             # per-tensor bar (ReLU sign flips between the precisions), as for G1
+
+
+def test_tc_render_conditional_vs_fp32(nerf_pth_state_dict):
+    """G2 render (train_conditional_nerf.py:120-153) on the tensor-core path: states_x enters as bias rows of
+    units 0 and 4.  The network is nerf.pth widened by random state columns (a random-init network puts sigma
+    near 0 at the last sample, where the 1e10 interval turns bf16 rounding into pixel flips in either
+    precision).  Ray mode (a state row per ray, ragged batch) and camera mode (a row per camera, flattened
+    ray ids across two cameras, a shard that starts mid-image) against our fp32 kernels: pixels within the
+    bf16 bars of D1 (max-abs 2e-2, PSNR >= 40 dB); camera mode equals ray mode on the same rays bit for bit."""
+    from nerf_b200 import ops
+    from nerf_b200.model import NeRF
+    torch.manual_seed(5)
+    m32 = NeRF(normalize_position=6.0, density_inputs=7, precision="fp32").cuda()
+    sd = {k: v.clone() for k, v in m32.state_dict().items()}
+    g = torch.Generator().manual_seed(11)
+    for k, v in nerf_pth_state_dict.items():
+        if k == "block_0.0.weight":
+            sd[k] = torch.cat([v, 0.05 * torch.randn(256, 80, generator=g)], dim=1).cuda()
+        elif k == "block_1.0.weight":
+            sd[k] = torch.cat([v, 0.05 * torch.randn(256, 80, generator=g)], dim=1).cuda()
+        else:
+            sd[k] = v.clone().cuda()
+    m32.load_state_dict(sd)
+    m16 = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").cuda()
+    m16.load_state_dict(m32.state_dict())
+    gen = torch.Generator().manual_seed(9)
+    cam_o = torch.tensor([[0.0, 0.0, 4.0], [0.5, -0.3, 4.2]]).cuda()
+    cam_r = torch.eye(3).expand(2, 3, 3).contiguous().cuda()
+    sx = (torch.rand(2, 4, generator=gen) * 2 - 1).cuda()
+    h, w, f = 37, 41, 50.0
+    with torch.no_grad():
+        img16 = m16.render_image(cam_o, cam_r, h, w, f, 2.0, 6.0, 64, states_x=sx)
+        img32 = m32.render_image(cam_o, cam_r, h, w, f, 2.0, 6.0, 64, states_x=sx)
+        assert img16.shape == (2, h, w, 3)
+        err = (img16 - img32).abs().max().item()
+        psnr = -10 * torch.log10(((img16 - img32) ** 2).mean()).item()
+        print(f"conditional render bf16 vs fp32: max-abs {err:.2e}, PSNR {psnr:.1f} dB")
+        assert err <= 2e-2 and psnr >= 40.0
+        assert (img16[0] - img16[1]).abs().max().item() > 1e-3        # the two cameras really see different states
+        # ray mode on the same rays, one state row per ray
+        o, d = ops.generate_rays(cam_o, cam_r, h, w, f, 0, 2 * h * w)
+        per_ray = sx[torch.arange(2 * h * w, device="cuda") // (h * w)].contiguous()
+        r = m16.render_rays_full(o, d, 2.0, 6.0, 64, states_x=per_ray)
+        assert torch.equal(r["pixels"].view(2, h, w, 3), img16)
+        # a shard starting inside the first image and ending inside the second
+        part = m16.render_image(cam_o, cam_r, h, w, f, 2.0, 6.0, 64, states_x=sx, ray_begin=1000, ray_end=2500)
+        assert torch.equal(part, img16.view(-1, 3)[1000:2500])
+        # G2 return shape of render_rays
+        px = m16.render_rays(o[:300], d[:300], 2.0, 6.0, 64, states_x=per_ray[:300])
+        ref = m32.render_rays(o[:300], d[:300], 2.0, 6.0, 64, states_x=per_ray[:300])
+        assert px.shape == ref.shape and (px - ref).abs().max().item() <= 2e-2
