@@ -217,8 +217,8 @@ def run_ours(args):
     for i in range(n_pool):
         o, d = synthetic_batch(RAYS, seed=1000 * rank + i)
         tgt = torch.rand(RAYS, 3, generator=torch.Generator().manual_seed(7 + i))
-        pool_h.append(tuple(x.pin_memory() for x in (o, d, tgt)))
-    pool_d = [tuple(x.to(dev) for x in b) for b in pool_h]
+        pool_h.append(torch.stack([o, d, tgt]).pin_memory())      # one pinned [3, RAYS, 3] block per batch: one H2D copy
+    pool_d = [tuple(b.to(dev)) for b in pool_h]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     K, W = args.steps, args.warmup
 
@@ -229,7 +229,7 @@ def run_ours(args):
     host_loss = torch.empty(1).pin_memory()
 
     def step_e2e(i):
-        o, d, tgt = (x.to(dev, non_blocking=True) for x in pool_h[i % n_pool])
+        o, d, tgt = pool_h[i % n_pool].to(dev, non_blocking=True)   # rays_o, rays_d, target pixels: contiguous views
         loss = trainer.step(o, d, tgt)
         host_loss.copy_(loss, non_blocking=True)
 

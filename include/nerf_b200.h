@@ -300,6 +300,17 @@ int nerf_adam_step(float* params, const float* grads, float* exp_avg, float* exp
 int nerf_mse_loss(const float* pixels, const float* target, int64_t n, float* loss_out,
                   float* g_pixels, void* stream);
 
+/* The loss side of one training step (train_conditional_nerf.py:120-133 after the MLP) in ONE launch:
+ * sigma + N(0,1)*noise_std (the draw of nerf_add_density_noise; sigma itself is not modified) ->
+ * composite (nerf/model.py:437-469,660) -> mean((pixels - target)^2) -> its gradient back through the
+ * composite.  Same results as nerf_add_density_noise + nerf_composite_fwd + nerf_mse_loss +
+ * nerf_composite_bwd.  pixels [B,3] optional; loss_out [1] overwritten; d_sigma [B,S], d_rgb [B,S,3].
+ * S <= 256 (NERF_ERR_UNSUPPORTED above: use the four calls). */
+int nerf_composite_mse_train(const float* sigma, const float* rgb, const float* rays_o, const float* rays_d,
+                             const float* t, const float* target, int64_t B, int S,
+                             float noise_std, uint64_t seed, int64_t ray_id_base,
+                             float* pixels, float* loss_out, float* d_sigma, float* d_rgb, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

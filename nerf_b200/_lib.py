@@ -56,6 +56,7 @@ SIGNATURES = {
     "nerf_head_composite": (c_i, [c_p, c_i, c_i, c_p, c_p, c_f, c_l, c_i, c_p, c_p, c_p, c_i, c_p]),
     "nerf_adam_step": (c_i, [c_p, c_p, c_p, c_p, c_l, c_l, c_f, c_f, c_f, c_f, c_f, c_p]),
     "nerf_mse_loss": (c_i, [c_p, c_p, c_l, c_p, c_p, c_p]),
+    "nerf_composite_mse_train": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_u64, c_l, c_p, c_p, c_p, c_p, c_p]),
 }
 
 

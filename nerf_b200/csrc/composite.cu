@@ -147,6 +147,97 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(
     }
 }
 
+// The loss side of a training step in one pass per ray: sigma += N(0,1) std (the draw of density_noise_kernel),
+// composite forward, mean((pixel - target)^2) with its gradient, composite backward.  Same arithmetic, in the same
+// order, as density_noise_kernel -> composite_fwd_kernel -> mse_kernel -> composite_bwd_kernel<NSEG>; the ray's
+// samples stay in registers between the sweeps (S <= 32 NSEG).
+template <int NSEG>
+__global__ void __launch_bounds__(256) composite_mse_train_kernel(
+        const float* __restrict__ sigma, const float* __restrict__ rgb,
+        const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ t,
+        const float* __restrict__ target, int64_t B, int S, float noise_std, uint64_t seed, int64_t ray_id_base,
+        float* __restrict__ pixels, float* __restrict__ loss, float* __restrict__ d_sigma, float* __restrict__ d_rgb) {
+    __shared__ float part[8];
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const float inv_n = 1.0f / (float)(B * 3);
+    float sq = 0.f;
+    for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < B; ray += warps) {
+        RayGeom g; load_geom(g, nullptr, rays_o, rays_d, t, ray);
+        const int64_t base = ray * S;
+        float coef[NSEG], Ts[NSEG], ws[NSEG], inv[NSEG], c0[NSEG], c1[NSEG], c2[NSEG];
+        float carry = 1.0f, pr = 0.f, pg = 0.f, pb = 0.f;
+#pragma unroll
+        for (int seg = 0; seg < NSEG; ++seg) {
+            const int k = seg * 32 + lane; const bool valid = k < S;
+            float a = 1.0f, ae = 1.0f, dl = 0.f, sg = 0.f;
+            if (valid) {
+                sg = sigma[base + k];
+                if (noise_std != 0.0f) {
+                    uint32_t r4[4];
+                    philox4x32(seed ^ 0x6E6F697365ull, (uint64_t)(ray_id_base + ray), (uint32_t)(k >> 2), r4);
+                    const int h = (k >> 1) & 1;
+                    float u1 = ((float)(r4[2 * h] >> 8) + 1.0f) * (1.0f / 16777216.0f);
+                    float u2 = u01_from_bits(r4[2 * h + 1]);
+                    float rad = sqrtf(-2.0f * logf(u1)), sn, cs;
+                    sincospif(2.0f * u2, &sn, &cs);
+                    sg += ((k & 1) ? rad * sn : rad * cs) * noise_std;
+                }
+                dl = delta_at(g, base, k, S);
+                a = expf(__fmul_rn(-fmaxf(sg, 0.f), dl));
+                ae = __fadd_rn(a, NERF_EPS_T);
+            }
+            float T = (seg * 32 < S) ? warp_excl_prod(ae, carry, lane) : 1.0f;
+            float w = 0.f; c0[seg] = c1[seg] = c2[seg] = 0.f;
+            if (valid) {
+                w = __fmul_rn(__fsub_rn(1.0f, a), T);
+                const float* c = rgb + (base + k) * 3;
+                c0[seg] = sigmoidf_(c[0]); c1[seg] = sigmoidf_(c[1]); c2[seg] = sigmoidf_(c[2]);
+                pr += w * c0[seg]; pg += w * c1[seg]; pb += w * c2[seg];
+            }
+            coef[seg] = (valid && sg > 0.f) ? dl * a : 0.f;
+            Ts[seg] = T; ws[seg] = w; inv[seg] = 1.0f / ae;
+        }
+        pr = warp_sum(pr); pg = warp_sum(pg); pb = warp_sum(pb);
+        const float er = pr - target[ray * 3], eg = pg - target[ray * 3 + 1], eb = pb - target[ray * 3 + 2];
+        const float gr = 2.0f * er * inv_n, gg = 2.0f * eg * inv_n, gb = 2.0f * eb * inv_n;
+        if (lane == 0) {
+            sq += er * er; sq += eg * eg; sq += eb * eb;
+            if (pixels) { pixels[ray * 3] = pr; pixels[ray * 3 + 1] = pg; pixels[ray * 3 + 2] = pb; }
+        }
+#pragma unroll
+        for (int seg = 0; seg < NSEG; ++seg) {
+            const int k = seg * 32 + lane;
+            const float s0 = c0[seg], s1 = c1[seg], s2 = c2[seg], w = ws[seg];
+            const float s = gr * s0 + gg * s1 + gb * s2 + 0.f;
+            if (k < S) {
+                float* o = d_rgb + (base + k) * 3;
+                o[0] = w * gr * s0 * (1.0f - s0); o[1] = w * gg * s1 * (1.0f - s1); o[2] = w * gb * s2 * (1.0f - s2);
+            }
+            Ts[seg] *= s; ws[seg] = w * s;
+        }
+        float tail = 0.f;
+#pragma unroll
+        for (int seg = NSEG - 1; seg >= 0; --seg) {
+            if (seg * 32 >= S) continue;
+            float incl = ws[seg];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { float n = __shfl_down_sync(0xffffffffu, incl, o); if (lane + o < 32) incl += n; }
+            float suffix = tail + (incl - ws[seg]);
+            const int k = seg * 32 + lane;
+            if (k < S) d_sigma[base + k] = coef[seg] * (Ts[seg] - suffix * inv[seg]);
+            tail += __shfl_sync(0xffffffffu, incl, 0);
+        }
+    }
+    if (lane == 0) part[threadIdx.x >> 5] = sq;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < 8 ? part[threadIdx.x] : 0.f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) atomicAdd(loss, v * inv_n);
+    }
+}
+
 static unsigned grid_for_rays(int64_t B) {
     int64_t blocks = (B + 7) / 8;                              // 8 warps (rays) per 256-thread block
     int64_t cap = (int64_t)nerf_num_sms() * 8 * 4;             // grid-stride beyond 4 waves
@@ -207,6 +298,25 @@ extern "C" int nerf_composite_bwd(const float* sigma, const float* rgb, const fl
     if (S <= 32) LAUNCH_BWD(1); else if (S <= 64) LAUNCH_BWD(2); else if (S <= 128) LAUNCH_BWD(4);
     else if (S <= 256) LAUNCH_BWD(8); else LAUNCH_BWD(32);
 #undef LAUNCH_BWD
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int nerf_composite_mse_train(const float* sigma, const float* rgb, const float* rays_o, const float* rays_d,
+                                        const float* t, const float* target, int64_t B, int S,
+                                        float noise_std, uint64_t seed, int64_t ray_id_base,
+                                        float* pixels, float* loss_out, float* d_sigma, float* d_rgb, void* stream) {
+    if (!loss_out || B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
+    if (S > 256) return NERF_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    NERF_CUDA(cudaMemsetAsync(loss_out, 0, sizeof(float), st));
+    if (B == 0) return NERF_OK;
+    if (!sigma || !rgb || !rays_o || !rays_d || !t || !target || !d_sigma || !d_rgb) return NERF_ERR_BAD_ARG;
+    unsigned grid = grid_for_rays(B);
+#define LAUNCH_CMT(N) composite_mse_train_kernel<N><<<grid, 256, 0, st>>>(sigma, rgb, rays_o, rays_d, t, target, B, S, \
+        noise_std, seed, ray_id_base, pixels, loss_out, d_sigma, d_rgb)
+    if (S <= 32) LAUNCH_CMT(1); else if (S <= 64) LAUNCH_CMT(2); else if (S <= 128) LAUNCH_CMT(4); else LAUNCH_CMT(8);
+#undef LAUNCH_CMT
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }

@@ -78,21 +78,29 @@ class Trainer:
                                      ptr(z["t"]), ptr(z["sigma"]), ptr(z["rgb"]), ptr(z["ws"]), z["n"], st),
               "nerf_g1_train_fwd_tc")
         launches = 4 + (5 if dx > 3 else 0)     # conditional: state weights, PE(states), ray bias; dz ray sums, state gradients
-        if noise is not None:
-            z["sigma"] += noise.view(b, s)
-        elif self.noise_std != 0.0:
-            ops.add_density_noise_(z["sigma"], self.noise_std, self.seed, ray_base); launches += 1
-        check(L.nerf_composite_fwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
-                                   ptr(z["pixels"]), None, None, None, st), "nerf_composite_fwd")
-        check(L.nerf_mse_loss(ptr(z["pixels"]), ptr(target), b * 3, ptr(z["loss"]), ptr(z["g_pixels"]), st), "nerf_mse_loss")
-        check(L.nerf_composite_bwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
-                                   ptr(z["g_pixels"]), None, None, None, ptr(z["pixels"]), None, None,
-                                   ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
-              "nerf_composite_bwd")
+        std = float(self.noise_std)
+        if noise is not None:                   # host-supplied draw (parity mode)
+            z["sigma"] += noise.view(b, s); std = 0.0
+        if s <= 256:                            # noise + composite + MSE + composite backward: one launch
+            check(L.nerf_composite_mse_train(ptr(z["sigma"]), ptr(z["rgb"]), ptr(rays_o), ptr(rays_d), ptr(z["t"]), ptr(target),
+                                             b, s, std, self.seed, ray_base, ptr(z["pixels"]), ptr(z["loss"]),
+                                             ptr(z["d_sigma"]), ptr(z["d_rgb"]), st), "nerf_composite_mse_train")
+            launches += 1
+        else:
+            if std != 0.0:
+                ops.add_density_noise_(z["sigma"], std, self.seed, ray_base); launches += 1
+            check(L.nerf_composite_fwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
+                                       ptr(z["pixels"]), None, None, None, st), "nerf_composite_fwd")
+            check(L.nerf_mse_loss(ptr(z["pixels"]), ptr(target), b * 3, ptr(z["loss"]), ptr(z["g_pixels"]), st), "nerf_mse_loss")
+            check(L.nerf_composite_bwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
+                                       ptr(z["g_pixels"]), None, None, None, ptr(z["pixels"]), None, None,
+                                       ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
+                  "nerf_composite_bwd")
+            launches += 3
         check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), dx, 3, ptr(z["d_sigma"]),
                                      ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
               "nerf_g1_train_bwd_tc")
-        launches += 3 + 4                                           # + bwd, wgrad, 2 unfold (memset not counted)
+        launches += 4                                               # bwd, wgrad, 2 unfold (memset not counted)
         if self.world > 1:
             dist.all_reduce(self.flat_grad, group=self.group)
         if apply_update:

@@ -394,3 +394,47 @@ def test_composite_tile_kernels_vs_autograd(b, s, saved):
     scale = sigma.grad.abs().max().item() + 1e-6
     np.testing.assert_allclose(ds.cpu().numpy(), sigma.grad.numpy(), rtol=1e-4, atol=2e-5 * scale)
     np.testing.assert_allclose(dcol.cpu().numpy(), rgb.grad.numpy(), rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("b,s,std", [(1, 32, 0.0), (77, 64, 1.0), (4096, 64, 1.0), (130, 48, 0.5), (33, 128, 1.0), (9, 256, 1.0), (5000, 200, 0.0)])
+def test_composite_mse_train_equals_the_four_calls(b, s, std):
+    """nerf_composite_mse_train (noise + composite + MSE + composite backward in one launch) against
+    nerf_add_density_noise -> nerf_composite_fwd -> nerf_mse_loss -> nerf_composite_bwd: the same draw and the
+    same arithmetic in the same order, so pixels and gradients agree to rounding of the contraction
+    (1e-6 relative) and the loss (an atomic sum over blocks in both) to 1e-6."""
+    from nerf_b200 import _lib
+    L = _lib.lib(); P = _lib.ptr; st = _lib.stream
+    gen = torch.Generator().manual_seed(3 * b + s)
+    o = torch.randn(b, 3, generator=gen).cuda(); d = torch.randn(b, 3, generator=gen).cuda()
+    t = (torch.rand(b, s, generator=gen) * 4 + 2).sort(dim=-1)[0].cuda()
+    sigma = (torch.randn(b, s, generator=gen) * 3).cuda(); rgb = torch.randn(b, s, 3, generator=gen).cuda()
+    tgt = torch.rand(b, 3, generator=gen).cuda()
+    seed, ray0 = 99, 12345
+    # the four calls
+    sg = sigma.clone()
+    _lib.check(L.nerf_add_density_noise(P(sg), s, b, std, seed, ray0, st()), "noise")
+    px = torch.empty(b, 3, device="cuda"); loss = torch.empty(1, device="cuda"); gp = torch.empty(b, 3, device="cuda")
+    ds = torch.empty(b, s, device="cuda"); dc = torch.empty(b, s, 3, device="cuda")
+    _lib.check(L.nerf_composite_fwd(P(sg), P(rgb), None, P(o), P(d), P(t), b, s, P(px), None, None, None, st()), "fwd")
+    _lib.check(L.nerf_mse_loss(P(px), P(tgt), b * 3, P(loss), P(gp), st()), "mse")
+    _lib.check(L.nerf_composite_bwd(P(sg), P(rgb), None, P(o), P(d), P(t), b, s, P(gp), None, None, None, None, None, None,
+                                    P(ds), P(dc), st()), "bwd")
+    # one call
+    px2 = torch.full((b, 3), float("nan"), device="cuda"); loss2 = torch.full((1,), float("nan"), device="cuda")
+    ds2 = torch.full((b, s), float("nan"), device="cuda"); dc2 = torch.full((b, s, 3), float("nan"), device="cuda")
+    sig_in = sigma.clone()
+    _lib.check(L.nerf_composite_mse_train(P(sig_in), P(rgb), P(o), P(d), P(t), P(tgt), b, s, std, seed, ray0,
+                                          P(px2), P(loss2), P(ds2), P(dc2), st()), "fused")
+    assert torch.equal(sig_in, sigma)                                   # sigma is an input only
+    np.testing.assert_allclose(px2.cpu().numpy(), px.cpu().numpy(), rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(loss2.item(), loss.item(), rtol=1e-5)
+    sc = ds.abs().max().item() + 1e-12
+    np.testing.assert_allclose(ds2.cpu().numpy(), ds.cpu().numpy(), rtol=1e-5, atol=1e-6 * sc)
+    np.testing.assert_allclose(dc2.cpu().numpy(), dc.cpu().numpy(), rtol=1e-5, atol=1e-9)
+    # status codes
+    assert L.nerf_composite_mse_train(P(sig_in), P(rgb), P(o), P(d), P(t), P(tgt), b, 512, std, seed, ray0,
+                                      P(px2), P(loss2), P(ds2), P(dc2), st()) == -2
+    assert L.nerf_composite_mse_train(P(sig_in), P(rgb), P(o), P(d), P(t), None, b, s, std, seed, ray0,
+                                      P(px2), P(loss2), P(ds2), P(dc2), st()) == -1
+    assert L.nerf_composite_mse_train(None, None, None, None, None, None, 0, s, std, seed, ray0,
+                                      None, P(loss2), None, None, st()) == 0 and loss2.item() == 0.0
