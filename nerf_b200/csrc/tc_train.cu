@@ -133,9 +133,9 @@ __global__ void __launch_bounds__(256) state_grad_kernel(const float* __restrict
 //   dW_l[i,k] = G_l[i,k] gamma_{l-1}[k] + c_l[i] beta_{l-1}[k]  (hidden k);  = G_l[i, 256+k2]  (encoding)
 //   db_l = c_l;  heads: dw[k] = gamma[k] H[k] + beta[k] s,  db = s
 //   conditional inputs: the state columns of units 0 and 4 come from gs (state_grad_kernel)
-__global__ void unfold_weights_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
-                                      const float* __restrict__ gh, const float* __restrict__ hsum, const float* __restrict__ gs,
-                                      float* __restrict__ grads) {
+__device__ __forceinline__ void unfold_weights_body(const float* __restrict__ params, const PackLayout& L, const float* __restrict__ gw,
+                                                    const float* __restrict__ gh, const float* __restrict__ hsum, const float* __restrict__ gs,
+                                                    float* __restrict__ grads) {
     const int l = blockIdx.y;
     if (l < 10) {
         const int Kt = L.Kt[l], hid = (l == 0) ? 0 : 256;
@@ -165,8 +165,8 @@ __global__ void unfold_weights_kernel(const float* __restrict__ params, PackLayo
     }
 }
 //   dgamma_j[k] = sum_i G_{j+1}[i,k] W_{j+1}[i,k]  (+ head: w[k] H[k]);  dbeta_j[k] = sum_i c_{j+1}[i] W_{j+1}[i,k]  (+ head: w[k] s)
-__global__ void unfold_affine_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
-                                     const float* __restrict__ gh, const float* __restrict__ hsum, float* __restrict__ grads) {
+__device__ __forceinline__ void unfold_affine_body(const float* __restrict__ params, const PackLayout& L, const float* __restrict__ gw,
+                                                   const float* __restrict__ gh, const float* __restrict__ hsum, float* __restrict__ grads) {
     const int j = blockIdx.x, k = threadIdx.x & 255, part = threadIdx.x >> 8;      // 1024 threads: 4 row groups x 256 columns
     __shared__ float sg[4][256], sb[4][256];
     float dg = 0.f, db = 0.f;
@@ -174,11 +174,19 @@ __global__ void unfold_affine_kernel(const float* __restrict__ params, PackLayou
         const int l = j + 1, Kt = L.Kt[l];
         const float* G = gw + (size_t)l * 256 * TC_GW_LD;
         const float* W = params + L.off_W[l];
-        for (int i = part * 64; i < part * 64 + 64; ++i) {
-            const float w = W[(size_t)i * Kt + k];
-            dg = fmaf(G[(size_t)i * TC_GW_LD + k], w, dg);
-            db = fmaf(G[(size_t)i * TC_GW_LD + 320], w, db);
+        float dgs[8], dbs[8];                                       // 8 rows in flight: the loop is load-latency bound
+#pragma unroll
+        for (int q = 0; q < 8; ++q) dgs[q] = dbs[q] = 0.f;
+        for (int i = part * 64; i < part * 64 + 64; i += 8) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const float w = W[(size_t)(i + q) * Kt + k];
+                dgs[q] = fmaf(G[(size_t)(i + q) * TC_GW_LD + k], w, dgs[q]);
+                dbs[q] = fmaf(G[(size_t)(i + q) * TC_GW_LD + 320], w, dbs[q]);
+            }
         }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { dg += dgs[q]; db += dbs[q]; }
     }
     sg[part][k] = dg; sb[part][k] = db;
     __syncthreads();
@@ -195,6 +203,14 @@ __global__ void unfold_affine_kernel(const float* __restrict__ params, PackLayou
         }
         grads[L.off_gamma[j] + k] = dg; grads[L.off_beta[j] + k] = db;
     }
+}
+
+// one launch: rows 0..10 of the grid unfold the weights (grid-stride), row 11 the LayerNorm affines (block = unit)
+__global__ void __launch_bounds__(1024) unfold_kernel(const float* __restrict__ params, PackLayout L, const float* __restrict__ gw,
+                                                      const float* __restrict__ gh, const float* __restrict__ hsum,
+                                                      const float* __restrict__ gs, float* __restrict__ grads) {
+    if (blockIdx.y < 11) unfold_weights_body(params, L, gw, gh, hsum, gs, grads);
+    else if (blockIdx.x < 10) unfold_affine_body(params, L, gw, gh, hsum, grads);
 }
 
 template <int CG>
@@ -315,9 +331,7 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
             rsum, reinterpret_cast<const float*>(ws + T.off_pes), B, T.EXs, reinterpret_cast<float*>(ws + T.off_gs));
         NERF_CUDA_CHECK_LAUNCH();
     }
-    unfold_weights_kernel<<<dim3(80, 11), 256, 0, st>>>(params, L, gw, gh, hsum, gs, grads);
-    NERF_CUDA_CHECK_LAUNCH();
-    unfold_affine_kernel<<<10, 1024, 0, st>>>(params, L, gw, gh, hsum, grads);
+    unfold_kernel<<<dim3(20, 12), 1024, 0, st>>>(params, L, gw, gh, hsum, gs, grads);
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }

@@ -100,7 +100,7 @@ class Trainer:
         check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), dx, 3, ptr(z["d_sigma"]),
                                      ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
               "nerf_g1_train_bwd_tc")
-        launches += 4                                               # bwd, wgrad, 2 unfold (memset not counted)
+        launches += 3                                               # bwd, wgrad, unfold (memset not counted)
         if self.world > 1:
             dist.all_reduce(self.flat_grad, group=self.group)
         if apply_update:
