@@ -310,29 +310,32 @@ __global__ void __launch_bounds__(TB_THREADS, 1) g1_bwd_tc_kernel(const BwdArgs 
                 tc::fence_proxy_async_smem();
                 tc::named_bar_sync(1 + x, 128);                      // dz_l complete in shared memory
                 if (pfe) a.prof[(l * 2 + x) * 8 + 6] = clock64();
-                if (io) {
-                    tc::tma_store_1d(a.dz + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), act_addr, 4 * TC_SLAB_BYTES);
-                    tc::tma_store_commit();
-                }
                 if (l > 0) {
                     tc::tcgen05_fence_before();
                     if (CG == 2) { __syncwarp(); if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
                     else tc::mbar_arrive(act_ready(x));
-                    if (io) {                                        // refill each K-slab with n_{l-1} once the MMA has consumed it
-                        const bool pfi = a.prof && blockIdx.x == 0 && q == 1 && l == 6;
-                        for (int ks = 0; ks < 4; ++ks) {
+                }
+                if (io) {
+                    // dz_l -> HBM slab by slab, each K-slab refilled with n_{l-1} as soon as its own store has been read out
+                    // and the MMA has consumed it: the refills do not queue behind the whole 64 KB store
+                    uint8_t* gdz = a.dz + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
+                    const bool pfi = a.prof && blockIdx.x == 0 && q == 1 && l == 6;
+                    for (int ks = 0; ks < 4; ++ks) {
+                        tc::tma_store_1d(gdz + (size_t)ks * TC_SLAB_BYTES, act_addr + ks * TC_SLAB_BYTES, TC_SLAB_BYTES);
+                        tc::tma_store_commit();
+                        if (l > 0) {
                             if (pfi && ks == 0) a.prof[176 + x * 4] = clock64();
                             tc::mbar_wait(slab_free(x, ks), sf_it & 1, a.wait_hint);
                             if (pfi && ks == 0) a.prof[177 + x * 4] = clock64();
-                            if (ks == 0) tc::tma_store_wait_read0();
+                            tc::tma_store_wait_read0();
                             if (pfi && ks == 0) a.prof[178 + x * 4] = clock64();
                             if (pfi && ks == 3) a.prof[179 + x * 4] = clock64();
                             tc::mbar_arrive_expect_tx(n_full(x, ks), TC_SLAB_BYTES);
                             tc::tma_load_1d(act_addr + ks * TC_SLAB_BYTES,
                                             a.act + (((size_t)(l - 1) * a.tr_tiles + tile) * 4 + ks) * TC_SLAB_BYTES, TC_SLAB_BYTES, n_full(x, ks));
                         }
-                        ++sf_it;
                     }
+                    if (l > 0) ++sf_it;
                 }
             }
         }
