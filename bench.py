@@ -375,6 +375,21 @@ def run_ours(args):
         ms_h = timed_steps(lambda i: hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES), 3, flush)
     head_rps = hh * hh / (float(np.mean(ms_h)) * 1e-3)
     head_tflops = head_rps * (SAMPLES - 1) * 601_088 / 1e12
+    # ... its fp32 training step through the public API (render_rays -> loss.backward(): composite + trunk backward
+    # kernels of head.cu; torch.optim.Adam on the 22 tensors), 4096 rays x 64 fenceposts
+    hopt = torch.optim.Adam(hm.parameters(), lr=1e-4)
+    hg = torch.Generator(device="cpu").manual_seed(8)
+    ho = (torch.randn(RAYS, 3, generator=hg) * 2).to(dev); hd = torch.randn(RAYS, 3, generator=hg).to(dev)
+    htgt = torch.rand(RAYS, 3, generator=hg).to(dev); hlab = torch.randint(0, 50, (RAYS,), generator=hg).to(dev)
+
+    def head_step(i):
+        hopt.zero_grad(set_to_none=True)
+        himg, hseg = hm.render_rays(ho, hd, SAMPLES, randomly_sample=True, density_noise_std=1.0, seed=i)
+        hl = ((himg[:, 0] - htgt) ** 2).mean() + torch.nn.functional.nll_loss(hseg[:, 0], hlab)
+        hl.backward(); hopt.step()
+    head_step(0)
+    ms_ht = timed_steps(head_step, 3, flush)
+    head_train_rps = RAYS / (float(np.mean(ms_ht)) * 1e-3)
     # ... and its tcgen05 bf16 path (head_tc.cu): 800x800
     torch.manual_seed(3)
     hb = HeadNeRF(precision="bf16").to(dev)
@@ -456,6 +471,9 @@ def run_ours(args):
             "kernels": kernels,
             "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
                             "mlp_tflops": head_tflops},
+            "head_train_fp32": {"value": head_train_rps, "unit": "rays/s", "ms_per_step": float(np.mean(ms_ht)),
+                                "workload": f"HEAD (mip-NeRF) train step fwd+bwd+Adam, {RAYS} rays x {SAMPLES} fenceposts, fp32 FFMA (head.cu), colour MSE + segmentation NLL",
+                                "mlp_tflops": head_train_rps * (SAMPLES - 1) * 1_754_112 / 1e12},
             "head_render_bf16": {"value": headb_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hbh}x{hbh} x {SAMPLES} fenceposts render_image, tcgen05 bf16 (head_tc_kernel)",
                                  "mlp_tflops": headb_tflops, "frac_tensor": headb_tflops / tensor_peak},
             "loss": loss_val,

@@ -286,6 +286,26 @@ int nerf_head_composite(const float* out, int n_out, int n_seg, const float* poi
                         float noise_std, int64_t B, int S, float* pixels, float* seg_out, float* weights,
                         int seg_is_log_softmax, void* stream);
 
+/* Backward of the HEAD generation in fp32: autograd of NeRF.render_rays (nerf/model.py:596-668) w.r.t. the 22
+ * prediction_heads tensors.  The reference has no training script for this generation; its nn.Module is
+ * differentiable through torch autograd, and these entry points are that backward.
+ *   nerf_head_mlp_fwd_train: nerf_head_mlp_fwd that keeps every unit's normalised output and LayerNorm
+ *     statistics in the workspace (nerf_head_mlp_train_workspace_bytes(P): 7 x [P,256] + 10 x [P] floats).
+ *   nerf_head_composite_bwd: gradients d_pixels [B,3] / d_seg [B,n_seg] (either may be NULL = zero) of
+ *     nerf_head_composite's outputs -> d_out [B*S, ldo] rows (density | colour | segmentation logits | zero pad),
+ *     ldo a multiple of 4, >= n_out.  seg_fwd [B,n_seg] is the forward's seg_out.  S <= 3072.
+ *   nerf_head_mlp_bwd: d_out [P, ldo = 64] -> grads_host: HOST array of 22 DEVICE pointers shaped like
+ *     params_host; gradients are ACCUMULATED (zero them first).  workspace = the one nerf_head_mlp_fwd_train filled. */
+int64_t nerf_head_mlp_train_workspace_bytes(int64_t P);
+int nerf_head_mlp_fwd_train(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
+                            float* out, void* workspace, int64_t workspace_bytes, void* stream);
+int nerf_head_composite_bwd(const float* out, int n_out, int n_seg, const float* points, const float* noise,
+                            float noise_std, int64_t B, int S, const float* seg_fwd, const float* d_pixels,
+                            const float* d_seg, float* d_out, int ldo, void* stream);
+int nerf_head_mlp_bwd(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
+                      const float* d_out, int ldo, float* const* grads_host, void* workspace,
+                      int64_t workspace_bytes, void* stream);
+
 /* -------------------------------------------------------------- optimiser --- */
 
 /* torch.optim.Adam(lr, betas, eps) step over a flat buffer

@@ -54,6 +54,10 @@ SIGNATURES = {
     "nerf_head_pack_weights": (c_i, [c_p, c_i, c_i, c_p, c_p]),
     "nerf_head_fwd_tc": (c_i, [c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_i, c_i, c_i, c_i, c_p, c_p, c_p]),
     "nerf_head_composite": (c_i, [c_p, c_i, c_i, c_p, c_p, c_f, c_l, c_i, c_p, c_p, c_p, c_i, c_p]),
+    "nerf_head_mlp_train_workspace_bytes": (c_l, [c_l]),
+    "nerf_head_mlp_fwd_train": (c_i, [c_p, c_p, c_l, c_i, c_i, c_p, c_p, c_l, c_p]),
+    "nerf_head_composite_bwd": (c_i, [c_p, c_i, c_i, c_p, c_p, c_f, c_l, c_i, c_p, c_p, c_p, c_p, c_i, c_p]),
+    "nerf_head_mlp_bwd": (c_i, [c_p, c_p, c_l, c_i, c_i, c_p, c_i, c_p, c_p, c_l, c_p]),
     "nerf_adam_step": (c_i, [c_p, c_p, c_p, c_p, c_l, c_l, c_f, c_f, c_f, c_f, c_f, c_p]),
     "nerf_mse_loss": (c_i, [c_p, c_p, c_l, c_p, c_p, c_p]),
     "nerf_composite_mse_train": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_u64, c_l, c_p, c_p, c_p, c_p, c_p]),

@@ -190,3 +190,286 @@ extern "C" int nerf_head_composite(const float* out, int n_out, int n_seg, const
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
+
+// ============================================================ HEAD backward (fp32) ====
+// The reference ships no training script for this generation, but its model is an nn.Module whose
+// render_rays is differentiable (autograd through nerf/model.py:596-668); these kernels are that
+// backward: composite (colour + segmentation logsumexp) -> output Linear -> 5 x (ReLU, LayerNorm, Linear).
+#include "mlp_fp32_rows.cuh"
+
+// ---- autograd of nerf/model.py:652-663 w.r.t. the trunk's output rows -----------------------------
+//   pixel_c = sum_k w_k sigmoid(c_kc),   seg_c = logsumexp_k v_kc,  v_kc = log(w_k + 1e-10) + log_softmax(x_k)_c
+//   d c_kc = dP_c w_k s (1 - s)
+//   d v_kc = dS_c exp(v_kc - seg_c);  d x_kc = d v_kc - softmax(x_k)_c sum_c' d v_kc'
+//   d w_k  = sum_c dP_c s_kc + (sum_c d v_kc) / (w_k + 1e-10)
+//   w_k = (1 - a_k) T_k, T_k = prod_{j<k} (a_j + 1e-10):
+//   d a_k  = -T_k d w_k + (sum_{j>k} d w_j w_j) / (a_k + 1e-10);   d sigma_k = [sigma_k > 0] (-delta_k a_k) d a_k
+// One warp per ray, per-ray scratch (a, T, d w, -delta a mask) in shared memory: pass A lane = sample
+// (forward product scan, colour terms), pass B lane = class (one sample row at a time, coalesced),
+// pass C lane = sample in reverse (suffix-sum scan).  d_out rows are [P, ldo] with the columns past
+// n_out zeroed: the row layout the trunk's weight-gradient / data-gradient tiles read with 16-byte loads.
+__global__ void __launch_bounds__(256) head_composite_bwd_kernel(
+        const float* __restrict__ out, int n_out, int n_seg, const float* __restrict__ points,
+        const float* __restrict__ noise, float noise_std, int64_t B, int S,
+        const float* __restrict__ seg_fwd, const float* __restrict__ d_pixels, const float* __restrict__ d_seg,
+        float* __restrict__ d_out, int ldo) {
+    extern __shared__ float head_bwd_sm[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    float* sa = head_bwd_sm + (size_t)wib * 4 * S; float* sT = sa + S; float* sdw = sT + S; float* sfac = sdw + S;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < B; ray += warps) {
+        const int64_t base = ray * S;
+        float dP[3] = {0.f, 0.f, 0.f};
+        if (d_pixels) { dP[0] = d_pixels[ray * 3]; dP[1] = d_pixels[ray * 3 + 1]; dP[2] = d_pixels[ray * 3 + 2]; }
+        // ---- pass A: forward transmittance scan, colour gradients, d w (colour part) ----
+        float carry = 1.0f;
+        for (int s0 = 0; s0 < S; s0 += 32) {
+            const int k = s0 + lane; const bool valid = k < S;
+            float a = 1.0f, ae = 1.0f, fac = 0.f;
+            if (valid) {
+                float sg = out[(base + k) * n_out];
+                if (noise) sg = __fadd_rn(sg, __fmul_rn(noise[base + k], noise_std));
+                float dl = NERF_LAST_DIST;
+                if (k < S - 1) {
+                    const float* p0 = points + (base + k) * 3;
+                    const float dx = __fsub_rn(p0[3], p0[0]), dy = __fsub_rn(p0[4], p0[1]), dz = __fsub_rn(p0[5], p0[2]);
+                    dl = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+                }
+                a = expf(__fmul_rn(-fmaxf(sg, 0.f), dl));
+                ae = __fadd_rn(a, NERF_EPS_T);
+                fac = sg > 0.f ? -dl * a : 0.f;
+            }
+            float incl = ae;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { float n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl *= n; }
+            const float prev = __shfl_up_sync(0xffffffffu, incl, 1);
+            const float T = carry * (lane == 0 ? 1.0f : prev);
+            carry = carry * __shfl_sync(0xffffffffu, incl, 31);
+            if (valid) {
+                const float w = __fmul_rn(__fsub_rn(1.0f, a), T);
+                const float* c = out + (base + k) * n_out + 1;
+                float* g = d_out + (base + k) * (int64_t)ldo;
+                float dwc = 0.f;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    const float s = 1.0f / (1.0f + expf(-c[ch]));
+                    dwc = fmaf(dP[ch], s, dwc);
+                    g[1 + ch] = dP[ch] * w * s * (1.0f - s);
+                }
+                sa[k] = a; sT[k] = T; sdw[k] = dwc; sfac[k] = fac;
+            }
+        }
+        __syncwarp();
+        // ---- pass B: segmentation logsumexp, lane = class ----
+        const bool seg_on = n_seg > 0 && d_seg != nullptr;
+        float sc0 = 0.f, sc1 = 0.f, dS0 = 0.f, dS1 = 0.f;
+        if (seg_on) {
+            if (lane < n_seg) { sc0 = seg_fwd[ray * n_seg + lane]; dS0 = d_seg[ray * n_seg + lane]; }
+            if (lane + 32 < n_seg) { sc1 = seg_fwd[ray * n_seg + lane + 32]; dS1 = d_seg[ray * n_seg + lane + 32]; }
+        }
+        for (int k = 0; k < S; ++k) {
+            float* g = d_out + (base + k) * (int64_t)ldo + 4;
+            float dx0 = 0.f, dx1 = 0.f;
+            if (seg_on) {
+                const float w = __fmul_rn(__fsub_rn(1.0f, sa[k]), sT[k]);
+                const float we = __fadd_rn(w, 1e-10f);
+                const float lw = logf(we);
+                const float* row = out + (base + k) * n_out + 4;
+                const float x0 = lane < n_seg ? row[lane] : -INFINITY;
+                const float x1 = lane + 32 < n_seg ? row[lane + 32] : -INFINITY;
+                const float m = warp_max(fmaxf(x0, x1));
+                const float e0 = expf(x0 - m), e1 = expf(x1 - m);
+                const float se = warp_sum(e0 + e1);
+                const float lse = m + logf(se);
+                const float dv0 = lane < n_seg ? dS0 * expf(lw + (x0 - lse) - sc0) : 0.f;
+                const float dv1 = lane + 32 < n_seg ? dS1 * expf(lw + (x1 - lse) - sc1) : 0.f;
+                const float sum = warp_sum(dv0 + dv1);
+                dx0 = dv0 - (e0 / se) * sum; dx1 = dv1 - (e1 / se) * sum;
+                if (lane == 0) sdw[k] += sum / we;
+            }
+            if (4 + lane < ldo) g[lane] = lane < n_seg ? dx0 : 0.f;
+            if (4 + lane + 32 < ldo) g[lane + 32] = lane + 32 < n_seg ? dx1 : 0.f;
+        }
+        __syncwarp();
+        // ---- pass C: reverse suffix sums of d w_j w_j, density gradient ----
+        float R = 0.f;
+        for (int s0 = ((S - 1) / 32) * 32; s0 >= 0; s0 -= 32) {
+            const int k = s0 + lane; const bool valid = k < S;
+            float a = 1.f, T = 0.f, dw = 0.f, fac = 0.f;
+            if (valid) { a = sa[k]; T = sT[k]; dw = sdw[k]; fac = sfac[k]; }
+            const float x = dw * __fmul_rn(__fsub_rn(1.0f, a), T);
+            float incl = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { float n = __shfl_down_sync(0xffffffffu, incl, o); if (lane + o < 32) incl += n; }
+            float excl = __shfl_down_sync(0xffffffffu, incl, 1); if (lane == 31) excl = 0.f;
+            if (valid) {
+                const float da = -T * dw + (R + excl) / __fadd_rn(a, NERF_EPS_T);
+                d_out[(base + k) * (int64_t)ldo] = fac == 0.f ? 0.f : da * fac;
+            }
+            R += __shfl_sync(0xffffffffu, incl, 0);
+        }
+        __syncwarp();
+    }
+}
+
+extern "C" int nerf_head_composite_bwd(const float* out, int n_out, int n_seg, const float* points, const float* noise,
+                                       float noise_std, int64_t B, int S, const float* seg_fwd, const float* d_pixels,
+                                       const float* d_seg, float* d_out, int ldo, void* stream) {
+    if (B == 0 && S > 0) return NERF_OK;
+    if (!out || !points || !d_out || B < 0 || S <= 0 || n_seg < 0 || n_seg > 64 || n_out != 4 + n_seg || ldo < n_out || (ldo & 3))
+        return NERF_ERR_BAD_ARG;
+    if (d_seg && !seg_fwd) return NERF_ERR_BAD_ARG;
+    if (B == 0) return NERF_OK;
+    if (S > 3072) return NERF_ERR_UNSUPPORTED;                   // per-ray scratch must fit 48 KB
+    int wpb = (int)(49152 / (16 * (int64_t)S)); if (wpb > 8) wpb = 8; if (wpb < 1) wpb = 1;
+    int64_t blocks = (B + wpb - 1) / wpb, cap = (int64_t)nerf_num_sms() * 32;
+    head_composite_bwd_kernel<<<(unsigned)(blocks < cap ? blocks : cap), wpb * 32, (size_t)wpb * 16 * S, (cudaStream_t)stream>>>(
+        out, n_out, n_seg, points, noise, noise_std, B, S, seg_fwd, d_pixels, d_seg, d_out, ldo);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+// ---- one trunk unit's ReLU + LayerNorm backward (unit = Linear -> LayerNorm -> ReLU, model.py:525-540) ----
+//   y = relu(gamma n + beta):  da = [gamma n + beta > 0] dy;  d gamma += da n;  d beta += da
+//   dz = rstd (dn - mean(dn) - n mean(dn n)),  dn = da gamma;  d bias += dz
+// One warp per point row, block reduction of the column sums through shared atomics.
+__global__ void __launch_bounds__(256) head_row_bwd_kernel(
+        const float* __restrict__ G, const float* __restrict__ n, const float* __restrict__ rstd,
+        const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ dz_out,
+        float* __restrict__ d_gamma, float* __restrict__ d_beta, float* __restrict__ d_bias, int64_t P) {
+    __shared__ float red[3 * HID];
+    const int lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 3 * HID; i += blockDim.x) red[i] = 0.f;
+    __syncthreads();
+    float g[8], bt[8], s_dg[8], s_db[8], s_dbias[8];
+    load_row8(gamma, lane, g); load_row8(beta, lane, bt);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s_dg[j] = 0.f; s_db[j] = 0.f; s_dbias[j] = 0.f; }
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t m = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < P; m += warps) {
+        float nn[8], dy[8], dn[8], c1 = 0.f, c2 = 0.f;
+        load_row8(n + m * HID, lane, nn); load_row8(G + m * HID, lane, dy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float da = fmaf(g[j], nn[j], bt[j]) > 0.f ? dy[j] : 0.f;
+            s_dg[j] = fmaf(da, nn[j], s_dg[j]); s_db[j] += da;
+            dn[j] = da * g[j]; c1 += dn[j]; c2 = fmaf(dn[j], nn[j], c2);
+        }
+        c1 = warp_sum(c1) * (1.0f / HID); c2 = warp_sum(c2) * (1.0f / HID);
+        const float rs = rstd[m];
+        float dz[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { dz[j] = rs * (dn[j] - c1 - nn[j] * c2); s_dbias[j] += dz[j]; }
+        store_row8(dz_out + m * HID, lane, dz);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int col = col_of(lane, j);
+        atomicAdd(&red[col], s_dg[j]); atomicAdd(&red[HID + col], s_db[j]); atomicAdd(&red[2 * HID + col], s_dbias[j]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < HID; i += blockDim.x) {
+        atomicAdd(d_gamma + i, red[i]); atomicAdd(d_beta + i, red[HID + i]); atomicAdd(d_bias + i, red[2 * HID + i]);
+    }
+}
+
+// column sums of d_out [P, ldo] -> bias gradient of the output Linear (first n_out columns)
+__global__ void __launch_bounds__(256) head_colsum_kernel(const float* __restrict__ d_out, int ldo, int n_out, int64_t P,
+                                                          float* __restrict__ d_bias) {
+    __shared__ float red[64];
+    if (threadIdx.x < 64) red[threadIdx.x] = 0.f;
+    __syncthreads();
+    const int col = threadIdx.x & 63, rg = threadIdx.x >> 6;
+    float s = 0.f;
+    if (col < n_out)
+        for (int64_t m = (int64_t)blockIdx.x * 4 + rg; m < P; m += (int64_t)gridDim.x * 4) s += d_out[m * ldo + col];
+    atomicAdd(&red[col], s);
+    __syncthreads();
+    if (threadIdx.x < n_out) atomicAdd(d_bias + threadIdx.x, red[threadIdx.x]);
+}
+
+// Training workspace (floats): n[5][P*256] | mu[5][P] | rstd[5][P] | G[P*256] | dz[P*256]
+struct HeadWs { float* n[5]; float* mu[5]; float* rstd[5]; float* G; float* dz; };
+static int64_t head_carve(int64_t P, void* base, HeadWs* ws) {
+    const int64_t act = (P * HID + 63) & ~(int64_t)63, vec = (P + 63) & ~(int64_t)63;
+    float* b = (float*)base; int64_t o = 0;
+    for (int l = 0; l < 5; ++l) { if (ws) ws->n[l] = b + o; o += act; }
+    for (int l = 0; l < 5; ++l) { if (ws) ws->mu[l] = b + o; o += vec; }
+    for (int l = 0; l < 5; ++l) { if (ws) ws->rstd[l] = b + o; o += vec; }
+    if (ws) ws->G = b + o; o += act;
+    if (ws) ws->dz = b + o; o += act;
+    return o * (int64_t)sizeof(float);
+}
+
+extern "C" int64_t nerf_head_mlp_train_workspace_bytes(int64_t P) {
+    if (P < 0) return NERF_ERR_BAD_ARG;
+    return head_carve(P, nullptr, nullptr);
+}
+
+extern "C" int nerf_head_mlp_fwd_train(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
+                                       float* out, void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!params_host || !feat || !out || P < 0 || n_in <= 0 || (n_in & 3) || n_out <= 0 || n_out > 64) return NERF_ERR_BAD_ARG;
+    if (P == 0) return NERF_OK;
+    HeadWs ws; if (!workspace || head_carve(P, workspace, &ws) > workspace_bytes) return NERF_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned tiles = (unsigned)((P + BM - 1) / BM);
+    for (int l = 0; l < 5; ++l) {
+        ASource s{};
+        s.row_div2 = 1;
+        if (l == 0) { s.seg2 = feat; s.K2 = n_in; }
+        else { s.n_prev = ws.n[l - 1]; s.gamma = params_host[4 * (l - 1) + 2]; s.beta = params_host[4 * (l - 1) + 3]; s.K1 = HID; s.relu = 1; }
+        mlp_tile_kernel<MODE_FWD_LN><<<tiles, 256, 0, st>>>(s, params_host[4 * l], l == 0 ? n_in : HID, params_host[4 * l + 1],
+                                                           ws.n[l], ws.mu[l], ws.rstd[l], P, HID);
+        NERF_CUDA_CHECK_LAUNCH();
+    }
+    ASource s{};
+    s.row_div2 = 1; s.n_prev = ws.n[4]; s.gamma = params_host[18]; s.beta = params_host[19]; s.K1 = HID; s.relu = 1;
+    mlp_tile_kernel<MODE_LINEAR><<<tiles, 256, 0, st>>>(s, params_host[20], HID, params_host[21], out, nullptr, nullptr, P, n_out);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int nerf_head_mlp_bwd(const float* const* params_host, const float* feat, int64_t P, int n_in, int n_out,
+                                 const float* d_out, int ldo, float* const* grads_host, void* workspace,
+                                 int64_t workspace_bytes, void* stream) {
+    if (!params_host || !grads_host || !feat || !d_out || P < 0 || n_in <= 0 || (n_in & 3) || n_out <= 0 || n_out > 64 || ldo != 64)
+        return NERF_ERR_BAD_ARG;
+    if (P == 0) return NERF_OK;
+    HeadWs ws; if (!workspace || head_carve(P, workspace, &ws) > workspace_bytes) return NERF_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned tiles = (unsigned)((P + BM - 1) / BM);
+    const int64_t rows_per_split = 4096, splits = (P + rows_per_split - 1) / rows_per_split;
+    int64_t rb = (P + 7) / 8, cap = (int64_t)nerf_num_sms() * 4;
+    const unsigned rgrid = (unsigned)(rb < cap ? rb : cap);
+    // output Linear: d b5, d W5 = d_out^T relu(gamma4 n4 + beta4), G = d_out W5
+    {
+        int64_t cb = (P + 3) / 4; if (cb > cap) cb = cap;
+        head_colsum_kernel<<<(unsigned)cb, 256, 0, st>>>(d_out, ldo, n_out, P, grads_host[21]);
+        NERF_CUDA_CHECK_LAUNCH();
+        ASource src{}; src.row_div2 = 1; src.n_prev = ws.n[4]; src.gamma = params_host[18]; src.beta = params_host[19]; src.K1 = HID; src.relu = 1;
+        dim3 wg(HID / 64, 1, (unsigned)splits);
+        mlp_wgrad_kernel<<<wg, 256, 0, st>>>(d_out, src, HID, grads_host[20], P, rows_per_split, ldo, n_out);
+        NERF_CUDA_CHECK_LAUNCH();
+        ASource d{}; d.n_prev = d_out; d.K1 = ldo;
+        mlp_tile_kernel<MODE_DGRAD><<<tiles, 256, 0, st>>>(d, params_host[20], HID, nullptr, ws.G, nullptr, nullptr, P, n_out);
+        NERF_CUDA_CHECK_LAUNCH();
+    }
+    for (int l = 4; l >= 0; --l) {
+        head_row_bwd_kernel<<<rgrid, 256, 0, st>>>(ws.G, ws.n[l], ws.rstd[l], params_host[4 * l + 2], params_host[4 * l + 3], ws.dz,
+                                                  grads_host[4 * l + 2], grads_host[4 * l + 3], grads_host[4 * l + 1], P);
+        NERF_CUDA_CHECK_LAUNCH();
+        ASource src{}; src.row_div2 = 1;
+        if (l == 0) { src.seg2 = feat; src.K2 = n_in; }
+        else { src.n_prev = ws.n[l - 1]; src.gamma = params_host[4 * (l - 1) + 2]; src.beta = params_host[4 * (l - 1) + 3]; src.K1 = HID; src.relu = 1; }
+        const int Kt = l == 0 ? n_in : HID;
+        dim3 wg((unsigned)((Kt + 63) / 64), HID / 64, (unsigned)splits);
+        mlp_wgrad_kernel<<<wg, 256, 0, st>>>(ws.dz, src, Kt, grads_host[4 * l], P, rows_per_split);
+        NERF_CUDA_CHECK_LAUNCH();
+        if (l > 0) {
+            ASource d{}; d.n_prev = ws.dz; d.K1 = HID;
+            mlp_tile_kernel<MODE_DGRAD><<<tiles, 256, 0, st>>>(d, params_host[4 * l], HID, nullptr, ws.G, nullptr, nullptr, P);
+            NERF_CUDA_CHECK_LAUNCH();
+        }
+    }
+    return NERF_OK;
+}

@@ -4,7 +4,8 @@
 //               epilogue = +bias, ReLU, LayerNorm statistics, normalise  (the whole
 //               Linear->ReLU->LayerNorm unit of SURVEY A.3 without its affine, which
 //               the NEXT consumer applies when it loads the row)
-//   MODE_DGRAD: A = dz, B = W[:, :256] (natural), epilogue = plain store.
+//   MODE_DGRAD: A = dz [P, lda = src.K1], B = W[:n_out, :256] (natural rows; n_out = rows of W = width of dz,
+//               256 for a trunk unit, 54 for HEAD's output Linear), epilogue = plain store.
 //   MODE_FWD_LN: HEAD trunk unit Linear->LayerNorm->ReLU (nerf/model.py:525-542): epilogue = +bias,
 //               LayerNorm statistics, normalise; the consumer applies the affine AND the ReLU on load
 //               (ASource.relu).   MODE_LINEAR: plain Linear with n_out <= 256 outputs (HEAD's 256->54).
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
     __shared__ __align__(16) float Bs[2][BK][HID];
     const int tid = threadIdx.x, tx = tid & 31, ty = tid >> 5;
     const int64_t row0 = (int64_t)blockIdx.x * BM;
-    const int K = IS_FWD ? (src.K1 + src.K2) : HID;
+    const int K = IS_FWD ? (src.K1 + src.K2) : n_out;
     const int nchunks = (K + BK - 1) / BK;
 
     float acc[8][8];
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
         {   // A tile: 64 rows x 16 k, one float4 per thread
             const int r = tid >> 2, kq = (tid & 3) * 4;
             if (IS_FWD) ra = load_a4(src, row0 + r, k0 + kq, P);
-            else ra = (row0 + r < P) ? *reinterpret_cast<const float4*>(src.n_prev + (row0 + r) * HID + k0 + kq)
+            else ra = (row0 + r < P && k0 + kq < src.K1) ? *reinterpret_cast<const float4*>(src.n_prev + (row0 + r) * src.K1 + k0 + kq)
                                      : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         if (IS_FWD) {     // B[k][n] = W[n][k]: thread = output feature n, 16 consecutive k
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 int idx = tid + q * 256; int kk = idx >> 6, j4 = (idx & 63) * 4;
-                rb[q] = *reinterpret_cast<const float4*>(W + (size_t)(k0 + kk) * Kt + j4);
+                rb[q] = (k0 + kk < n_out) ? *reinterpret_cast<const float4*>(W + (size_t)(k0 + kk) * Kt + j4) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
     };
@@ -178,9 +179,10 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
 
 // ---- weight gradient: dW[n][k] += sum_m dz[m][n] * x[m][k],  x = [gamma*n_prev+beta | seg2] ----
 // 64(n) x 64(k) tile per CTA, rows [m_begin, m_end) reduced in chunks of 16, atomics at the end.
+// dz is [P, ldz] and only its first n_rows columns are weight rows (HEAD's output Linear: ldz 64, 54 rows).
 static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
         const float* __restrict__ dz, ASource src, int Kt, float* __restrict__ dW,
-        int64_t P, int64_t rows_per_split) {
+        int64_t P, int64_t rows_per_split, int ldz = HID, int n_rows = HID) {
     __shared__ __align__(16) float As[2][BK][64];
     __shared__ __align__(16) float Bs[2][BK][64];
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
@@ -197,7 +199,7 @@ static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
     float4 ra, rb;
     auto gload = [&](int64_t m0) {
         int64_t m = m0 + lr;
-        ra = (m < m_end) ? *reinterpret_cast<const float4*>(dz + m * HID + n0 + lc) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ra = (m < m_end) ? *reinterpret_cast<const float4*>(dz + m * ldz + n0 + lc) : make_float4(0.f, 0.f, 0.f, 0.f);
         rb = (m < m_end) ? load_a4(src, m, k0 + lc, P) : make_float4(0.f, 0.f, 0.f, 0.f);
     };
     auto sstore = [&](int buf) {
@@ -227,6 +229,6 @@ static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int n = n0 + ty * 4 + i, k = k0 + tx * 4 + j;
-            if (k < Kt) atomicAdd(dW + (size_t)n * Kt + k, acc[i][j]);
+            if (k < Kt && n < n_rows) atomicAdd(dW + (size_t)n * Kt + k, acc[i][j]);
         }
 }

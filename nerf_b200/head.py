@@ -2,8 +2,11 @@
 style integrated positional encoding, a Linear->LayerNorm->ReLU trunk and a 1+3+50 output head with a
 segmentation composite.  Same constructor, method names, argument meaning, return shapes and
 state_dict keys as the reference class (nerf/model.py:471-770); every arithmetic stage is a kernel of
-libnerf_b200.so (csrc/head.cu, csrc/rays.cu).  Inference only: the reference ships no training entry
-point for this generation (train_conditional_nerf.py and the notebook drive the G1/G2 API).
+libnerf_b200.so (csrc/head.cu, csrc/rays.cu).  The reference ships no training entry point for this
+generation (train_conditional_nerf.py and the notebook drive the G1/G2 API), but its module is
+differentiable: in fp32 mode `render_rays` called with autograd enabled records ONE autograd node
+(`_HeadRenderFn`) whose backward is the composite + trunk backward kernels of csrc/head.cu, so
+`loss.backward()` fills `.grad` of the 22 prediction_heads tensors exactly as it does on the reference.
 """
 import ctypes
 import math
@@ -16,6 +19,62 @@ from ._lib import check, lib, ptr, stream
 from .model import NeRF as _G1
 
 LOG2_NEAR = -9.43633744014          # nerf/model.py:414
+
+
+LDO = 64        # row stride of the output-row gradients (n_out <= 64, zero padded): 16-byte loads in the tiles
+
+
+class _HeadRenderFn(torch.autograd.Function):
+    """render_rays of the HEAD generation (nerf/model.py:596-668) as one autograd node over the 22
+    prediction_heads tensors: forward = encoder + trunk (activations kept) + composite, backward =
+    nerf_head_composite_bwd + nerf_head_mlp_bwd.  Rays and fenceposts get no gradient (they depend on no
+    parameter)."""
+
+    @staticmethod
+    def forward(ctx, model, o, d, t, noise, noise_std, *params):
+        b, s = t.shape
+        s1 = s - 1
+        n_seg = model.segmentation_outputs
+        n_out = 1 + model.color_outputs + n_seg
+        if n_out > LDO:
+            raise ValueError("HEAD training supports at most 60 segmentation outputs")
+        mean, _, feat = model.integrated_pe(o, d, t)
+        feat = feat.view(b * s1, -1)
+        ptrs, keep = model._param_pointers()
+        nbytes = lib().nerf_head_mlp_train_workspace_bytes(b * s1)
+        ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=t.device)
+        out = torch.empty(b * s1, n_out, device=t.device)
+        check(lib().nerf_head_mlp_fwd_train(ptrs, ptr(feat), b * s1, feat.shape[1], n_out, ptr(out), ptr(ws), nbytes, stream()),
+              "nerf_head_mlp_fwd_train")
+        img = torch.empty(b, 3, device=t.device); seg = torch.empty(b, n_seg, device=t.device)
+        mean = mean.view(b, s1, 3).contiguous()
+        check(lib().nerf_head_composite(ptr(out), n_out, n_seg, ptr(mean), ptr(noise), float(noise_std), b, s1,
+                                        ptr(img), ptr(seg), None, 0, stream()), "nerf_head_composite")
+        ctx.model, ctx.noise_std, ctx.shape = model, float(noise_std), (b, s1, n_out, n_seg)
+        ctx.noise = noise
+        ctx.save_for_backward(out, mean, feat, ws, seg, *params)
+        return img, seg
+
+    @staticmethod
+    def backward(ctx, d_img, d_seg):
+        out, mean, feat, ws, seg, *params = ctx.saved_tensors
+        b, s1, n_out, n_seg = ctx.shape
+        d_img = ops._f32c(d_img) if d_img is not None else None
+        d_seg = ops._f32c(d_seg) if (d_seg is not None and n_seg > 0) else None
+        d_out = torch.empty(b * s1, LDO, device=out.device)
+        check(lib().nerf_head_composite_bwd(ptr(out), n_out, n_seg, ptr(mean), ptr(ctx.noise), ctx.noise_std, b, s1,
+                                            ptr(seg), ptr(d_img), ptr(d_seg), ptr(d_out), LDO, stream()),
+              "nerf_head_composite_bwd")
+        sizes = [p.numel() for p in params]
+        flat = torch.zeros(sum((n + 3) // 4 * 4 for n in sizes), device=out.device)      # 16-byte aligned views
+        grads, off = [], 0
+        for p, n in zip(params, sizes):
+            grads.append(flat[off:off + n].view_as(p)); off += (n + 3) // 4 * 4
+        pp = (ctypes.c_void_p * 22)(*[p.data_ptr() for p in params])
+        gp = (ctypes.c_void_p * 22)(*[g.data_ptr() for g in grads])
+        check(lib().nerf_head_mlp_bwd(pp, ptr(feat), b * s1, feat.shape[1], n_out, ptr(d_out), LDO, gp, ptr(ws),
+                                      ws.numel(), stream()), "nerf_head_mlp_bwd")
+        return (None,) * 6 + tuple(grads)
 
 
 class HeadNeRF(nn.Module):
@@ -134,10 +193,26 @@ class HeadNeRF(nn.Module):
         density, color, seg = out.split([1, self.color_outputs, self.segmentation_outputs], dim=-1)
         return mean, density, color, seg
 
-    @torch.no_grad()
     def render_rays(self, rays_o, rays_d, num_samples, states_x=None, states_d=None,
                     randomly_sample=False, density_noise_std=0.0, u=None, noise=None, seed=0):
-        """nerf/model.py:596-668 -> (image [B,1,3], segmentation [B,1,n_seg])."""
+        """nerf/model.py:596-668 -> (image [B,1,3], segmentation [B,1,n_seg]).  With autograd enabled and
+        parameters that require grad (fp32 mode) the result carries the graph of `_HeadRenderFn`; the
+        tcgen05 (bf16) form is inference only."""
+        params = list(self.prediction_heads.parameters())
+        if torch.is_grad_enabled() and self.precision == "fp32" and any(p.requires_grad for p in params):
+            with torch.no_grad():
+                o = ops._f32c(rays_o.reshape(-1, 3)); d = ops._f32c(rays_d.reshape(-1, 3))
+                b, s1 = o.shape[0], num_samples - 1
+                t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)
+                if noise is None and density_noise_std != 0.0:   # the reference draws torch.randn here (:652)
+                    noise = torch.randn(b, s1, device=o.device)
+                nz = ops._f32c(noise.reshape(b, s1)) if noise is not None else None
+            img, seg = _HeadRenderFn.apply(self, o, d, t, nz, float(density_noise_std), *params)
+            return img.unsqueeze(-2), seg.unsqueeze(-2)
+        with torch.no_grad():
+            return self._render_rays_eval(rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed)
+
+    def _render_rays_eval(self, rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed):
         o = ops._f32c(rays_o.reshape(-1, 3)); d = ops._f32c(rays_d.reshape(-1, 3))
         b = o.shape[0]
         t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)

@@ -65,6 +65,8 @@ def test_head_render_rays(head_model, head_ref):
     o, d = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"])
     img, seg = head_model.render_rays(o, d, 16, randomly_sample=False, density_noise_std=0.0)
     assert img.shape == (6, 1, 3) and seg.shape == (6, 1, 50)
+    assert img.requires_grad            # like the reference: outside no_grad the render carries its autograd graph
+    img, seg = img.detach(), seg.detach()
     err = np.abs(img.cpu().numpy() - head_ref["head_rr_img"]).max()
     print("HEAD render_rays pixel max|diff|", err)
     assert err <= 1e-3
@@ -93,7 +95,9 @@ def test_head_vs_oracle_large(head_model, head_ref):
     u = torch.rand(77, 65, generator=g); noise = torch.randn(77, 64, 1, generator=g)
     with torch.no_grad():
         wi, ws = om.render_rays(o, d, 65, u=u, noise=noise)
-    gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+    with torch.no_grad():
+        gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+    assert not gi.requires_grad
     assert np.abs(gi.cpu().numpy() - wi.numpy()).max() <= 1e-3
     np.testing.assert_allclose(gi.cpu().numpy(), wi.numpy(), rtol=0, atol=2e-5)
     np.testing.assert_allclose(gs.cpu().numpy(), ws.numpy(), rtol=1e-4, atol=1e-3)
@@ -129,7 +133,8 @@ def test_head_tc_render_vs_fp32(head_model, head_model_bf16):
     g = torch.Generator().manual_seed(31)
     o = (torch.randn(301, 3, generator=g) * 2).cuda(); d = torch.randn(301, 3, generator=g).cuda()
     u = torch.rand(301, 48, generator=g).cuda()
-    wi, ws = head_model.render_rays(o, d, 48, u=u)
+    with torch.no_grad():
+        wi, ws = head_model.render_rays(o, d, 48, u=u)
     gi, gs = head_model_bf16.render_rays(o, d, 48, u=u)
     assert gi.shape == wi.shape and gs.shape == ws.shape
     err = (gi - wi).abs().max().item()
@@ -150,3 +155,107 @@ def test_head_tc_render_image_shards(head_model_bf16):
     assert torch.equal(img, img2)
     part, _ = head_model_bf16.render_image(co, cr, 20, 24, 30.0, 33, ray_begin=100, ray_end=333)
     assert torch.allclose(part, img.reshape(-1, 3)[100:333], atol=1e-6)
+
+
+# ------------------------------------------------------------------ fp32 backward ----
+def _rel_l2(a, b):
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def _head_loss(img, seg, target, labels):
+    return ((img[:, 0] - target) ** 2).mean() + torch.nn.functional.nll_loss(seg[:, 0], labels)
+
+
+def test_head_backward_vs_reference(head_model, head_ref):
+    """loss.backward() through render_rays (composite + trunk backward kernels) against the parameter gradients
+    the UNMODIFIED reference's autograd produced (tests/golden/head_grad_ref.npz): deterministic sampling, and
+    stratified sampling + density noise with the reference's own torch.rand / torch.randn draws."""
+    gr = load_golden("head_grad_ref.npz")
+    o, d = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"])
+    target, labels = _cuda(gr["target"]), _cuda(gr["labels"])
+    cases = (("det", dict(randomly_sample=False, density_noise_std=0.0)),
+             ("noisy", dict(u=_cuda(gr["noisy_u"]), noise=_cuda(gr["noisy_noise"]), density_noise_std=1.0)))
+    for tag, kw in cases:
+        head_model.zero_grad()
+        img, seg = head_model.render_rays(o, d, 16, **kw)
+        assert img.requires_grad and seg.requires_grad and img.shape == (6, 1, 3) and seg.shape == (6, 1, 50)
+        np.testing.assert_allclose(img.detach().cpu().numpy(), gr[tag + "_img"], rtol=0, atol=1e-5)
+        np.testing.assert_allclose(seg.detach().cpu().numpy(), gr[tag + "_seg"], rtol=1e-5, atol=1e-4)
+        loss = _head_loss(img, seg, target, labels)
+        loss.backward()
+        np.testing.assert_allclose(loss.item(), gr[tag + "_loss"], rtol=1e-5)
+        worst = 0.0
+        for k, p in head_model.named_parameters():
+            want = gr[f"{tag}_grad/{k}"]
+            assert p.grad is not None and p.grad.shape == want.shape, k
+            worst = max(worst, _rel_l2(p.grad.cpu().numpy(), want))
+            assert _rel_l2(p.grad.cpu().numpy(), want) <= 2e-3, (tag, k, _rel_l2(p.grad.cpu().numpy(), want))
+        print(f"HEAD backward [{tag}] worst per-tensor rel-L2 vs the reference's autograd: {worst:.2e}")
+    head_model.zero_grad()
+
+
+@pytest.mark.parametrize("branch", ["both", "colour", "segmentation"])
+def test_head_backward_vs_oracle_large(head_model, head_ref, branch):
+    """Ragged sizes (77 rays x 64 intervals: two 32-sample segments per ray, partial row tiles) against autograd
+    through the pinned oracle, with either output's gradient absent (NULL d_pixels / d_seg through the ABI)."""
+    from oracle import head as oh
+    om = oh.HeadNeRF()
+    om.load_state_dict({str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]})
+    g = torch.Generator().manual_seed(23)
+    o = torch.randn(77, 3, generator=g) * 2; d = torch.randn(77, 3, generator=g)
+    u = torch.rand(77, 65, generator=g); noise = torch.randn(77, 64, 1, generator=g)
+    target = torch.rand(77, 3, generator=g); labels = torch.randint(0, 50, (77,), generator=g)
+
+    def loss_of(img, seg, tgt, lab):
+        a = ((img[:, 0] - tgt) ** 2).mean() if branch != "segmentation" else 0.0
+        b = torch.nn.functional.nll_loss(seg[:, 0], lab) if branch != "colour" else 0.0
+        return a + b
+
+    wi, ws = om.render_rays(o, d, 65, u=u, noise=noise)
+    loss_of(wi, ws, target, labels).backward()
+    head_model.zero_grad()
+    gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+    loss_of(gi, gs, target.cuda(), labels.cuda()).backward()
+    for (k, p), (_, q) in zip(head_model.named_parameters(), om.named_parameters()):
+        err = _rel_l2(p.grad.cpu().numpy(), q.grad.numpy())
+        assert err <= 2e-3, (branch, k, err)
+    head_model.zero_grad()
+
+
+def test_head_training_reduces_loss(head_ref):
+    """A few Adam steps through the public API (model.render_rays -> loss.backward -> torch.optim.Adam.step)."""
+    from nerf.model import NeRF
+    torch.manual_seed(0)
+    m = NeRF().cuda()
+    m.load_state_dict({str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]}, strict=True)
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(5)
+    o = (torch.randn(512, 3, generator=g) * 2).cuda(); d = torch.randn(512, 3, generator=g).cuda()
+    target = torch.rand(512, 3, generator=g).cuda() * 0.2 + 0.4; labels = torch.randint(0, 50, (512,), generator=g).cuda() % 3
+    losses = []
+    for _ in range(30):
+        opt.zero_grad()
+        img, seg = m.render_rays(o, d, 33)
+        loss = _head_loss(img, seg, target, labels)
+        loss.backward(); opt.step(); losses.append(loss.item())
+    print("HEAD training loss", losses[0], "->", losses[-1])
+    assert np.isfinite(losses).all() and losses[-1] < 0.7 * losses[0]
+
+
+def test_head_backward_abi_edges():
+    """Status codes of the backward entry points: zero rays are no-ops, bad strides / missing forward outputs /
+    short workspaces are refused."""
+    from nerf_b200._lib import lib
+    L = lib()
+    x = torch.zeros(64 * 64, device="cuda")
+    assert L.nerf_head_composite_bwd(None, 54, 50, None, None, 0.0, 0, 15, None, None, None, None, 64, None) == 0
+    assert L.nerf_head_composite_bwd(x.data_ptr(), 54, 50, x.data_ptr(), None, 0.0, 4, 15, None, None, x.data_ptr(), x.data_ptr(), 64, None) == -1
+    assert L.nerf_head_composite_bwd(x.data_ptr(), 54, 50, x.data_ptr(), None, 0.0, 4, 15, None, None, None, x.data_ptr(), 50, None) == -1
+    assert L.nerf_head_composite_bwd(x.data_ptr(), 54, 50, x.data_ptr(), None, 0.0, 1, 4000, None, None, None, x.data_ptr(), 64, None) == -2
+    assert L.nerf_head_mlp_train_workspace_bytes(0) == 0 and L.nerf_head_mlp_train_workspace_bytes(64) == (7 * 64 * 256 + 10 * 64) * 4
+    import ctypes
+    pp = (ctypes.c_void_p * 22)(*[x.data_ptr()] * 22)
+    assert L.nerf_head_mlp_bwd(pp, x.data_ptr(), 0, 96, 54, x.data_ptr(), 64, pp, None, 0, None) == 0
+    assert L.nerf_head_mlp_bwd(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), 56, pp, x.data_ptr(), 1 << 20, None) == -1
+    assert L.nerf_head_mlp_bwd(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), 64, pp, x.data_ptr(), 16, None) == -3
+    assert L.nerf_head_mlp_fwd_train(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), x.data_ptr(), 16, None) == -3

@@ -119,3 +119,24 @@ def test_head_render_vs_reference(head_ref):
                                   max_chunk_size=7)
         np.testing.assert_allclose(img.numpy(), head_ref["head_ri_img"], atol=1e-6)
         np.testing.assert_allclose(seg.numpy(), head_ref["head_ri_seg"], atol=1e-4)
+
+
+def test_head_gradients_vs_reference(head_ref):
+    """Autograd through the HEAD oracle against the UNMODIFIED reference's parameter gradients
+    (tests/golden/head_grad_ref.npz, tests/golden/make_head_grad.py): pins the checker the CUDA backward is
+    compared with at sizes the fixture does not hold."""
+    from oracle import head as oh
+    gr = load_golden("head_grad_ref.npz")
+    m = oh.HeadNeRF()
+    m.load_state_dict({str(k): torch.from_numpy(head_ref["head_sd/" + str(k)]) for k in head_ref["head_keys"]})
+    ro, rd = torch.from_numpy(head_ref["head_ro"]), torch.from_numpy(head_ref["head_rd"])
+    target, labels = torch.from_numpy(gr["target"]), torch.from_numpy(gr["labels"])
+    for tag, kw in (("det", {}), ("noisy", dict(u=torch.from_numpy(gr["noisy_u"]), noise=torch.from_numpy(gr["noisy_noise"])))):
+        m.zero_grad()
+        img, seg = m.render_rays(ro, rd, 16, **kw)
+        loss = ((img[:, 0] - target) ** 2).mean() + torch.nn.functional.nll_loss(seg[:, 0], labels)
+        loss.backward()
+        np.testing.assert_allclose(loss.item(), gr[tag + "_loss"], rtol=1e-6)
+        for k, p in m.named_parameters():
+            want = gr[f"{tag}_grad/{k}"]
+            np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-4, atol=1e-6 * max(1.0, np.abs(want).max()), err_msg=f"{tag} {k}")
