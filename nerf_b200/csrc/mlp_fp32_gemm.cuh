@@ -44,7 +44,7 @@ __device__ __forceinline__ float4 load_a4(const ASource& s, int64_t row, int k, 
 enum { MODE_FWD = 0, MODE_DGRAD = 1, MODE_FWD_LN = 2, MODE_LINEAR = 3 };
 
 template <int MODE>
-__global__ void __launch_bounds__(256) mlp_tile_kernel(
+__global__ void __launch_bounds__(256, 2) mlp_tile_kernel(
         ASource src,                       // FWD: inputs; DGRAD: n_prev = dz, K1 = 256, gamma = null
         const float* __restrict__ W, int Kt,        // weight [256][Kt]
         const float* __restrict__ bias,             // FWD
@@ -58,11 +58,13 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
     const int K = IS_FWD ? (src.K1 + src.K2) : n_out;
     const int nchunks = (K + BK - 1) / BK;
 
-    float acc[8][8];
+    // accumulators as packed pairs: the inner product issues fma.rn.f32x2 (FFMA2, two IEEE fp32 FMAs per
+    // instruction -- same results as scalar FFMA, half the issue slots / register-file reads)
+    float2 acc2[8][4];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < 4; ++j) acc2[i][j] = make_float2(0.f, 0.f);
 
     float4 ra; float4 rb[4];
     auto gload = [&](int chunk) {
@@ -118,17 +120,24 @@ __global__ void __launch_bounds__(256) mlp_tile_kernel(
             float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
             float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][128 + tx * 4]);
             const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-            const float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            const float2 b[4] = {make_float2(b0.x, b0.y), make_float2(b0.z, b0.w), make_float2(b1.x, b1.y), make_float2(b1.z, b1.w)};
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < 8; ++i) {
+                const float2 aa = make_float2(a[i], a[i]);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                for (int j = 0; j < 4; ++j) acc2[i][j] = __ffma2_rn(aa, b[j], acc2[i][j]);
+            }
         }
         if (c + 1 < nchunks) { sstore(buf ^ 1); }
         __syncthreads();
     }
 
     // ---- epilogue: thread owns rows ty*8..+7, columns tx*4..+3 and 128+tx*4..+3 ----
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { acc[i][2 * j] = acc2[i][j].x; acc[i][2 * j + 1] = acc2[i][j].y; }
     if (MODE == MODE_LINEAR) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -190,11 +199,11 @@ static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
     const int64_t m_begin = (int64_t)blockIdx.z * rows_per_split;
     int64_t m_end = m_begin + rows_per_split; if (m_end > P) m_end = P;
     if (m_begin >= m_end) return;
-    float acc[4][4];
+    float2 acc2[4][2];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < 2; ++j) acc2[i][j] = make_float2(0.f, 0.f);
     const int lr = tid >> 4, lc = (tid & 15) * 4;     // loader: row within chunk, column group
     float4 ra, rb;
     auto gload = [&](int64_t m0) {
@@ -214,11 +223,14 @@ static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
         for (int mm = 0; mm < BK; ++mm) {
             float4 a = *reinterpret_cast<const float4*>(&As[buf][mm][ty * 4]);
             float4 b = *reinterpret_cast<const float4*>(&Bs[buf][mm][tx * 4]);
-            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+            const float av[4] = {a.x, a.y, a.z, a.w};
+            const float2 bv[2] = {make_float2(b.x, b.y), make_float2(b.z, b.w)};
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int i = 0; i < 4; ++i) {
+                const float2 aa = make_float2(av[i], av[i]);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+                for (int j = 0; j < 2; ++j) acc2[i][j] = __ffma2_rn(aa, bv[j], acc2[i][j]);
+            }
         }
         if (m0 + BK < m_end) sstore(buf ^ 1);
         __syncthreads();
@@ -229,6 +241,7 @@ static __global__ void __launch_bounds__(256) mlp_wgrad_kernel(
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             int n = n0 + ty * 4 + i, k = k0 + tx * 4 + j;
-            if (k < Kt && n < n_rows) atomicAdd(dW + (size_t)n * Kt + k, acc[i][j]);
+            const float v = (j & 1) ? acc2[i][j >> 1].y : acc2[i][j >> 1].x;
+            if (k < Kt && n < n_rows) atomicAdd(dW + (size_t)n * Kt + k, v);
         }
 }
