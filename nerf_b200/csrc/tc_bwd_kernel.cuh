@@ -112,18 +112,33 @@ __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr
         const uint32_t mask = __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&nbits), shift_bf);
         return *reinterpret_cast<uint32_t*>(&dbf) & mask;
     };
-#pragma unroll 1
-    for (int ch = 0; ch < 8; ++ch) {
-        if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
+    auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t addr = slab + tc::sw128_offset(row, (ch & 1) * 4 + i);
             const uint4 nv = lds128u(addr);
             float2 g0, g1, g2, g3;
-            grad4(r, ch, i * 8, g0, g1); grad4(r, ch, i * 8 + 4, g2, g3);
+            grad4(rc, ch, i * 8, g0, g1); grad4(rc, ch, i * 8 + 4, g2, g3);
             const uint4 o = make_uint4(dz2(g0, nv.x), dz2(g1, nv.y), dz2(g2, nv.z), dz2(g3, nv.w));
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+        }
+    };
+    if (SRC == 2) {
+#pragma unroll 1
+        for (int ch = 0; ch < 8; ++ch) pass2(r, ch);
+    } else {
+        // the next 32 columns of g are in flight while the current ones are turned into dz (static register double buffer)
+        uint32_t rb[32];
+        tc::tmem_ld32(taddr, r); tc::tmem_ld_wait();
+#pragma unroll 1
+        for (int c2 = 0; c2 < 4; ++c2) {
+            tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, rb);
+            pass2(r, 2 * c2);
+            tc::tmem_ld_wait();
+            if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r);
+            pass2(rb, 2 * c2 + 1);
+            tc::tmem_ld_wait();
         }
     }
 }

@@ -25,7 +25,7 @@ __device__ __forceinline__ void tma_store(void* dst, uint32_t src, uint32_t byte
 __device__ __forceinline__ void tma_prefetch(const void* src, uint32_t bytes) { asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory"); }
 
 // chunk = 64 KB moved as 4 x 16 KB requests.  Thread w (one lane of warp w < n_thr) owns chunks w, w + n_thr*grid ... of its CTA.
-__global__ void __launch_bounds__(128, 1) stream_kernel(const uint8_t* src, uint8_t* dst, int n_chunks, int n_thr, int depth, int prefetch, int chunk_kb) {
+__global__ void __launch_bounds__(128, 1) stream_kernel(const uint8_t* src, uint8_t* dst, int n_chunks, int n_thr, int depth, int prefetch, int chunk_kb, int scatter) {
     extern __shared__ __align__(1024) uint8_t sm[];
     const int w = threadIdx.x >> 5;
     if ((threadIdx.x & 31) != 0 || w >= n_thr) return;
@@ -37,10 +37,11 @@ __global__ void __launch_bounds__(128, 1) stream_kernel(const uint8_t* src, uint
     const int stride = gridDim.x * n_thr, first = blockIdx.x * n_thr + w;
     int n_my = 0; for (int c = first; c < n_chunks; c += stride) ++n_my;
     auto issue = [&](int i) {
-        const int c = first + i * stride; const int b = i % depth;
+        int c = first + i * stride; const int b = i % depth;
+        if (scatter) c = (int)(((long long)c * 7919) % n_chunks);
         mbar_expect(bars + 8 * b, CH);
         for (int r = 0; r < 4; ++r) tma_load(base + b * CH + r * RQ, src + (size_t)c * CH + r * RQ, RQ, bars + 8 * b);
-        if (prefetch && i + depth < n_my) tma_prefetch(src + (size_t)(c + depth * stride) * CH, CH);
+        if (prefetch && i + depth < n_my) { int cn = first + (i + depth) * stride; if (scatter) cn = (int)(((long long)cn * 7919) % n_chunks); tma_prefetch(src + (size_t)cn * CH, CH); }
     };
     for (int i = 0; i < depth - 1 && i < n_my; ++i) issue(i);
     for (int i = 0; i < n_my; ++i) {
@@ -52,7 +53,8 @@ __global__ void __launch_bounds__(128, 1) stream_kernel(const uint8_t* src, uint
             issue(i + depth - 1);
         }
         mbar_wait(bars + 8 * b, (i / depth) & 1);
-        const int c = first + i * stride;
+        int c = first + i * stride;
+        if (scatter) c = (int)(((long long)c * 7919) % n_chunks);
         for (int r = 0; r < 4; ++r) tma_store(dst + (size_t)c * CH + r * RQ, base + b * CH + r * RQ, RQ);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         if (depth == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -72,7 +74,8 @@ int main() {
         for (int it = 0; it < 5; ++it) { CK(cudaMemset(flush, it, 256u << 20)); cudaEventRecord(e0); CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice)); cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms; }
         printf("cudaMemcpy D2D                                  : %.3f ms  %.0f GB/s\n", best, 2.0 * bytes / best / 1e6);
     }
-    const int cfg[][4] = {{2, 1, 0, 64}, {2, 1, 1, 64}, {2, 2, 0, 64}, {2, 2, 1, 64}, {3, 1, 1, 64}, {1, 3, 0, 64}, {4, 1, 1, 32}, {4, 2, 0, 16}, {2, 3, 0, 32}, {4, 3, 0, 16}};
+    const int cfg[][4] = {{2, 1, 0, 64}, {2, 1, 1, 64}, {1, 3, 0, 64}, {4, 2, 0, 16}, {2, 3, 0, 32}};
+    for (int scatter = 0; scatter < 2; ++scatter)
     for (auto& c : cfg) {
         const int n_thr = c[0], depth = c[1], pf = c[2], kb = c[3];
         const int n_chunks = (int)(bytes / (kb * 1024));
@@ -82,11 +85,11 @@ int main() {
         for (int it = 0; it < 5; ++it) {
             CK(cudaMemset(flush, it, 256u << 20));
             cudaEventRecord(e0);
-            stream_kernel<<<148, 128, smem>>>(src, dst, n_chunks, n_thr, depth, pf, kb);
+            stream_kernel<<<148, 128, smem>>>(src, dst, n_chunks, n_thr, depth, pf, kb, scatter);
             cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
             float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
         }
-        printf("threads/CTA %d  buffers/thread %d  L2 prefetch %d  chunk %2d KB : %.3f ms  %.0f GB/s\n", n_thr, depth, pf, kb, best, 2.0 * bytes / best / 1e6);
+        printf("%s threads/CTA %d  buffers/thread %d  L2 prefetch %d  chunk %2d KB : %.3f ms  %.0f GB/s\n", scatter ? "scattered " : "sequential", n_thr, depth, pf, kb, best, 2.0 * bytes / best / 1e6);
     }
     return 0;
 }
