@@ -60,7 +60,7 @@ template <int SRC>
 __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr, uint32_t row, uint32_t hw_addr,
                                                float rstd, float shift, float ds, float dr, float dg, float db,
                                                uint32_t nfull_base, uint32_t nf_parity, uint32_t wait_hint, long long* pf = nullptr) {
-    float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
+    float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f), s1b = s1, s2b = s2;
     uint32_t r[32];
     // g for columns [ch*32 + j, +4)
     auto grad4 = [&](const uint32_t (&rc)[32], int ch, int j, float2& g0, float2& g1) {
@@ -87,18 +87,24 @@ __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr
         if ((ch & 1) == 0) { tc::mbar_wait(nfull_base + 8u * (ch >> 1), nf_parity, wait_hint); if (pf) pf[ch >> 1] = clock64(); }
         if (SRC != 2) tc::tmem_ld_wait();
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
+        // the four 16-byte row pieces of the chunk are requested back to back (the asm loads keep program order:
+        // issued one per use they would expose the shared-memory latency 32 times per pass), two sum chains each
+        uint4 nq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) nq[i] = lds128u(slab + tc::sw128_offset(row, (ch & 1) * 4 + i));
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint4 nv = lds128u(slab + tc::sw128_offset(row, (ch & 1) * 4 + i));
+            const uint4 nv = nq[i];
             float2 g0, g1, g2, g3;
             grad4(r, ch, i * 8, g0, g1); grad4(r, ch, i * 8 + 4, g2, g3);
-            s1 = __fadd2_rn(s1, g0); s1 = __fadd2_rn(s1, g1); s1 = __fadd2_rn(s1, g2); s1 = __fadd2_rn(s1, g3);
+            s1 = __fadd2_rn(s1, g0); s1b = __fadd2_rn(s1b, g1); s1 = __fadd2_rn(s1, g2); s1b = __fadd2_rn(s1b, g3);
             s2 = __ffma2_rn(g0, make_float2(bf_lo(nv.x), bf_hi(nv.x)), s2);
-            s2 = __ffma2_rn(g1, make_float2(bf_lo(nv.y), bf_hi(nv.y)), s2);
+            s2b = __ffma2_rn(g1, make_float2(bf_lo(nv.y), bf_hi(nv.y)), s2b);
             s2 = __ffma2_rn(g2, make_float2(bf_lo(nv.z), bf_hi(nv.z)), s2);
-            s2 = __ffma2_rn(g3, make_float2(bf_lo(nv.w), bf_hi(nv.w)), s2);
+            s2b = __ffma2_rn(g3, make_float2(bf_lo(nv.w), bf_hi(nv.w)), s2b);
         }
     }
+    s1 = __fadd2_rn(s1, s1b); s2 = __fadd2_rn(s2, s2b);
     if (pf) pf[4] = clock64();
     const float m1 = (s1.x + s1.y) * (1.0f / 256.f), m2 = (s2.x + s2.y) * (1.0f / 256.f);
     const float2 rs2 = make_float2(rstd, rstd);
@@ -114,10 +120,13 @@ __device__ __noinline__ void bwd_epilogue_unit(uint32_t taddr, uint32_t act_addr
     };
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
+        uint4 nq[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) nq[i] = lds128u(slab + tc::sw128_offset(row, (ch & 1) * 4 + i));
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t addr = slab + tc::sw128_offset(row, (ch & 1) * 4 + i);
-            const uint4 nv = lds128u(addr);
+            const uint4 nv = nq[i];
             float2 g0, g1, g2, g3;
             grad4(rc, ch, i * 8, g0, g1); grad4(rc, ch, i * 8 + 4, g2, g3);
             const uint4 o = make_uint4(dz2(g0, nv.x), dz2(g1, nv.y), dz2(g2, nv.z), dz2(g3, nv.w));
