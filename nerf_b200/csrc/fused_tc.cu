@@ -22,6 +22,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     auto act_ready = [&](int x) { return bar0 + 8u * (2 * TC_RING + x); };
     auto acc_ready = [&](int x) { return bar0 + 8u * (2 * TC_RING + 2 + x); };
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 4));
+    // TRAIN: act_local[2] (this CTA's slab of slot x is complete: 4 epilogue warps), store_done[2] (its bulk store has been read out)
+    auto act_local = [&](int x) { return bar0 + 8u * (2 * TC_RING + 5 + x); };
+    auto store_done = [&](int x) { return bar0 + 8u * (2 * TC_RING + 7 + x); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = (CG == 2) ? tc::cluster_ctarank() : 0u;
@@ -36,7 +39,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     for (int i = threadIdx.x; i < TC_SMVEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[TC_VEC_HEADW + i];
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), (CG == 2 && leader) ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
-        for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), CG == 2 ? 8 : 128); tc::mbar_init(acc_ready(x), 1); }
+        for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), CG == 2 ? 8 : 128); tc::mbar_init(acc_ready(x), 1); tc::mbar_init(act_local(x), 4); tc::mbar_init(store_done(x), 1); }
         tc::fence_barrier_init();
     }
     if (warp == 1) { if (CG == 2) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 512); else tc::tmem_alloc(tc::smem_u32((const void*)tmem_slot), 512); }
@@ -140,6 +143,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                         }
                     }
         }
+    } else if (warp == 10) {
+        // ===================== TRAIN: activation-store thread =====================
+        // The normalised output of unit l is the A operand of unit l+1's MMAs AND a slab image the backward needs.  One 64 KB
+        // bulk store issued by the epilogue right before it releases the MMA sits in front of the weight-stage loads in the
+        // SM's bulk-copy queue (forward timeline: the slot whose MMAs follow the stores took 5.5 k cycles per unit instead of
+        // 2.2 k); this thread spreads the store as four 16 KB pieces over the MMA's duration instead and tells the epilogue
+        // when the slab may be overwritten.
+        if (TRAIN && lane == 0) {
+            uint32_t al_it[2] = {0, 0};
+            for (int q = 0; q < cnt0; ++q)
+                for (int sgn = 0; sgn < 10; ++sgn)                     // signal 0: encoding ready; signal l+1: n_l ready
+                    for (int x = 0; x < 2; ++x) {
+                        if (x == 1 && q >= cnt1) continue;
+                        tc::mbar_wait(act_local(x), al_it[x] & 1, a.wait_hint); ++al_it[x];
+                        if (sgn == 0) continue;
+                        const int unit = me + (2 * q + x) * G;
+                        const int tile = (CG == 2) ? 2 * unit + (int)rank : unit;
+                        uint8_t* dst = a.tr_act + ((size_t)(sgn - 1) * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
+                        const uint32_t src = base + SM_ACT + x * 65536;
+                        for (int ks = 0; ks < 4; ++ks) {
+                            tc::tma_store_1d(dst + (size_t)ks * TC_SLAB_BYTES, src + ks * TC_SLAB_BYTES, TC_SLAB_BYTES);
+                            tc::tma_store_commit();
+                            if (ks < 3) { const long long t0 = clock64(); while (clock64() - t0 < (long long)a.store_gap) { } }
+                        }
+                        tc::tma_store_wait_read0();
+                        tc::mbar_arrive(store_done(x));
+                    }
+            tc::tma_store_wait_all0();
+        }
     } else {
         // ===================== encoder + epilogue groups =====================
         const int x = (warp - 2) >> 2;                               // tile slot of this group
@@ -151,10 +183,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
         auto signal_act = [&]() {
             tc::fence_proxy_async_smem();
             tc::tcgen05_fence_before();
-            if (CG == 2) { __syncwarp(); if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
+            if (CG == 2 || TRAIN) __syncwarp();
+            if (TRAIN && lane == 0) tc::mbar_arrive(act_local(x));
+            if (CG == 2) { if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
             else tc::mbar_arrive(act_ready(x));
         };
-        uint32_t acc_it = 0;
+        uint32_t acc_it = 0, sd_it = 0;
         for (int q = 0; q < cnt; ++q) {
             const int unit = me + (2 * q + x) * G;
             const int tile = (CG == 2) ? 2 * unit + (int)rank : unit;
@@ -171,8 +205,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 tc::tcgen05_fence_after();
                 if (a.prof && blockIdx.x == 0 && q == 1 && threadIdx.x == 64 + x * 128) a.prof[(l * 2 + x) * 8 + 4] = clock64();
                 if (TRAIN) {                                         // pending bulk stores must have read the slabs we overwrite
-                    if (row == 0) tc::tma_store_wait_read0();
+                    if (row == 0) tc::tma_store_wait_read0();            // (this thread's: encodings, n_9 of the previous tile)
                     tc::named_bar_sync(1 + x, 128);
+                    if (l >= 1) { tc::mbar_wait(store_done(x), sd_it & 1, a.wait_hint); ++sd_it; }   // n_{l-1}: the store thread's
                 }
                 if (!TRAIN && a.dbg && a.dbg_layer == l) epilogue_unit<3, false>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 else if (l == 7) epilogue_unit<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
@@ -182,10 +217,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                                                   a.ray_bias + ((size_t)(l ? 1 : 0) * a.rb_rows + (st.valid ? (a.rb_ray0 + st.p / a.S) / a.rb_div : 0)) * 256);
                 else epilogue_unit<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row(a, row, pe_addr, st);     // unit 4 was the last reader of the position slab
-                if (TRAIN) {                                         // normalised output of unit l (and the direction slab) -> HBM
-                    tc::fence_proxy_async_smem(); tc::named_bar_sync(1 + x, 128);
+                if (TRAIN && (l == 4 || l == 9)) {                   // direction slab, and n_9 (no MMA follows it) -> HBM from here;
+                    tc::fence_proxy_async_smem(); tc::named_bar_sync(1 + x, 128);   // n_0..n_8 leave through the store thread
                     if (row == 0) {
-                        tc::tma_store_1d(a.tr_act + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), act_addr, 4 * TC_SLAB_BYTES);
+                        if (l == 9) tc::tma_store_1d(a.tr_act + ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES), act_addr, 4 * TC_SLAB_BYTES);
                         if (l == 4) tc::tma_store_1d(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
                         tc::tma_store_commit();
                     }
@@ -209,6 +244,7 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
     { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
+    { const char* e = getenv("NERF_FWD_STORE_GAP"); a.store_gap = e ? (uint32_t)atoi(e) : 600u; }   // measured: 0 -> 0.410, 400-800 -> 0.389-0.393, 1200 -> 0.442 ms
     static int cg = -1;
     if (cg < 0) {
         const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2;

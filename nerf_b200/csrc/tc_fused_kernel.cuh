@@ -14,7 +14,7 @@
 #pragma once
 #include "tc_layout.cuh"
 
-#define TC_THREADS 320
+#define TC_THREADS 352                            // 10 role warps + the training forward's activation-store warp
 #define TC_RING 3
 #define SM_ACT 0                                  // 2 x 64 KB
 #define SM_PE (2 * 65536)                         // 2 x 16 KB
@@ -44,6 +44,7 @@ struct FusedArgs {
     int64_t rb_rows, rb_ray0, rb_div;             //   ray r of this launch uses row (rb_ray0 + r) / rb_div (one row per ray, or per camera)
     long long* prof;                              // NERF_TC_PROF: clock64 stamps of CTA 0, second work unit
     uint32_t wait_hint;                           // mbarrier try_wait suspend-time hint (0 = plain spin)
+    uint32_t store_gap;                           // TRAIN: cycles between the 16 KB pieces of an activation store
 };
 
 __device__ __forceinline__ void store_row_chunk(uint32_t slab_addr, uint32_t row, uint32_t c16, uint4 v) {
