@@ -193,6 +193,9 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
     const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
     const __nv_bfloat162 shift_bf = __floats2bfloat162_rn(shift, shift);
     float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products
+    float h0b = 0.f, h1b = 0.f, h2b = 0.f;                   // (two chains per head: the adds are latency-bound at one warp per SMSP)
+    float4 hbias = make_float4(0.f, 0.f, 0.f, 0.f);          // head biases from the shared copy, requested before the pass, not after it
+    if (MODE == 1 || MODE == 2) hbias = tc::lds128(vec_addr + (TC_VEC_HEADB - TC_VEC_HEADW) * 4);
     const uint32_t hw_addr = vec_addr;
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         uint32_t packed[16];
@@ -212,14 +215,14 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
                 const float n0 = fmaxf(y0.x, shift), n1 = fmaxf(y0.y, shift), n2 = fmaxf(y1.x, shift), n3 = fmaxf(y1.y, shift);
                 if (MODE == 1) {
                     const float4 w = tc::lds128(hw_addr + (ch * 32 + j) * 4);
-                    h0 = fmaf(n0, w.x, h0); h0 = fmaf(n1, w.y, h0); h0 = fmaf(n2, w.z, h0); h0 = fmaf(n3, w.w, h0);
+                    h0 = fmaf(n0, w.x, h0); h0b = fmaf(n1, w.y, h0b); h0 = fmaf(n2, w.z, h0); h0b = fmaf(n3, w.w, h0b);
                 } else if (MODE == 2) {
                     const float4 w0 = tc::lds128(hw_addr + (256 + ch * 32 + j) * 4);
                     const float4 w1 = tc::lds128(hw_addr + (512 + ch * 32 + j) * 4);
                     const float4 w2 = tc::lds128(hw_addr + (768 + ch * 32 + j) * 4);
-                    h0 = fmaf(n0, w0.x, h0); h0 = fmaf(n1, w0.y, h0); h0 = fmaf(n2, w0.z, h0); h0 = fmaf(n3, w0.w, h0);
-                    h1 = fmaf(n0, w1.x, h1); h1 = fmaf(n1, w1.y, h1); h1 = fmaf(n2, w1.z, h1); h1 = fmaf(n3, w1.w, h1);
-                    h2 = fmaf(n0, w2.x, h2); h2 = fmaf(n1, w2.y, h2); h2 = fmaf(n2, w2.z, h2); h2 = fmaf(n3, w2.w, h2);
+                    h0 = fmaf(n0, w0.x, h0); h0b = fmaf(n1, w0.y, h0b); h0 = fmaf(n2, w0.z, h0); h0b = fmaf(n3, w0.w, h0b);
+                    h1 = fmaf(n0, w1.x, h1); h1b = fmaf(n1, w1.y, h1b); h1 = fmaf(n2, w1.z, h1); h1b = fmaf(n3, w1.w, h1b);
+                    h2 = fmaf(n0, w2.x, h2); h2b = fmaf(n1, w2.y, h2b); h2 = fmaf(n2, w2.z, h2); h2b = fmaf(n3, w2.w, h2b);
                 } else if (st.valid) {
                     float* o = a.dbg + st.p * 256 + ch * 32 + j;
                     o[0] = n0; o[1] = n1; o[2] = n2; o[3] = n3;
@@ -245,10 +248,10 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
     }
     if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
     if (st.valid) {
-        if (MODE == 1) a.out_sigma[st.p] = h0 + a.vec[TC_VEC_HEADB];
+        if (MODE == 1) a.out_sigma[st.p] = (h0 + h0b) + hbias.x;
         if (MODE == 2) {
-            a.out_rgb[st.p * 3] = h0 + a.vec[TC_VEC_HEADB + 1]; a.out_rgb[st.p * 3 + 1] = h1 + a.vec[TC_VEC_HEADB + 2];
-            a.out_rgb[st.p * 3 + 2] = h2 + a.vec[TC_VEC_HEADB + 3];
+            a.out_rgb[st.p * 3] = (h0 + h0b) + hbias.y; a.out_rgb[st.p * 3 + 1] = (h1 + h1b) + hbias.z;
+            a.out_rgb[st.p * 3 + 2] = (h2 + h2b) + hbias.w;
         }
     }
 }
