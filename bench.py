@@ -341,7 +341,20 @@ def run_ours(args):
     ms_cb = float(np.mean(timed_steps(comp_bwd, 5, flush)))
     comp_fwd_gbs = COMPOSITE_FWD_BYTES_PER_RAY * cb / (ms_cf * 1e-3) / 1e9
     comp_bwd_gbs = COMPOSITE_BWD_BYTES_PER_RAY * cb / (ms_cb * 1e-3) / 1e9
-    del csig, crgb, ct, dsg, drg
+    # the stratified sampler alone at the same size: 4 S bytes per ray written (+ 4 S read with host-supplied uniforms)
+    cu = torch.rand(cb, s, device=dev)
+
+    def samp_u(i):
+        _lib.check(_lib.lib().nerf_sample_linear(NEAR, FAR, None, s, cb, P(cu), 1, 6, 0, P(ct), _lib.stream()), "su")
+
+    def samp_philox(i):
+        _lib.check(_lib.lib().nerf_sample_linear(NEAR, FAR, None, s, cb, None, 1, 6, 0, P(ct), _lib.stream()), "sp")
+    samp_u(0); samp_philox(0)
+    ms_su = float(np.mean(timed_steps(samp_u, 5, flush)))
+    ms_sp = float(np.mean(timed_steps(samp_philox, 5, flush)))
+    samp_u_gbs = 8 * s * cb / (ms_su * 1e-3) / 1e9
+    samp_p_gbs = 4 * s * cb / (ms_sp * 1e-3) / 1e9
+    del csig, crgb, ct, dsg, drg, cu
 
     # ---- render throughput: 800x800 x 64 (fused bf16 path) or 200x200 (fp32 path) through render_image ----
     from oracle.g1 import pose_spherical, TINY_NERF_FOCAL
@@ -460,6 +473,9 @@ def run_ours(args):
                                   "frac": mlp_tflops / tensor_peak, "ms": ms_mlp},
             "roofline_hbm": {"composite_fwd": {"achieved": comp_fwd_gbs, "frac": comp_fwd_gbs / peaks["hbm"], "ms": ms_cf},
                              "composite_bwd": {"achieved": comp_bwd_gbs, "frac": comp_bwd_gbs / peaks["hbm"], "ms": ms_cb},
+                             "sample_host_u": {"achieved": samp_u_gbs, "frac": samp_u_gbs / peaks["hbm"], "ms": ms_su},
+                             "sample_philox": {"achieved": samp_p_gbs, "frac": samp_p_gbs / peaks["hbm"], "ms": ms_sp,
+                                               "note": "fma-pipe bound: 20 IMAD.WIDE per 4 samples (Philox4x32-10)"},
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
             "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},

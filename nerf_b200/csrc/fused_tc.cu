@@ -37,6 +37,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
     const int stages_per_slab = (CG == 2) ? 1 : 2;
 
     for (int i = threadIdx.x; i < TC_SMVEC_FLOATS; i += TC_THREADS) vec_s[i] = a.vec[TC_VEC_HEADW + i];
+    if (warp < 4) {                                               // sum_k w_k of head `warp` (the affine part of the head dot products)
+        float sw = 0.f;
+        for (int i = lane; i < 256; i += 32) sw += a.vec[TC_VEC_HEADW + warp * 256 + i];
+        sw = warp_sum(sw);
+        if (lane == 0) reinterpret_cast<float*>(sm + SM_HSUM)[warp] = sw;
+    }
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), (CG == 2 && leader) ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
         for (int x = 0; x < 2; ++x) { tc::mbar_init(act_ready(x), CG == 2 ? 8 : 128); tc::mbar_init(acc_ready(x), 1); tc::mbar_init(act_local(x), 4); tc::mbar_init(store_done(x), 1); }

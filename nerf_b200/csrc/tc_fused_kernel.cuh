@@ -22,6 +22,7 @@
 #define SM_VEC (SM_RING + TC_RING * TF_SLOT_BYTES)         // head weights [4][256] + head biases [4], fp32
 #define TC_SMVEC_FLOATS (TC_VEC_FLOATS - TC_VEC_HEADW)
 #define SM_BAR (SM_VEC + ((TC_SMVEC_FLOATS * 4 + 15) & ~15))
+#define SM_HSUM (SM_BAR + 192)                    // sum_k w_k of the 4 heads (fp32), inside the barrier block's slack
 #define SM_TOTAL (SM_BAR + 256)
 #define TC_SMEM_BYTES (SM_TOTAL + 1024)           // + slack for the manual 1024 B alignment
 
@@ -160,8 +161,10 @@ __device__ __forceinline__ float2 f2(uint32_t a, uint32_t b) { return make_float
 template <int MODE, bool TRAIN, bool RB = false>
 __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr,
                                            uint32_t row, uint32_t vec_addr, const RowState& st, const float* rb = nullptr) {
+    const uint32_t hsum_addr = vec_addr + (SM_HSUM - SM_VEC);
     uint32_t r0[32], r1[32];
     float2 s2 = make_float2(0.f, 0.f), q2 = make_float2(0.f, 0.f), s3 = s2, q3 = q2;   // two chains each: the adds are latency-bound
+    float2 hp0 = make_float2(0.f, 0.f), hp1 = hp0, hp2 = hp0, hp0b = hp0, hp1b = hp0, hp2b = hp0;   // head partial sums (two chains each)
     auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
@@ -173,6 +176,19 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
             z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
             s2 = __fadd2_rn(s2, z0); s3 = __fadd2_rn(s3, z1);
             q2 = __ffma2_rn(z0, z0, q2); q3 = __ffma2_rn(z1, z1, q3);
+            // heads: sum_k n_k w_k with n_k = relu(z_k) rstd + shift  =  rstd sum_k relu(z_k) w_k + shift sum_k w_k: the dot product
+            // rides on the relu(z) pairs of this pass (packed FMAs), the affine part is applied once after it
+            if (MODE == 1) {
+                const float4 w = tc::lds128(vec_addr + (ch * 32 + j) * 4);
+                hp0 = __ffma2_rn(z0, make_float2(w.x, w.y), hp0); hp0b = __ffma2_rn(z1, make_float2(w.z, w.w), hp0b);
+            } else if (MODE == 2) {
+                const float4 w0 = tc::lds128(vec_addr + (256 + ch * 32 + j) * 4);
+                const float4 w1 = tc::lds128(vec_addr + (512 + ch * 32 + j) * 4);
+                const float4 w2 = tc::lds128(vec_addr + (768 + ch * 32 + j) * 4);
+                hp0 = __ffma2_rn(z0, make_float2(w0.x, w0.y), hp0); hp0b = __ffma2_rn(z1, make_float2(w0.z, w0.w), hp0b);
+                hp1 = __ffma2_rn(z0, make_float2(w1.x, w1.y), hp1); hp1b = __ffma2_rn(z1, make_float2(w1.z, w1.w), hp1b);
+                hp2 = __ffma2_rn(z0, make_float2(w2.x, w2.y), hp2); hp2b = __ffma2_rn(z1, make_float2(w2.z, w2.w), hp2b);
+            }
         }
     };
     tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
@@ -192,11 +208,18 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
     const float shift = -mean * rstd;
     const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
     const __nv_bfloat162 shift_bf = __floats2bfloat162_rn(shift, shift);
-    float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head dot products
-    float h0b = 0.f, h1b = 0.f, h2b = 0.f;                   // (two chains per head: the adds are latency-bound at one warp per SMSP)
-    float4 hbias = make_float4(0.f, 0.f, 0.f, 0.f);          // head biases from the shared copy, requested before the pass, not after it
-    if (MODE == 1 || MODE == 2) hbias = tc::lds128(vec_addr + (TC_VEC_HEADB - TC_VEC_HEADW) * 4);
-    const uint32_t hw_addr = vec_addr;
+    float h0 = 0.f, h1 = 0.f, h2 = 0.f;                      // head outputs
+    if (MODE == 1 || MODE == 2) {
+        const float4 hbias = tc::lds128(vec_addr + (TC_VEC_HEADB - TC_VEC_HEADW) * 4);   // head biases and sum_k w_k from shared memory
+        const float4 hwsum = tc::lds128(hsum_addr);
+        hp0 = __fadd2_rn(hp0, hp0b); hp1 = __fadd2_rn(hp1, hp1b); hp2 = __fadd2_rn(hp2, hp2b);
+        if (MODE == 1) h0 = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.x, hbias.x));
+        else {
+            h0 = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.y, hbias.y));
+            h1 = fmaf(rstd, hp1.x + hp1.y, fmaf(shift, hwsum.z, hbias.z));
+            h2 = fmaf(rstd, hp2.x + hp2.y, fmaf(shift, hwsum.w, hbias.w));
+        }
+    }
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         uint32_t packed[16];
 #pragma unroll
@@ -211,22 +234,10 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
             __nv_bfloat162 p0 = __hmax2(__float22bfloat162_rn(y0), shift_bf);
             __nv_bfloat162 p1 = __hmax2(__float22bfloat162_rn(y1), shift_bf);
             packed[j / 2] = *reinterpret_cast<uint32_t*>(&p0); packed[j / 2 + 1] = *reinterpret_cast<uint32_t*>(&p1);
-            if (MODE != 0) {
+            if (MODE == 3 && st.valid) {
                 const float n0 = fmaxf(y0.x, shift), n1 = fmaxf(y0.y, shift), n2 = fmaxf(y1.x, shift), n3 = fmaxf(y1.y, shift);
-                if (MODE == 1) {
-                    const float4 w = tc::lds128(hw_addr + (ch * 32 + j) * 4);
-                    h0 = fmaf(n0, w.x, h0); h0b = fmaf(n1, w.y, h0b); h0 = fmaf(n2, w.z, h0); h0b = fmaf(n3, w.w, h0b);
-                } else if (MODE == 2) {
-                    const float4 w0 = tc::lds128(hw_addr + (256 + ch * 32 + j) * 4);
-                    const float4 w1 = tc::lds128(hw_addr + (512 + ch * 32 + j) * 4);
-                    const float4 w2 = tc::lds128(hw_addr + (768 + ch * 32 + j) * 4);
-                    h0 = fmaf(n0, w0.x, h0); h0b = fmaf(n1, w0.y, h0b); h0 = fmaf(n2, w0.z, h0); h0b = fmaf(n3, w0.w, h0b);
-                    h1 = fmaf(n0, w1.x, h1); h1b = fmaf(n1, w1.y, h1b); h1 = fmaf(n2, w1.z, h1); h1b = fmaf(n3, w1.w, h1b);
-                    h2 = fmaf(n0, w2.x, h2); h2b = fmaf(n1, w2.y, h2b); h2 = fmaf(n2, w2.z, h2); h2b = fmaf(n3, w2.w, h2b);
-                } else if (st.valid) {
-                    float* o = a.dbg + st.p * 256 + ch * 32 + j;
-                    o[0] = n0; o[1] = n1; o[2] = n2; o[3] = n3;
-                }
+                float* o = a.dbg + st.p * 256 + ch * 32 + j;
+                o[0] = n0; o[1] = n1; o[2] = n2; o[3] = n3;
             }
         }
         if (MODE != 2 || TRAIN) {
@@ -248,10 +259,7 @@ __device__ __noinline__ void epilogue_unit(const FusedArgs& a, int l, uint32_t t
     }
     if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
     if (st.valid) {
-        if (MODE == 1) a.out_sigma[st.p] = (h0 + h0b) + hbias.x;
-        if (MODE == 2) {
-            a.out_rgb[st.p * 3] = (h0 + h0b) + hbias.y; a.out_rgb[st.p * 3 + 1] = (h1 + h1b) + hbias.z;
-            a.out_rgb[st.p * 3 + 2] = (h2 + h2b) + hbias.w;
-        }
+        if (MODE == 1) a.out_sigma[st.p] = h0;
+        if (MODE == 2) { a.out_rgb[st.p * 3] = h0; a.out_rgb[st.p * 3 + 1] = h1; a.out_rgb[st.p * 3 + 2] = h2; }
     }
 }
