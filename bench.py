@@ -40,7 +40,7 @@ def load_peaks():
 def ncu_traffic():
     """dram__bytes_read + dram__bytes_write per launch of the training kernels from the committed ncu --set full
     summary (profiles/, written by scripts/ncu_summary.py at this workload size); {} when absent."""
-    path = os.path.join(ROOT, "profiles", "r01_train_tc_v9_ncu.json")
+    path = os.path.join(ROOT, "profiles", "r01_train_tc_v10_ncu.json")
     out = {}
     if os.path.exists(path):
         for k in json.load(open(path))["kernels"]:
