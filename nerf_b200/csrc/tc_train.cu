@@ -140,8 +140,9 @@ __device__ __forceinline__ void unfold_weights_body(const float* __restrict__ pa
     if (l < 10) {
         const int Kt = L.Kt[l], hid = (l == 0) ? 0 : 256;
         const float* G = gw + (size_t)l * 256 * TC_GW_LD;
-        for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < 256ll * (Kt + 1); e += (int64_t)gridDim.x * blockDim.x) {
-            const int i = (int)(e / (Kt + 1)), k = (int)(e % (Kt + 1));
+        const uint32_t row_len = (uint32_t)Kt + 1u, n_el = 256u * row_len;       // 32-bit index math: the kernel is a few elements per thread
+        for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n_el; e += gridDim.x * blockDim.x) {
+            const int i = (int)(e / row_len), k = (int)(e - (uint32_t)i * row_len);
             const float c = G[(size_t)i * TC_GW_LD + 320];
             if (k == Kt) { grads[L.off_b[l] + i] = c; continue; }
             float v;
