@@ -159,11 +159,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
         if (TRAIN && lane == 0) {
             uint32_t al_it[2] = {0, 0};
             for (int q = 0; q < cnt0; ++q)
-                for (int sgn = 0; sgn < 10; ++sgn)                     // signal 0: encoding ready; signal l+1: n_l ready
+                // (every act_local phase is followed, in the epilogue, by a wait on the store_done it leads to before the next one can
+                // complete: two phases can never pass unobserved, whatever the timing)
+                for (int sgn = 1; sgn < 10; ++sgn)                     // signal l+1: n_l ready
                     for (int x = 0; x < 2; ++x) {
                         if (x == 1 && q >= cnt1) continue;
                         tc::mbar_wait(act_local(x), al_it[x] & 1, a.wait_hint); ++al_it[x];
-                        if (sgn == 0) continue;
                         const int unit = me + (2 * q + x) * G;
                         const int tile = (CG == 2) ? 2 * unit + (int)rank : unit;
                         uint8_t* dst = a.tr_act + ((size_t)(sgn - 1) * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
@@ -186,11 +187,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
         const uint32_t act_addr = base + SM_ACT + x * 65536, pe_addr = base + SM_PE + x * TC_SLAB_BYTES;
         const int cnt = x == 0 ? cnt0 : cnt1;
         const uint32_t act_bar_remote = (CG == 2) ? tc::mapa(act_ready(x), 0) : 0u;
-        auto signal_act = [&]() {
+        auto signal_act = [&](bool slab_to_store = true) {
             tc::fence_proxy_async_smem();
             tc::tcgen05_fence_before();
             if (CG == 2 || TRAIN) __syncwarp();
-            if (TRAIN && lane == 0) tc::mbar_arrive(act_local(x));
+            if (TRAIN && slab_to_store && lane == 0) tc::mbar_arrive(act_local(x));
             if (CG == 2) { if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote); }
             else tc::mbar_arrive(act_ready(x));
         };
@@ -204,7 +205,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) g1_fused_tc_kernel(const FusedA
                 tc::fence_proxy_async_smem(); tc::named_bar_sync(1 + x, 128);
                 if (row == 0) { tc::tma_store_1d(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES); tc::tma_store_commit(); }
             }
-            signal_act();
+            signal_act(false);                                       // the encoding slab: nothing for the store thread
             for (int l = 0; l < 10; ++l) {
                 if (a.prof && blockIdx.x == 0 && q == 1 && threadIdx.x == 64 + x * 128) a.prof[(l * 2 + x) * 8 + 3] = clock64();
                 tc::mbar_wait(acc_ready(x), acc_it & 1, a.wait_hint); ++acc_it;
