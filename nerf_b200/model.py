@@ -282,18 +282,28 @@ class NeRF(nn.Module):
                 outs.append(r["pixels"])
             img = torch.cat(outs, dim=0)
             return img.reshape(bc, image_h, image_w, 3) if full else img
-        for i in range(ray_begin, ray_end, chunk):
-            j = min(i + chunk, ray_end)
-            o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, i, j)
+        # Chunks are cut on multiples of `chunk` in the FRAME's ray ids, whatever the shard: a shard then runs the frame's own chunks.
+        # The coarse composite of the hierarchical path picks its kernel by the chunk's ray count (ops.COMPOSITE_WARP_BELOW), so an
+        # edge piece shorter than that is rendered as the frame's whole chunk and sliced: shards stay bit-identical to the frame.
+        i = ray_begin
+        while i < ray_end:
+            c0 = (i // chunk) * chunk
+            c1 = min(c0 + chunk, total)
+            j = min(c1, ray_end)
+            lo, hi = i, j
+            if num_fine > 0 and hi - lo < ops.COMPOSITE_WARP_BELOW <= c1 - c0:
+                lo, hi = c0, c1
+            o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, lo, hi)
             sx = sd = None
             if states_x is not None or states_d is not None:
-                cam = torch.arange(i, j, device=o.device) // (image_h * image_w)
+                cam = torch.arange(lo, hi, device=o.device) // (image_h * image_w)
                 sx = None if states_x is None else states_x.float()[cam].contiguous()
                 sd = None if states_d is None else states_d.float()[cam].contiguous()
             if num_fine > 0:
                 r = self.render_rays_hierarchical(o, d, near, far, num_samples, num_fine, sx, sd)
             else:
                 r = self.render_rays_full(o, d, near, far, num_samples, sx, sd)
-            outs.append(r["pixels"])
+            outs.append(r["pixels"][i - lo:j - lo])
+            i = j
         img = torch.cat(outs, dim=0)
         return img.reshape(bc, image_h, image_w, 3) if full else img

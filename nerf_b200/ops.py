@@ -12,6 +12,10 @@ PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
 HIDDEN = 256
 
 
+# nerf_composite_fwd takes the warp-per-ray kernels below this many rays and the thread-per-ray tile kernels from it on
+# (csrc/composite.cu); the two sum in different orders
+COMPOSITE_WARP_BELOW = 1 << 14
+
 def _f32c(t):
     if t is None:
         return None
