@@ -37,16 +37,22 @@ def load_peaks():
     return dict(hbm=6650.0, tensor_burst=1590.0, tensor_sustained=1400.0, src="fallback")
 
 
-def ncu_traffic():
-    """dram__bytes_read + dram__bytes_write per launch of the training kernels from the committed ncu --set full
-    summary (profiles/, written by scripts/ncu_summary.py at this workload size); {} when absent."""
-    path = os.path.join(ROOT, "profiles", "r01_train_tc_v10_ncu.json")
+NCU_TRAIN = ("profiles/r02_train_tc_ncu.json", "profiles/r01_train_tc_v10_ncu.json")     # newest first
+NCU_RENDER = ("profiles/r02_render_tc_ncu.json", "profiles/r01_render_fwd_v5_ncu.json")
+
+
+def ncu_counters(paths, names):
+    """Per-launch ncu counters of the committed `ncu --set full` summaries under profiles/ (scripts/ncu_summary.py, taken at
+    this workload size): {kernel: {dram_bytes, tensor_pipe_pct, source}}; {} when absent."""
     out = {}
-    if os.path.exists(path):
+    for rel in paths:
+        path = os.path.join(ROOT, rel)
+        if not os.path.exists(path):
+            continue
         for k in json.load(open(path))["kernels"]:
-            for name in ("g1_fused_tc_kernel", "g1_bwd_tc_kernel", "g1_wgrad_tc_kernel"):
-                if name in k["kernel"] and "dram_bytes" in k:
-                    out[name] = k["dram_bytes"]
+            for name in names:
+                if name in k["kernel"] and name not in out and "dram_bytes" in k:
+                    out[name] = {"dram_bytes": k["dram_bytes"], "tensor_pipe_pct": k.get("tensor_pipe_pct"), "source": rel}
     return out
 
 
@@ -144,45 +150,43 @@ def cpu_train_step_rays_per_s(n_rays, steps, warmup=1):
     return n_rays / float(np.median(times)), float(np.sum(times))
 
 
+def bench_config(world):
+    """The `config` object, identical in both arms (the reference arm runs the same 4096 x 64 batch per step)."""
+    return {"workload": "tiny NeRF train step fwd+bwd+Adam, 4096-ray batches x 64 samples (G1, nerf.pth), per GPU",
+            "rays_per_gpu": RAYS, "samples": SAMPLES,
+            "l2": "no flush needed: every step streams its own 2.7 GB activation workspace (>> 126 MB L2) and K steps are "
+                  "timed back to back in ONE CUDA-event bracket (launch gaps included); the CPU arm has no L2 policy",
+            "parallelism": f"dp{world}"}
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation (oracle port; the G1
-    source is not in the reference tree) on a bounded sample per step."""
+    """--impl reference: the reference's own CPU implementation of the path (the oracle port: the G1 source is not
+    in the reference tree) with all host threads, on the SAME workload: 4096 rays x 64 samples per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sample = 512
     t0 = time.perf_counter()
-    rps, _ = cpu_train_step_rays_per_s(sample, args.steps, args.warmup)
-    ms = 1e3 * sample / rps
+    rps, _ = cpu_train_step_rays_per_s(RAYS, args.steps, args.warmup)
+    ms = 1e3 * RAYS / rps
     line = {"impl": "reference", "metric": "rays/sec (train fwd+bwd)", "value": rps, "unit": "rays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "tiny NeRF train step fwd+bwd+Adam, 4096-ray batches x 64 samples (G1, nerf.pth)",
-                       "sample": f"{sample} rays x {SAMPLES} samples per step"},
+            "config": bench_config(args.gpus),
             "cpu_baseline": {"value": rps, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
-                             "sample": f"{sample} rays x {SAMPLES} samples per step, median of {args.steps}"},
+                             "sample": f"the full workload: {RAYS} rays x {SAMPLES} samples per step, median of {args.steps} steps"},
             "e2e": {"value": rps, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "wall_s": time.perf_counter() - t0}
     print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------ our arm -----
-def dominant_roofline(kernels, peaks):
-    """The contract's `roofline` object for the longest kernel of the step, against the resource that binds it."""
-    name, k = max(kernels.items(), key=lambda kv: kv[1]["ms"])
-    r = k[k["bound"]]
-    return {"bound": k["bound"], "kernel": name, "achieved": r["achieved"], "unit": r["unit"], "frac": r["frac"],
-            "peak": peaks["hbm"] if k["bound"] == "hbm" else peaks["tensor_sustained"],
-            "peak_source": peaks["src"] + (" HBM copy" if k["bound"] == "hbm" else " bf16 sustained"),
-            "traffic": k["traffic"], "ms": k["ms"], "algorithmic_bytes": k["hbm"]["bytes"]}
-
-
-def timed_steps(fn, steps, flush):
-    """Each step bracketed by its own CUDA events on the current stream; L2 is flushed
-    (a 256 MiB write) between steps, outside the timed brackets."""
+def timed_steps(fn, steps, flush=None):
+    """Per-call CUDA-event brackets on the current stream (kernel-level timings: each call alone, L2 flushed by a
+    256 MiB write outside the bracket when `flush` is given)."""
     evs = []
     for i in range(steps):
-        flush.zero_()
+        if flush is not None:
+            flush.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(); fn(i); b.record()
         evs.append((a, b))
@@ -190,9 +194,30 @@ def timed_steps(fn, steps, flush):
     return [a.elapsed_time(b) for a, b in evs]
 
 
+def timed_region(fn, steps):
+    """EXACTLY `steps` calls back to back inside ONE CUDA-event bracket (synchronised on both sides by the caller's
+    barrier): device time of the whole region, launch gaps included.  Returns (device ms, wall ms)."""
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.perf_counter()
+    a.record()
+    for i in range(steps):
+        fn(i)
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b), 1e3 * (time.perf_counter() - w0)
+
+
+def safe(section, fn):
+    """Secondary measurements never take the headline line down with them."""
+    try:
+        return fn()
+    except Exception as e:      # noqa: BLE001
+        return {"error": f"{section}: {type(e).__name__}: {e}"[:300]}
+
+
 def run_ours(args):
     import torch.distributed as dist
-    from nerf_b200 import _lib, ops
+    from nerf_b200 import _lib, ops, parallel
     from nerf_b200.model import NeRF
     from nerf_b200.train import Trainer
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -206,9 +231,26 @@ def run_ours(args):
     _lib.lib()
     peaks = load_peaks()
     dev = torch.device("cuda", local)
+    sd = nerf_pth_state_dict()
+    K, W = args.steps, args.warmup
+    b, s = RAYS, SAMPLES
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(*vals):
+        if world == 1:
+            return list(vals)
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
+
+    clk = ClockSampler(local).__enter__()                 # before the warm-up: the timed region at --steps 20 is ~30 ms
 
     model = NeRF(normalize_position=6.0, precision=args.precision).to(dev)
-    model.load_state_dict(nerf_pth_state_dict())
+    model.load_state_dict(sd)
     trainer = Trainer(model, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0,
                       randomly_sample=True, seed=1234)
     # a pool of distinct batches, resident in HBM (value) and in pinned host memory (e2e)
@@ -216,11 +258,10 @@ def run_ours(args):
     pool_h = []
     for i in range(n_pool):
         o, d = synthetic_batch(RAYS, seed=1000 * rank + i)
-        tgt = torch.rand(RAYS, 3, generator=torch.Generator().manual_seed(7 + i))
+        tgt = torch.rand(RAYS, 3, generator=torch.Generator().manual_seed(7 + 100 * rank + i))
         pool_h.append(torch.stack([o, d, tgt]).pin_memory())      # one pinned [3, RAYS, 3] block per batch: one H2D copy
-    pool_d = [tuple(b.to(dev)) for b in pool_h]
+    pool_d = [tuple(x.to(dev)) for x in pool_h]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    K, W = args.steps, args.warmup
 
     def step_resident(i):
         o, d, tgt = pool_d[i % n_pool]
@@ -233,34 +274,105 @@ def run_ours(args):
         loss = trainer.step(o, d, tgt)
         host_loss.copy_(loss, non_blocking=True)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    # ------------------------------------------------------------------ headline: K steps, one bracket ----
     for i in range(W):
         step_resident(i)
     barrier()
-    with ClockSampler(local) as clk:                     # spans both timed regions (value and e2e)
-        ms = timed_steps(step_resident, K, flush)
-        barrier()
-        total_ms = float(np.sum(ms))
-        for i in range(max(W // 2, 1)):
-            step_e2e(i)
-        barrier()
-        ms_e2e = timed_steps(step_e2e, K, flush)
-        barrier()
-        time.sleep(0.05)
-    total_e2e = float(np.sum(ms_e2e))
+    total_ms, wall_ms = timed_region(step_resident, K)
+    barrier()
+    for i in range(max(W // 2, 1)):
+        step_e2e(i)
+    barrier()
+    total_e2e, wall_e2e = timed_region(step_e2e, K)
+    barrier()
     loss_val = float(host_loss.item())
+    launches_per_step = trainer.kernel_launches
 
-    # ---- dominant kernel group timed alone: MLP fwd+bwd through the C ABI ----
-    b, s = RAYS, SAMPLES
+    # DP correctness on the hardware: parameters identical on every rank after the timed steps, and the
+    # all-reduced gradient of one more step equal to the 1-GPU gradient of the CONCATENATED batch
+    dp_check = None
+    allreduce_us = None
+    if world > 1:
+        def _dp():
+            flat = model.flat_parameters()
+            lo_, hi_ = flat.clone(), flat.clone()
+            dist.all_reduce(lo_, op=dist.ReduceOp.MIN); dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+            param_spread = float((hi_ - lo_).abs().max().item())
+            # every rank rebuilds ALL ranks' batches (synthetic, seeded by rank) and runs them as ONE batch without the exchange
+            o_all = torch.cat([synthetic_batch(512, seed=5000 + r)[0] for r in range(world)]).to(dev)
+            d_all = torch.cat([synthetic_batch(512, seed=5000 + r)[1] for r in range(world)]).to(dev)
+            t_all = torch.cat([torch.rand(512, 3, generator=torch.Generator().manual_seed(900 + r)) for r in range(world)]).to(dev)
+            u_all = torch.cat([torch.rand(512, s, generator=torch.Generator().manual_seed(950 + r)) for r in range(world)]).to(dev)
+            sl = slice(512 * rank, 512 * (rank + 1))
+            tr_dp = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision)
+            tr_dp.step(o_all[sl].contiguous(), d_all[sl].contiguous(), t_all[sl].contiguous(), u=u_all[sl].contiguous(), apply_update=False)
+            g_dp = tr_dp.flat_grad.clone() / world                          # what Adam sees (grad_scale = 1/world)
+            tr_one = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision, process_group=None)
+            tr_one.world = 1                                               # same kernels, no exchange
+            tr_one.step(o_all, d_all, t_all, u=u_all, apply_update=False)
+            rel = float(((g_dp - tr_one.flat_grad).norm() / tr_one.flat_grad.norm()).item())
+            return {"param_max_abs_spread_across_ranks": param_spread, "grad_rel_l2_vs_single_gpu_concatenated_batch": rel,
+                    "rays_per_rank": 512, "ok": bool(param_spread == 0.0 and rel <= 1e-5)}
+        dp_check = safe("dp_check", _dp)
+
+        def _ar():
+            g = torch.zeros_like(trainer.flat_grad)
+            for _ in range(5):
+                dist.all_reduce(g)
+            barrier()
+            ms = timed_steps(lambda i: dist.all_reduce(g), 20)
+            return {"us": 1e3 * float(np.median(ms)), "bytes": g.numel() * 4, "what": "ncclAllReduce(sum, fp32) of the flat gradient, alone"}
+        allreduce_us = safe("allreduce", _ar)
+
+    # ------------------------------------------------------------------ the reference loop through the public API ----
+    def _api_loop():
+        m2 = NeRF(normalize_position=6.0, precision=args.precision).to(dev); m2.load_state_dict(sd)
+        opt = torch.optim.Adam(m2.parameters(), lr=1e-4)
+
+        def it(i):
+            o, d, tgt = pool_d[i % n_pool]
+            px = m2.render_rays(o, d, NEAR, FAR, SAMPLES, randomly_sample=True, density_noise_std=1.0)
+            opt.zero_grad()
+            ((px - tgt) ** 2).mean().backward()
+            opt.step()
+        for i in range(3):
+            it(i)
+        torch.cuda.synchronize()
+        n = min(K, 50)
+        ms, wall = timed_region(it, n)
+        return {"value": RAYS * n / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms / n, "wall_ms_per_step": wall / n, "steps": n,
+                "what": "example.ipynb cell 8 / train_conditional_nerf.py:120-135 verbatim: pixels = nerf.render_rays(...); "
+                        "loss.backward(); torch.optim.Adam.step() -- per GPU, no gradient exchange",
+                "tcgen05_calls": {k: v for k, v in ops.COUNTERS.items() if "tc" in k}}
+    api_loop = safe("api_loop", _api_loop)
+
+    # ------------------------------------------------------------------ the other precision of config 2 ----
+    def _other_precision():
+        other = "fp32" if args.precision == "bf16" else "bf16"
+        m3 = NeRF(normalize_position=6.0, precision=other).to(dev); m3.load_state_dict(sd)
+        tr3 = Trainer(m3, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=1234)
+        tr3.world = 1
+
+        def it(i):
+            o, d, tgt = pool_d[i % n_pool]
+            tr3.step(o, d, tgt)
+        for i in range(2):
+            it(i)
+        torch.cuda.synchronize()
+        n = min(K, 10) if other == "fp32" else min(K, 50)
+        ms, _ = timed_region(it, n)
+        return {"value": RAYS * n / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms / n, "steps": n, "precision": other, "per_gpu": True,
+                "contraction": "fp32 FFMA tiles (mlp_fp32_*.cuh)" if other == "fp32" else "tcgen05 kind::f16",
+                "mlp_tflops": RAYS * SAMPLES * FLOP_PER_POINT_FWD_BWD * n / (ms * 1e-3) / 1e12}
+    other_prec = safe("other_precision", _other_precision)
+
+    # ------------------------------------------------------------------ kernels timed alone through the C ABI ----
     o, d, tgt = pool_d[0]
     flat = model.flat_parameters()
     P = _lib.ptr
     L = _lib.lib()
     kernels = {}
+    roofline = None
     if args.precision == "bf16":
         z = trainer._tc_buffers(b, s, dev)
         ladder = model._ladder(NEAR, FAR, s, dev)
@@ -284,26 +396,44 @@ def run_ours(args):
         ms_fwd = float(np.mean(timed_steps(k_fwd, n_it, flush)))
         ms_dgrad = float(np.mean(timed_steps(k_bwd(1), n_it, flush)))
         ms_wg = float(np.mean(timed_steps(k_bwd(3), n_it, flush)))
-        ms_mlp = float(np.mean(timed_steps(mlp_only, n_it, flush)))
+        ms_mlp, _ = timed_region(mlp_only, n_it); ms_mlp /= n_it
         n_tiles = (b * s + 127) // 128
         wgrad_bytes = n_tiles * ((10 + 9 + 2) * 65536 + 3 * 16384 + 2 * 4096)     # dz + unit inputs + head inputs + encodings + dh
         act_bytes = n_tiles * 65536                                                # one unit's [128 x 256] bf16 slabs, all tiles
         fwd_bytes = 10 * act_bytes + 2 * n_tiles * 16384 + 10 * n_tiles * 128 * 8 + b * s * 20   # activations, encodings, stats, t/sigma/rgb
         dgrad_bytes = 20 * act_bytes + 10 * n_tiles * 128 * 8 + n_tiles * 4096 + b * s * 16      # n_l in, dz_l out, stats, dh image, d_sigma/d_rgb
-        traffic = ncu_traffic()
+        ncu = ncu_counters(NCU_TRAIN, ("g1_fused_tc_kernel", "g1_bwd_tc_kernel", "g1_wgrad_tc_kernel"))
+        io_bytes_8d = b * 24 + b * s * 20                  # what the MLP must move -- rays in, (t, sigma, rgb) out
 
-        def kern(name, ms, flop, nbytes):
-            tf, gbs = flop / ms / 1e9, nbytes / ms / 1e6
-            ft, fh = tf / peaks["tensor_sustained"], gbs / peaks["hbm"]
-            return {"ms": ms, "bound": "tensor" if ft >= fh else "hbm", "frac": max(ft, fh),
-                    "tensor": {"achieved": tf, "unit": "TFLOP/s", "frac": ft}, "hbm": {"achieved": gbs, "unit": "GB/s", "frac": fh, "bytes": nbytes},
-                    "traffic": traffic.get(name)}
+        def kern(name, ms, flop, design_bytes):
+            tf, gbs = flop / ms / 1e9, design_bytes / ms / 1e6
+            c = ncu.get(name, {})
+            return {"ms": ms, "flop": flop,
+                    # the MLP kernels are scored on the TENSOR roofline; a kernel timed alone gets the BURST peak
+                    "tensor": {"achieved": tf, "unit": "TFLOP/s", "peak": peaks["tensor_burst"], "frac": tf / peaks["tensor_burst"],
+                               "frac_of_sustained": tf / peaks["tensor_sustained"], "tensor_pipe_pct_ncu": c.get("tensor_pipe_pct")},
+                    # the HBM view of THIS design: the bf16 activation stash is traffic the design chose, not algorithmic bytes
+                    "hbm_design": {"achieved": gbs, "unit": "GB/s", "peak": peaks["hbm"], "frac": gbs / peaks["hbm"], "stash_bytes": design_bytes,
+                                   "traffic_ncu": c.get("dram_bytes"), "ncu_source": c.get("source")}}
         kernels = {
             "g1_fused_tc_kernel<2,train>": kern("g1_fused_tc_kernel", ms_fwd, FLOP_PER_POINT_FWD * b * s, fwd_bytes),
             "g1_bwd_tc_kernel<2>": kern("g1_bwd_tc_kernel", ms_dgrad, 2 * 9 * 65536 * b * s, dgrad_bytes),
             "g1_wgrad_tc_kernel": kern("g1_wgrad_tc_kernel", ms_wg, 2 * (9 * 65536 + 3 * 16384 + 10 * 256 + 2 * 1024) * b * s, wgrad_bytes),
         }
-        mlp_kernel_name = "G1 MLP fwd+bwd on tcgen05 (g1_fused_tc_kernel<train> + g1_bwd_tc_kernel + g1_wgrad_tc_kernel + unfold)"
+        name, k = max(kernels.items(), key=lambda kv: kv[1]["ms"])
+        traffic = k["hbm_design"]["traffic_ncu"]
+        roofline = {"bound": "tensor", "kernel": name, "achieved": k["tensor"]["achieved"], "peak": peaks["tensor_burst"], "unit": "TFLOP/s",
+                    "frac": k["tensor"]["frac"], "traffic": traffic, "ms": k["ms"],
+                    "peak_source": peaks["src"] + " bf16 burst (kernel timed alone); SURVEY 8(d): MLP kernels on the tensor roofline",
+                    "tensor_pipe_pct_ncu": k["tensor"]["tensor_pipe_pct_ncu"], "flop_per_launch": k["flop"],
+                    "algorithmic_bytes_8d": io_bytes_8d,
+                    "wasted_traffic_x": None if not traffic else traffic / io_bytes_8d}
+        total_traffic = sum((v["hbm_design"]["traffic_ncu"] or v["hbm_design"]["stash_bytes"]) for v in kernels.values())
+        roofline_hbm_design = {"note": "HBM view of the activation-stash design: bytes the three kernels move per step against the copy peak",
+                               "bytes_per_step": total_traffic, "floor_ms_at_copy_peak": total_traffic / peaks["hbm"] / 1e6,
+                               "vs_8d_bytes_x": total_traffic / io_bytes_8d,
+                               "kernels": {kn: v["hbm_design"] for kn, v in kernels.items()}}
+        mlp_kernel_name = "G1 MLP fwd+bwd on tcgen05 (" + " + ".join(kernels) + " + unfold)"
     else:
         t = ops.sample_linear(NEAR, FAR, s, b, dev, jitter=True, seed=1)
         ex, ed, _ = ops.encode_g1(o, d, t, 6.0)
@@ -321,7 +451,11 @@ def run_ours(args):
             mlp_only(i)
         ms_mlp = float(np.mean(timed_steps(mlp_only, max(K // 2, 3), flush)))
         mlp_kernel_name = "G1 MLP fwd+bwd (nerf_g1_mlp_fwd + nerf_g1_mlp_bwd, FFMA tiles)"
+        roofline_hbm_design = None
     mlp_tflops = FLOP_PER_POINT_FWD_BWD * b * s / (ms_mlp * 1e-3) / 1e12
+    if roofline is None:
+        roofline = {"bound": "tensor", "kernel": mlp_kernel_name, "achieved": mlp_tflops, "peak": peaks["tensor_sustained"], "unit": "TFLOP/s",
+                    "frac": mlp_tflops / peaks["tensor_sustained"], "traffic": None, "peak_source": peaks["src"] + " bf16 sustained", "ms": ms_mlp}
 
     # ---- compositing fwd+bwd alone at a sweep size larger than L2 (HBM roofline) ----
     cb = 1 << 20
@@ -359,145 +493,192 @@ def run_ours(args):
     # ---- render throughput: 800x800 x 64 (fused bf16 path) or 200x200 (fp32 path) through render_image ----
     from oracle.g1 import pose_spherical, TINY_NERF_FOCAL
     pose = pose_spherical(30.0, -30.0, 4.0311).to(dev)
+    cam_o, cam_r = pose[None, :3, 3].contiguous(), pose[None, :3, :3].contiguous()
     rh = rw = 800 if args.precision == "bf16" else 200
     rfocal = TINY_NERF_FOCAL * rh / 100
     with torch.no_grad():
-        model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES)
-        ms_r = timed_steps(lambda i: model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw,
-                                                        rfocal, NEAR, FAR, SAMPLES), 3, flush)
+        model.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES)
+        ms_r = timed_steps(lambda i: model.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES), 3, flush)
     render_rps = rh * rw / (float(np.mean(ms_r)) * 1e-3)
     render_tflops = render_rps * SAMPLES * FLOP_PER_POINT_FWD / 1e12
-    # D3: 64 coarse + 128 fine samples (hierarchical inverse-CDF pass, 192-point fine evaluation)
+    rncu = ncu_counters(NCU_RENDER, ("g1_fused_tc_kernel",)).get("g1_fused_tc_kernel", {})
+
+    # ---- D3 / config 3: 800x800, 64 coarse + 128 fine, RAY-SHARDED over the ranks, frame gathered ----
     d3 = None
+    render_sharded = None
     if args.precision == "bf16":
-        with torch.no_grad():
-            model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES, num_fine=128)
-            ms_d3 = timed_steps(lambda i: model.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw,
-                                                             rfocal, NEAR, FAR, SAMPLES, num_fine=128), 2, flush)
-        d3_rps = rh * rw / (float(np.mean(ms_d3)) * 1e-3)
-        d3 = {"value": d3_rps, "unit": "rays/s", "workload": f"{rh}x{rw}, 64 coarse + 128 fine samples (256 MLP evaluations per ray)",
-              "mlp_tflops": d3_rps * 256 * FLOP_PER_POINT_FWD / 1e12, "frac_tensor": d3_rps * 256 * FLOP_PER_POINT_FWD / 1e12 / peaks["tensor_sustained"]}
+        def _d3():
+            kw = dict(num_fine=128)
+            total = rh * rw
+            with torch.no_grad():
+                parallel.render_image_sharded(model, cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES, gather=True, **kw)    # warm-up
+                barrier()
+                # (i) the shard alone: no collective in the timed region
+                lo, hi = parallel.shard_range(total, rank, world)
+                ms_sh = float(np.mean(timed_steps(lambda i: model.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES,
+                                                                                ray_begin=lo, ray_end=hi, **kw), 2)))
+                barrier()
+                # (ii) shard + all_gather of the [rays/N, 3] pieces into the frame on every rank
+                ms_g = timed_steps(lambda i: parallel.render_image_sharded(model, cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES,
+                                                                           gather=True, **kw), 2)
+                frame = parallel.render_image_sharded(model, cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES, gather=True, **kw)
+                ms_g = float(np.mean(ms_g))
+                barrier()
+                ms_sh, ms_g = max_over_ranks(ms_sh, ms_g)
+                equal = None
+                if rank == 0:                                        # the gathered frame against the 1-GPU render of the whole frame
+                    full = model.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES, **kw)
+                    equal = {"bit_identical": bool(torch.equal(full, frame)), "max_abs_diff": float((full - frame).abs().max().item())}
+                barrier()
+            rps = total / (ms_sh * 1e-3)
+            return {"value": rps, "unit": "rays/s", "n_gpus": world, "ms_per_frame": ms_sh, "scaling": "strong",
+                    "workload": f"{rh}x{rw}, 64 coarse + 128 fine samples (256 MLP evaluations per ray); rank r renders "
+                                f"shard_range({total}, r, {world}); no collective in the timed region; time = max over ranks",
+                    "with_all_gather": {"value": total / (ms_g * 1e-3), "ms_per_frame": ms_g},
+                    "gathered_frame_vs_single_gpu": equal,
+                    "mlp_tflops": rps * 256 * FLOP_PER_POINT_FWD / 1e12,
+                    "frac_tensor_sustained": rps * 256 * FLOP_PER_POINT_FWD / 1e12 / (world * peaks["tensor_sustained"])}
+        render_sharded = safe("render_sharded", _d3)
+        if world == 1 and "value" in render_sharded:
+            d3 = {"value": render_sharded["value"], "unit": "rays/s", "workload": render_sharded["workload"],
+                  "mlp_tflops": render_sharded["mlp_tflops"], "frac_tensor": render_sharded["frac_tensor_sustained"]}
 
-    # ---- HEAD generation (fp32 FFMA path): render_image 200x200 x 64 fenceposts (63 intervals per ray) ----
-    from nerf_b200.head import HeadNeRF
-    torch.manual_seed(3)
-    hm = HeadNeRF().to(dev)
-    hh = 200
-    with torch.no_grad():
-        hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES)
-        ms_h = timed_steps(lambda i: hm.render_image(pose[None, :3, 3], pose[None, :3, :3], hh, hh, 224.0, SAMPLES), 3, flush)
-    head_rps = hh * hh / (float(np.mean(ms_h)) * 1e-3)
-    head_tflops = head_rps * (SAMPLES - 1) * 601_088 / 1e12
-    # ... its fp32 training step through the public API (render_rays -> loss.backward(): composite + trunk backward
-    # kernels of head.cu; torch.optim.Adam on the 22 tensors), 4096 rays x 64 fenceposts
-    hopt = torch.optim.Adam(hm.parameters(), lr=1e-4)
-    hg = torch.Generator(device="cpu").manual_seed(8)
-    ho = (torch.randn(RAYS, 3, generator=hg) * 2).to(dev); hd = torch.randn(RAYS, 3, generator=hg).to(dev)
-    htgt = torch.rand(RAYS, 3, generator=hg).to(dev); hlab = torch.randint(0, 50, (RAYS,), generator=hg).to(dev)
+    head = None
+    c4 = {"train": None, "render": None}
+    if world == 1 or args.all_sections:
+        # ---- HEAD generation (fp32 FFMA path): render_image 200x200 x 64 fenceposts (63 intervals per ray) ----
+        def _head():
+            from nerf_b200.head import HeadNeRF
+            torch.manual_seed(3)
+            hm = HeadNeRF().to(dev)
+            hh = 200
+            with torch.no_grad():
+                hm.render_image(cam_o, cam_r, hh, hh, 224.0, SAMPLES)
+                ms_h = timed_steps(lambda i: hm.render_image(cam_o, cam_r, hh, hh, 224.0, SAMPLES), 3, flush)
+            head_rps = hh * hh / (float(np.mean(ms_h)) * 1e-3)
+            # ... its fp32 training step through the public API (render_rays -> loss.backward(): composite + trunk backward
+            # kernels of head.cu; torch.optim.Adam on the 22 tensors), 4096 rays x 64 fenceposts
+            hopt = torch.optim.Adam(hm.parameters(), lr=1e-4)
+            hg = torch.Generator(device="cpu").manual_seed(8)
+            ho = (torch.randn(RAYS, 3, generator=hg) * 2).to(dev); hd = torch.randn(RAYS, 3, generator=hg).to(dev)
+            htgt = torch.rand(RAYS, 3, generator=hg).to(dev); hlab = torch.randint(0, 50, (RAYS,), generator=hg).to(dev)
 
-    def head_step(i):
-        hopt.zero_grad(set_to_none=True)
-        himg, hseg = hm.render_rays(ho, hd, SAMPLES, randomly_sample=True, density_noise_std=1.0, seed=i)
-        hl = ((himg[:, 0] - htgt) ** 2).mean() + torch.nn.functional.nll_loss(hseg[:, 0], hlab)
-        hl.backward(); hopt.step()
-    head_step(0)
-    ms_ht = timed_steps(head_step, 3, flush)
-    head_train_rps = RAYS / (float(np.mean(ms_ht)) * 1e-3)
-    # ... and its tcgen05 bf16 path (head_tc.cu): 800x800
-    torch.manual_seed(3)
-    hb = HeadNeRF(precision="bf16").to(dev)
-    hbh = 800
-    with torch.no_grad():
-        hb.render_image(pose[None, :3, 3], pose[None, :3, :3], hbh, hbh, 896.0, SAMPLES)
-        ms_hb = timed_steps(lambda i: hb.render_image(pose[None, :3, 3], pose[None, :3, :3], hbh, hbh, 896.0, SAMPLES), 3, flush)
-    headb_rps = hbh * hbh / (float(np.mean(ms_hb)) * 1e-3)
-    headb_tflops = headb_rps * (SAMPLES - 1) * 601_088 / 1e12
+            def head_step(i):
+                hopt.zero_grad(set_to_none=True)
+                himg, hseg = hm.render_rays(ho, hd, SAMPLES, randomly_sample=True, density_noise_std=1.0)
+                hl = ((himg[:, 0] - htgt) ** 2).mean() + torch.nn.functional.nll_loss(hseg[:, 0], hlab)
+                hl.backward(); hopt.step()
+            head_step(0)
+            ms_ht = timed_steps(head_step, 3, flush)
+            head_train_rps = RAYS / (float(np.mean(ms_ht)) * 1e-3)
+            # ... and its tcgen05 bf16 path (head_tc.cu): 800x800
+            torch.manual_seed(3)
+            hb = HeadNeRF(precision="bf16").to(dev)
+            hbh = 800
+            with torch.no_grad():
+                hb.render_image(cam_o, cam_r, hbh, hbh, 896.0, SAMPLES)
+                ms_hb = timed_steps(lambda i: hb.render_image(cam_o, cam_r, hbh, hbh, 896.0, SAMPLES), 3, flush)
+            headb_rps = hbh * hbh / (float(np.mean(ms_hb)) * 1e-3)
+            headb_tflops = headb_rps * (SAMPLES - 1) * 601_088 / 1e12
+            return {
+                "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
+                                "mlp_tflops": head_rps * (SAMPLES - 1) * 601_088 / 1e12},
+                "head_train_fp32": {"value": head_train_rps, "unit": "rays/s", "ms_per_step": float(np.mean(ms_ht)),
+                                    "workload": f"HEAD (mip-NeRF) train step fwd+bwd+Adam, {RAYS} rays x {SAMPLES} fenceposts, fp32 FFMA (head.cu), colour MSE + segmentation NLL",
+                                    "mlp_tflops": head_train_rps * (SAMPLES - 1) * 1_754_112 / 1e12},
+                "head_render_bf16": {"value": headb_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hbh}x{hbh} x {SAMPLES} fenceposts render_image, tcgen05 bf16 (head_tc_kernel)",
+                                     "mlp_tflops": headb_tflops, "frac_tensor": headb_tflops / peaks["tensor_sustained"]}}
+        head = safe("head", _head)
 
-    # ---- C4 / D4: the same step with latent-coded inputs (8 scenes, states_x in [-1,1]^4 => density_inputs 7) ----
-    c4_ms = None
-    c4_render = None
+    # ---- C4 / D4: the same step with latent-coded inputs (8 scenes, states_x in [-1,1]^4 => density_inputs 7), data-parallel ----
     if args.precision == "bf16":
-        torch.manual_seed(5)
-        cm = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").to(dev)
-        sx1 = torch.tensor([[0.3, -0.2, 0.7, -0.9]], device=dev)         # validation render of train_conditional_nerf.py:141-153
-        with torch.no_grad():
-            cm.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES, states_x=sx1)
-            ms_c4r = timed_steps(lambda i: cm.render_image(pose[None, :3, 3], pose[None, :3, :3], rh, rw, rfocal, NEAR, FAR, SAMPLES,
-                                                           states_x=sx1), 3, flush)
-        c4_rps = rh * rw / (float(np.mean(ms_c4r)) * 1e-3)
-        c4_render = {"value": c4_rps, "unit": "rays/s", "workload": f"conditional {rh}x{rw} x {SAMPLES} samples render_image(states_x=[1,4])",
-                     "mlp_tflops": c4_rps * SAMPLES * 1_343_488 / 1e12}        # G1 + 4 latents: 671 744 MAC per point
-        ctr = Trainer(cm, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=4321)
-        g4 = torch.Generator().manual_seed(4)
-        scenes = torch.rand(8, 4, generator=g4) * 2 - 1
-        c4_pool = [scenes[torch.randint(0, 8, (RAYS,), generator=g4)].to(dev) for _ in range(n_pool)]
+        def _c4():
+            torch.manual_seed(5)
+            cm = NeRF(normalize_position=6.0, density_inputs=7, precision="bf16").to(dev)
+            parallel.broadcast_parameters(cm)
+            sx1 = torch.tensor([[0.3, -0.2, 0.7, -0.9]], device=dev)         # validation render of train_conditional_nerf.py:141-153
+            with torch.no_grad():
+                cm.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES, states_x=sx1)
+                ms_c4r = timed_steps(lambda i: cm.render_image(cam_o, cam_r, rh, rw, rfocal, NEAR, FAR, SAMPLES, states_x=sx1), 3, flush)
+            c4_rps = rh * rw / (float(np.mean(ms_c4r)) * 1e-3)
+            ctr = Trainer(cm, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=4321)
+            g4 = torch.Generator().manual_seed(4 + rank)
+            scenes = torch.rand(8, 4, generator=torch.Generator().manual_seed(4)) * 2 - 1
+            c4_pool = [scenes[torch.randint(0, 8, (RAYS,), generator=g4)].to(dev) for _ in range(n_pool)]
 
-        def step_c4(i):
-            o_, d_, tgt_ = pool_d[i % n_pool]
-            return ctr.step(o_, d_, tgt_, states_x=c4_pool[i % n_pool])
-        for i in range(3):
-            step_c4(i)
-        barrier()
-        c4_ms = float(np.sum(timed_steps(step_c4, min(K, 50), flush))) / min(K, 50)
+            def step_c4(i):
+                o_, d_, tgt_ = pool_d[i % n_pool]
+                return ctr.step(o_, d_, tgt_, states_x=c4_pool[i % n_pool])
+            for i in range(3):
+                step_c4(i)
+            barrier()
+            n = min(K, 50)
+            ms, _ = timed_region(step_c4, n)
+            barrier()
+            ms = max_over_ranks(ms)[0]
+            return {"train": {"value": world * RAYS * n / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms / n, "n_gpus": world,
+                              "workload": "conditional train step (8 scenes, 4 latents per ray: block_0.0.weight [256,140]), 4096 rays x 64 samples per GPU, data-parallel"},
+                    "render": {"value": c4_rps, "unit": "rays/s", "workload": f"conditional {rh}x{rw} x {SAMPLES} samples render_image(states_x=[1,4]), one GPU",
+                               "mlp_tflops": c4_rps * SAMPLES * 1_343_488 / 1e12}}        # G1 + 4 latents: 671 744 MAC per point
+        r = safe("c4", _c4)
+        c4 = r if "train" in r else {"train": r, "render": None}
 
     # max over ranks of the timed totals
-    if world > 1:
-        tt = torch.tensor([total_ms, total_e2e, c4_ms or 0.0], device=dev, dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        total_ms, total_e2e, c4_max = tt.tolist()
-        c4_ms = c4_max if c4_ms is not None else None
+    total_ms, total_e2e, wall_ms, wall_e2e = max_over_ranks(total_ms, total_e2e, wall_ms, wall_e2e)
     value = world * RAYS * K / (total_ms * 1e-3)
     e2e = world * RAYS * K / (total_e2e * 1e-3)
+    time.sleep(0.05)
+    clk.__exit__(None, None, None)
 
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            rps, secs = cpu_train_step_rays_per_s(1024, 8, warmup=1)
+            rps, secs = cpu_train_step_rays_per_s(RAYS, 5, warmup=1)
             cpu = {"value": rps, "unit": "rays/s", "cores": os.cpu_count(), "kind": "port",
-                   "sample": f"oracle G1 train step (fwd+bwd+Adam), 1024 rays x {SAMPLES} samples, median of 8 ({secs:.1f} s)"}
+                   "sample": f"oracle G1 train step (fwd+bwd+Adam) on the full batch, {RAYS} rays x {SAMPLES} samples, median of 5 ({secs:.1f} s)"}
         tensor_peak = peaks["tensor_sustained"]
         line = {
             "metric": "rays/sec (train fwd+bwd)", "value": value, "unit": "rays/s", "n_gpus": world,
             "steps": K, "warmup": W, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32" if args.precision == "fp32" else "bf16", "data": "synthetic",
-            "config": {"workload": "tiny NeRF train step fwd+bwd+Adam, 4096-ray batches x 64 samples (G1, nerf.pth), per GPU",
-                       "rays_per_gpu": RAYS, "samples": SAMPLES, "precision": args.precision,
-                       "l2": "256 MiB flush between timed steps", "parallelism": f"dp{world}"},
-            "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": RAYS * 9 * 4, "d2h_bytes_per_step": 4},
-            "gpu_launches": trainer.kernel_launches * K,
+            "config": bench_config(world),
+            "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": RAYS * 9 * 4, "d2h_bytes_per_step": 4,
+                    "ms_per_step": total_e2e / K, "wall_ms_per_step": wall_e2e / K,
+                    "what": "Trainer.step on a batch copied from pinned host memory each step, loss copied back each step"},
+            "wall_ms_per_step": wall_ms / K,
+            "gpu_launches": launches_per_step * K,
             "clocks": clk.summary(),
-            "roofline": dominant_roofline(kernels, peaks) if kernels else
-                        {"bound": "tensor", "kernel": mlp_kernel_name, "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
-                         "frac": mlp_tflops / tensor_peak, "traffic": None, "peak_source": peaks["src"] + " bf16 sustained", "ms": ms_mlp},
+            "roofline": roofline,
             "roofline_mlp_step": {"bound": "tensor", "kernel": mlp_kernel_name, "achieved": mlp_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
-                                  "frac": mlp_tflops / tensor_peak, "ms": ms_mlp},
+                                  "frac": mlp_tflops / tensor_peak, "ms": ms_mlp,
+                                  "peak_source": peaks["src"] + " bf16 sustained (kernels back to back inside a step)"},
+            "roofline_hbm_design": roofline_hbm_design,
             "roofline_hbm": {"composite_fwd": {"achieved": comp_fwd_gbs, "frac": comp_fwd_gbs / peaks["hbm"], "ms": ms_cf},
                              "composite_bwd": {"achieved": comp_bwd_gbs, "frac": comp_bwd_gbs / peaks["hbm"], "ms": ms_cb},
                              "sample_host_u": {"achieved": samp_u_gbs, "frac": samp_u_gbs / peaks["hbm"], "ms": ms_su},
                              "sample_philox": {"achieved": samp_p_gbs, "frac": samp_p_gbs / peaks["hbm"], "ms": ms_sp,
                                                "note": "fma-pipe bound: 20 IMAD.WIDE per 4 samples (Philox4x32-10)"},
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
-            "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image",
-                       "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak},
-            "train_c4": None if c4_ms is None else {
-                "value": world * RAYS / (c4_ms * 1e-3), "unit": "rays/s", "ms_per_step": c4_ms,
-                "workload": "conditional train step (8 scenes, 4 latents per ray: block_0.0.weight [256,140]), 4096 rays x 64 samples per GPU"},
+            "fp32" if args.precision == "bf16" else "bf16": other_prec,
+            "api_loop": api_loop,
+            "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image, one GPU",
+                       "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak,
+                       "frac_tensor_burst": render_tflops / peaks["tensor_burst"], "tensor_pipe_pct_ncu": rncu.get("tensor_pipe_pct"),
+                       "ncu_source": rncu.get("source")},
+            "render_sharded": render_sharded,
             "render_d3": d3,
-            "render_c4": c4_render,
+            "train_c4": c4["train"], "render_c4": c4["render"],
+            "dp_check": dp_check, "allreduce": allreduce_us,
             "kernels": kernels,
-            "head_render": {"value": head_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hh}x{hh} x {SAMPLES} fenceposts render_image, fp32 FFMA",
-                            "mlp_tflops": head_tflops},
-            "head_train_fp32": {"value": head_train_rps, "unit": "rays/s", "ms_per_step": float(np.mean(ms_ht)),
-                                "workload": f"HEAD (mip-NeRF) train step fwd+bwd+Adam, {RAYS} rays x {SAMPLES} fenceposts, fp32 FFMA (head.cu), colour MSE + segmentation NLL",
-                                "mlp_tflops": head_train_rps * (SAMPLES - 1) * 1_754_112 / 1e12},
-            "head_render_bf16": {"value": headb_rps, "unit": "rays/s", "workload": f"HEAD (mip-NeRF) {hbh}x{hbh} x {SAMPLES} fenceposts render_image, tcgen05 bf16 (head_tc_kernel)",
-                                 "mlp_tflops": headb_tflops, "frac_tensor": headb_tflops / tensor_peak},
             "loss": loss_val,
         }
+        if isinstance(head, dict):
+            line.update(head if "error" not in head else {"head": head})
         if cpu:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -509,6 +690,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--all-sections", action="store_true", help="also run the HEAD sections at N > 1")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -13,11 +13,33 @@ int nerf_set_error(cudaError_t e);   // records + returns (int)e
     if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)
 #define NERF_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)
 
+// Per-DEVICE caches (a process may touch more than one GPU): SM count and the opt-in shared-memory attribute.
+#define NERF_MAX_DEVICES 64
+static inline int nerf_current_device() { int dev = 0; cudaGetDevice(&dev); return dev; }
 static inline int nerf_num_sms() {
-    static int n = 0;
-    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
-    return n;
+    static int n[NERF_MAX_DEVICES] = {};
+    const int dev = nerf_current_device();
+    int v = (dev >= 0 && dev < NERF_MAX_DEVICES) ? n[dev] : 0;
+    if (!v) {
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev); if (v <= 0) v = 148;
+        if (dev >= 0 && dev < NERF_MAX_DEVICES) n[dev] = v;
+    }
+    return v;
 }
+// cudaFuncAttributeMaxDynamicSharedMemorySize once per (kernel, device)
+template <auto Kernel>
+static inline cudaError_t nerf_smem_opt_in(int bytes) {
+    static bool done[NERF_MAX_DEVICES] = {};
+    const int dev = nerf_current_device();
+    if (dev >= 0 && dev < NERF_MAX_DEVICES && done[dev]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && dev >= 0 && dev < NERF_MAX_DEVICES) done[dev] = true;
+    return e;
+}
+// tuning knobs from the environment, read once per process (not per launch)
+#include <stdlib.h>
+static inline uint32_t nerf_env_u32(const char* name, uint32_t dflt) { const char* e = getenv(name); return e ? (uint32_t)strtoul(e, nullptr, 0) : dflt; }
+static inline bool nerf_env_set(const char* name) { return getenv(name) != nullptr; }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

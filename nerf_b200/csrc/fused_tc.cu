@@ -250,18 +250,15 @@ static int launch_fused(const void* packed, int Dx, int Dd, FusedArgs& a, cudaSt
     for (int l = 0; l < 10; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.unit_off[l] = L.unit_off[l]; }
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_vec_offset(L));
-    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
-    { const char* e = getenv("NERF_FWD_STORE_GAP"); a.store_gap = e ? (uint32_t)atoi(e) : 600u; }   // measured: 0 -> 0.410, 400-800 -> 0.389-0.393, 1200 -> 0.442 ms
-    static int cg = -1;
-    if (cg < 0) {
-        const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2;
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        NERF_CUDA(cudaFuncSetAttribute(g1_fused_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-    }
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    static const uint32_t store_gap = nerf_env_u32("NERF_FWD_STORE_GAP", 600u);   // measured: 0 -> 0.410, 400-800 -> 0.389-0.393, 1200 -> 0.442 ms
+    static const int cg = nerf_env_u32("NERF_TC_CG", 2) == 1 ? 1 : 2;
+    static const bool prof = nerf_env_set("NERF_TC_PROF");
+    a.wait_hint = wait_hint; a.store_gap = store_gap;
+    if (cg == 2) NERF_CUDA(train ? (nerf_smem_opt_in<g1_fused_tc_kernel<2, true>>(TC_SMEM_BYTES)) : (nerf_smem_opt_in<g1_fused_tc_kernel<2, false>>(TC_SMEM_BYTES)));
+    else NERF_CUDA(train ? (nerf_smem_opt_in<g1_fused_tc_kernel<1, true>>(TC_SMEM_BYTES)) : (nerf_smem_opt_in<g1_fused_tc_kernel<1, false>>(TC_SMEM_BYTES)));
     a.prof = nullptr;
-    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
+    if (prof) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
     const int sms = nerf_num_sms();
     if (cg == 2) {
         int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;

@@ -445,9 +445,9 @@ extern "C" int nerf_head_fwd_tc(const void* packed, const float* rays_o, const f
     for (int l = 0; l < HT_UNITS; ++l) { a.nk[l] = L.nk[l]; a.half_kcores[l] = L.half_kcores[l]; a.kcore_bytes[l] = L.kcore_bytes[l]; a.unit_off[l] = L.unit_off[l]; }
     a.rays_o = rays_o; a.rays_d = rays_d; a.t = t; a.B = B; a.S = S; a.P = B * (int64_t)(S - 1); a.n_tiles = (int)((a.P + 127) / 128);
     a.base_radius = base_radius; a.min_deg = min_deg; a.out = out; a.n_out = n_out; a.mean_out = mean_out; a.log_softmax_seg = log_softmax_seg;
-    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
-    static bool attr = false;
-    if (!attr) { NERF_CUDA(cudaFuncSetAttribute(head_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HT_SMEM_BYTES)); attr = true; }
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    a.wait_hint = wait_hint;
+    NERF_CUDA(nerf_smem_opt_in<head_tc_kernel>(HT_SMEM_BYTES));
     const int sms = nerf_num_sms();
     const int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
     cudaLaunchConfig_t cfg{};

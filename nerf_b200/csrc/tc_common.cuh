@@ -43,14 +43,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_
     }
 }
 
-// The same wait without the iteration counter, for the one-warp role loops whose instruction count per
-// stage is the kernel's critical path (the protocol there is covered by the tests; the epilogue side keeps
-// the trapping version).
+// The same wait for the one-warp role loops whose instruction count per stage is the kernel's critical path: the
+// fast path is ONE try_wait + branch.  Only after a failed try does it start reading %globaltimer, and a phase
+// that has not completed 5 s later traps (a protocol slip then fails the launch instead of hanging the GPU).
 __device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity, uint32_t hint) {
-    asm volatile("{\n\t.reg .pred p;\n\t"
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 t0, t1;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+                 "@p bra WAIT_DONE;\n\t"
+                 "mov.u64 t0, %%globaltimer;\n\t"
                  "WAIT_LOOP:\n\t"
                  "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
                  "@p bra WAIT_DONE;\n\t"
+                 "mov.u64 t1, %%globaltimer;\n\t"
+                 "sub.u64 t1, t1, t0;\n\t"
+                 "setp.gt.u64 p, t1, 5000000000;\n\t"
+                 "@p trap;\n\t"
                  "bra WAIT_LOOP;\n\t"
                  "WAIT_DONE:\n\t}"
                  ::"r"(bar), "r"(parity), "r"(hint) : "memory");

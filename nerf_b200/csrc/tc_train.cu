@@ -217,9 +217,9 @@ __global__ void __launch_bounds__(1024) unfold_kernel(const float* __restrict__ 
 template <int CG>
 static int launch_bwd(BwdArgs& a, cudaStream_t st) {
     a.prof = nullptr;
-    if (getenv("NERF_TC_PROF")) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
-    static bool init = false;
-    if (!init) { NERF_CUDA(cudaFuncSetAttribute(g1_bwd_tc_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, TB_SMEM_BYTES)); init = true; }
+    static const bool want_prof = nerf_env_set("NERF_TC_PROF");     // debug timeline: allocates and synchronises, never on by default
+    if (want_prof) { NERF_CUDA(cudaMalloc(&a.prof, 192 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 192 * sizeof(long long))); }
+    NERF_CUDA(nerf_smem_opt_in<g1_bwd_tc_kernel<CG>>(TB_SMEM_BYTES));
     const int sms = nerf_num_sms();
     if (CG == 2) {
         int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
@@ -312,10 +312,10 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz = ws + T.off_dz; a.dh = ws + T.off_dh;
     a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
     a.P = T.P; a.P_pad = T.P_pad; a.n_tiles = T.n_tiles; a.tr_tiles = T.tr_tiles;
-    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
-    { const char* e = getenv("NERF_BWD_PF"); const int v = e ? atoi(e) : 11; a.pf_dist = v % 10; a.pf_next = v >= 10; }
-    static int cg = -1;
-    if (cg < 0) { const char* e = getenv("NERF_TC_CG"); cg = (e && atoi(e) == 1) ? 1 : 2; }
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    static const int pf = (int)nerf_env_u32("NERF_BWD_PF", 11);
+    static const int cg = nerf_env_u32("NERF_TC_CG", 2) == 1 ? 1 : 2;
+    a.wait_hint = wait_hint; a.pf_dist = pf % 10; a.pf_next = pf >= 10;
     if (stage != 3) { rc = (cg == 2) ? launch_bwd<2>(a, st) : launch_bwd<1>(a, st); if (rc) return rc; }
     if (stage == 1) return NERF_OK;
     rc = launch_wgrad_tc_units(ws, T, st); if (rc) return rc;

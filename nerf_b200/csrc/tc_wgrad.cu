@@ -287,13 +287,11 @@ __global__ void __launch_bounds__(WG_THREADS, 1) g1_wgrad_tc_kernel(const WgradA
 }
 
 int launch_wgrad_tc(WgradArgs& a, cudaStream_t st) {
-    static bool init = false;
-    if (!init) {
-        NERF_CUDA(cudaFuncSetAttribute(g1_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES));
-        init = true;
-    }
-    { const char* e = getenv("NERF_TC_WAIT_HINT"); a.wait_hint = e ? (uint32_t)strtoul(e, nullptr, 0) : 0x989680u; }
-    { const char* e = getenv("NERF_WG_DBG"); a.dbg = e ? atoi(e) : 0; }
+    NERF_CUDA(nerf_smem_opt_in<g1_wgrad_tc_kernel>(WG_SMEM_BYTES));
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    static const int dbg = (int)nerf_env_u32("NERF_WG_DBG", 0);
+    static const bool want_prof = nerf_env_set("NERF_WG_PROF");
+    a.wait_hint = wait_hint; a.dbg = dbg;
     int n_units = 0;
     for (int l = 0; l < WG_NU; ++l) n_units += a.dz[l] != nullptr;
     int pairs = nerf_num_sms() / 2;
@@ -305,7 +303,7 @@ int launch_wgrad_tc(WgradArgs& a, cudaStream_t st) {
     attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     a.prof = nullptr;
-    if (getenv("NERF_WG_PROF")) { cudaMalloc(&a.prof, 2 * pairs * 8 * sizeof(long long)); cudaMemset(a.prof, 0, 2 * pairs * 8 * sizeof(long long)); }
+    if (want_prof) { cudaMalloc(&a.prof, 2 * pairs * 8 * sizeof(long long)); cudaMemset(a.prof, 0, 2 * pairs * 8 * sizeof(long long)); }
     NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_wgrad_tc_kernel, a));
     NERF_CUDA_CHECK_LAUNCH();
     if (a.prof) {

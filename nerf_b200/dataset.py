@@ -18,13 +18,21 @@ from . import ops
 
 class PixelRayDataset(data.Dataset):
 
-    def __init__(self, images, *args, states_x=None, states_d=None, x_states=None, d_states=None):
-        if len(args) >= 3 and isinstance(args[2], numbers.Number):       # HEAD: (images, segmentation, poses, focal, ...)
-            segmentation, poses, focal_length = args[0], args[1], args[2]
-            rest = args[3:]
-        else:                                                           # G1/G2: (images, poses, focal, ...)
-            segmentation, poses, focal_length = None, args[0], args[1]
-            rest = args[2:]
+    def __init__(self, images, *args, states_x=None, states_d=None, x_states=None, d_states=None,
+                 segmentation=None, poses=None, focal_length=None):
+        # leading tensors before the focal length: (poses) = G1/G2, (segmentation, poses) = HEAD; each of
+        # segmentation / poses / focal_length may also come as a keyword (nerf/dataset.py:194-195)
+        rest, lead = list(args), []
+        while rest and len(lead) < 2 and not isinstance(rest[0], numbers.Number):
+            lead.append(rest.pop(0))
+        if rest and isinstance(rest[0], numbers.Number) and focal_length is None:
+            focal_length = rest.pop(0)
+        if poses is None and lead:
+            poses = lead.pop()
+        if segmentation is None and lead:
+            segmentation = lead.pop()
+        if poses is None or focal_length is None or lead:
+            raise TypeError("PixelRayDataset(images, poses, focal_length, ...) or PixelRayDataset(images, segmentation, poses, focal_length, ...)")
         if len(rest) > 0 and states_x is None:
             states_x = rest[0]
         if len(rest) > 1 and states_d is None:
@@ -103,6 +111,9 @@ class PixelRayDataset(data.Dataset):
         n = len(self)
         dev = self.images.device
         order = torch.randperm(n, generator=generator) if shuffle else torch.arange(n)
+        # every rank must run the same number of steps with the same batch sizes (each step is one all-reduce):
+        # cut the permutation to a multiple of world_size before striding, like DistributedSampler(drop_last=True)
+        order = order[:(n // world_size) * world_size]
         order = order[rank::world_size].to(dev)
         for i in range(0, order.numel(), batch_size):
             sel = order[i:i + batch_size]

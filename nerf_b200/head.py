@@ -135,13 +135,19 @@ class HeadNeRF(nn.Module):
         return self._ladders[key]
 
     def sample_along_rays(self, rays_o, rays_d, num_samples, states_x=None, states_d=None,
-                          randomly_sample=True, u=None, seed=0):
-        """nerf/model.py:369-435: geometric ladder x world-box diagonal, stratified jitter."""
+                          randomly_sample=True, u=None, seed=None, ray_id_base=0):
+        """nerf/model.py:369-435: geometric ladder x world-box diagonal, stratified jitter.  The jitter is a fresh
+        `torch.rand` draw per call like the reference's (:432, so `torch.manual_seed` governs it), unless `u` is
+        handed in or `seed` selects the counter-based stream keyed by (seed, ray_id_base + ray, sample)."""
         batch = rays_o.shape[:-1]
         b = int(math.prod(batch)) if len(batch) else 1
+        if not randomly_sample:
+            u = None
+        elif u is None and seed is None:
+            u = torch.rand(b, num_samples, dtype=torch.float32, device=rays_o.device)
         t = ops.sample_geometric(self._box_diag(), num_samples, b, rays_o.device, u=u,
-                                 jitter=bool(randomly_sample) and u is None, seed=seed,
-                                 t_base=self._ladder(num_samples, rays_o.device))
+                                 jitter=bool(randomly_sample) and u is None, seed=0 if seed is None else seed,
+                                 ray_id_base=ray_id_base, t_base=self._ladder(num_samples, rays_o.device))
         return t.view(*batch, num_samples)
 
     def integrated_pe(self, rays_o, rays_d, samples):
@@ -182,7 +188,9 @@ class HeadNeRF(nn.Module):
 
     @torch.no_grad()
     def forward(self, rays_o, rays_d, samples, states_x=None, states_d=None):
-        """nerf/model.py:553-594 -> (mean, density [..,1], color [..,3], segmentation [..,n_seg])."""
+        """nerf/model.py:553-594 -> (mean, density [..,1], color [..,3], segmentation [..,n_seg]).
+        Inference only: the differentiable entry point of this generation is `render_rays` (one autograd node
+        over encoder + trunk + composite); the raw network outputs returned here carry no graph."""
         if self.precision == "bf16":
             batch = samples.shape[:-1]; s = samples.shape[-1]
             mean, out = self._fwd_tc(ops._f32c(rays_o.reshape(-1, 3)), ops._f32c(rays_d.reshape(-1, 3)), ops._f32c(samples.reshape(-1, s)))
@@ -194,28 +202,31 @@ class HeadNeRF(nn.Module):
         return mean, density, color, seg
 
     def render_rays(self, rays_o, rays_d, num_samples, states_x=None, states_d=None,
-                    randomly_sample=False, density_noise_std=0.0, u=None, noise=None, seed=0):
+                    randomly_sample=False, density_noise_std=0.0, u=None, noise=None, seed=None, ray_id_base=0):
         """nerf/model.py:596-668 -> (image [B,1,3], segmentation [B,1,n_seg]).  With autograd enabled and
         parameters that require grad (fp32 mode) the result carries the graph of `_HeadRenderFn`; the
-        tcgen05 (bf16) form is inference only."""
+        tcgen05 (bf16) form is inference only.  RNG like the reference: `torch.rand` for the jitter (:432), then
+        `torch.randn` for the density noise, drawn even when std == 0 (:652-654)."""
         params = list(self.prediction_heads.parameters())
         if torch.is_grad_enabled() and self.precision == "fp32" and any(p.requires_grad for p in params):
             with torch.no_grad():
                 o = ops._f32c(rays_o.reshape(-1, 3)); d = ops._f32c(rays_d.reshape(-1, 3))
                 b, s1 = o.shape[0], num_samples - 1
-                t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)
-                if noise is None and density_noise_std != 0.0:   # the reference draws torch.randn here (:652)
+                t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed,
+                                           ray_id_base=ray_id_base)
+                if noise is None:                                # the reference draws torch.randn here, whatever std (:652)
                     noise = torch.randn(b, s1, device=o.device)
-                nz = ops._f32c(noise.reshape(b, s1)) if noise is not None else None
+                nz = ops._f32c(noise.reshape(b, s1)) if density_noise_std != 0.0 else None
             img, seg = _HeadRenderFn.apply(self, o, d, t, nz, float(density_noise_std), *params)
             return img.unsqueeze(-2), seg.unsqueeze(-2)
         with torch.no_grad():
-            return self._render_rays_eval(rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed)
+            return self._render_rays_eval(rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed,
+                                          ray_id_base)
 
-    def _render_rays_eval(self, rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed):
+    def _render_rays_eval(self, rays_o, rays_d, num_samples, randomly_sample, density_noise_std, u, noise, seed, ray_id_base=0):
         o = ops._f32c(rays_o.reshape(-1, 3)); d = ops._f32c(rays_d.reshape(-1, 3))
         b = o.shape[0]
-        t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed)
+        t = self.sample_along_rays(o, d, num_samples, randomly_sample=randomly_sample, u=u, seed=seed, ray_id_base=ray_id_base)
         s1 = num_samples - 1
         if self.precision == "bf16":
             mean, out = self._fwd_tc(o, d, t, log_softmax_seg=True)      # :662 fused into the output head's epilogue
@@ -223,10 +234,10 @@ class HeadNeRF(nn.Module):
         else:
             mean, _, feat = self.integrated_pe(o, d, t)
             out = self._trunk(feat.view(b * s1, -1))
-        if noise is None and density_noise_std != 0.0:           # the reference draws torch.randn here (:652)
+        if noise is None:                                        # the reference draws torch.randn here, whatever std (:652)
             noise = torch.randn(b, s1, device=o.device)
         img = torch.empty(b, 3, device=o.device); seg = torch.empty(b, self.segmentation_outputs, device=o.device)
-        nz = ops._f32c(noise.reshape(b, s1)) if noise is not None else None
+        nz = ops._f32c(noise.reshape(b, s1)) if density_noise_std != 0.0 else None
         check(lib().nerf_head_composite(ptr(out), out.shape[1], self.segmentation_outputs, ptr(mean.view(b, s1, 3).contiguous()),
                                         ptr(nz), float(density_noise_std), b, s1, ptr(img), ptr(seg), None,
                                         int(self.precision == "bf16"), stream()),
@@ -236,21 +247,25 @@ class HeadNeRF(nn.Module):
     @torch.no_grad()
     def render_image(self, camera_o, camera_r, image_h, image_w, focal_length, num_samples,
                      states_x=None, states_d=None, max_chunk_size=1024, randomly_sample=False,
-                     density_noise_std=0.0, ray_begin=0, ray_end=None):
+                     density_noise_std=0.0, ray_begin=0, ray_end=None, seed=None):
         """nerf/model.py:670-770 -> (image [Bc,H,W,3], segmentation [Bc,H,W,n_seg]).  Rays are generated
         on the device from their flattened id; chunks are independent (max_chunk_size only bounds
-        memory here, so it is raised to max_chunk_rays).  ray_begin/ray_end render a shard."""
+        memory here, so it is raised to max_chunk_rays).  ray_begin/ray_end render a shard.  A jittered frame
+        uses ONE seed (drawn from torch's generator when not given) with the counter-based stream keyed by the
+        frame's ray ids, so chunk sizes and shard boundaries do not change the draw."""
         camera_o, camera_r = ops._f32c(camera_o), ops._f32c(camera_r)
         bc = camera_o.shape[0]
         total = bc * image_h * image_w
         ray_end = total if ray_end is None else ray_end
         chunk = max(int(max_chunk_size), self.max_chunk_rays)
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if randomly_sample else 0
         imgs, segs = [], []
         for r0 in range(ray_begin, ray_end, chunk):
             r1 = min(r0 + chunk, ray_end)
             o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, r0, r1)
             a, s = self.render_rays(o, d, num_samples, randomly_sample=randomly_sample,
-                                    density_noise_std=density_noise_std, seed=r0)
+                                    density_noise_std=density_noise_std, seed=seed, ray_id_base=r0)
             imgs.append(a[:, -1]); segs.append(s[:, -1])
         img, seg = torch.cat(imgs), torch.cat(segs)
         if ray_begin == 0 and ray_end == total:

@@ -11,6 +11,7 @@ Generations:
            (nerf/model.py:242-367, 437-469).
 """
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -40,11 +41,15 @@ def g1_param_layout_py(dx, dd):
 class NeRF(nn.Module):
 
     def __init__(self, normalize_position=1.0, density_inputs=None, color_inputs=None,
-                 hidden_size=HIDDEN, precision="fp32", normalize_direction=True,
+                 hidden_size=HIDDEN, precision=None, normalize_direction=True,
                  stages_axis=None, max_chunk_rays=32768):
         super().__init__()
         if hidden_size != HIDDEN:
             raise ValueError("the sm_100a kernels are built for hidden_size=256 (examples/nerf.pth)")
+        if precision is None:
+            # the reference's call sites (`NeRF(normalize_position=6.0)`, train_conditional_nerf.py:103-104) carry no
+            # precision argument: NERF_B200_PRECISION picks the contraction for them (default: the fp32 parity mode)
+            precision = os.environ.get("NERF_B200_PRECISION", "fp32")
         if precision not in ops.PRECISIONS:
             raise ValueError(f"precision must be one of {list(ops.PRECISIONS)}")
         # G2 call sites pass density_inputs explicitly and expect a [B,stages,3] result
@@ -199,6 +204,17 @@ class NeRF(nn.Module):
         """All outputs of one pass (dict); `u`/`noise` are host-supplied draws (parity mode)."""
         rays_o = rays_o.float().contiguous(); rays_d = rays_d.float().contiguous()
         b = rays_o.shape[0]
+        if self._train_tc_ok(num_samples, states_x, states_d) and b > 0:
+            # tcgen05 training path under autograd: `loss.backward()` of the reference loop runs the tensor-core
+            # data-/weight-gradient kernels (ops._G1TrainTC); the composite is its own differentiable node
+            t, sigma, rgb = ops.g1_train_tc(self.flat_parameters(), list(self.parameters()), rays_o, rays_d, num_samples,
+                                            near, far, self.normalize_position, self.normalize_direction,
+                                            t_base=self._ladder(near, far, num_samples, rays_o.device), t_in=t, u=u,
+                                            states_x=states_x)
+            if noise is not None:
+                sigma = sigma + noise.view(b, num_samples)
+            pixels, depth, acc, weights = ops.composite(sigma, rgb, rays_o=rays_o, rays_d=rays_d, t=t)
+            return dict(pixels=pixels, depth=depth, acc=acc, weights=weights, t=t, density=sigma.unsqueeze(-1), color=rgb)
         if self._fused_ok(num_samples, states_x, states_d) and noise is None:
             # tcgen05 path: one persistent kernel for sample+encode+MLP, then the compositing kernel
             packed = ops.g1_pack_weights(self.flat_parameters(), self.density_inputs, 3)
@@ -224,12 +240,22 @@ class NeRF(nn.Module):
                                            sl(states_x, i), sl(states_d, i), sl(u, i), sl(noise, i), sl(t, i)))
         return {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
 
-    def _fused_ok(self, num_samples, states_x, states_d):
-        """bf16 tcgen05 render path (training on tensor cores goes through train.Trainer): position-side
-        conditional inputs are supported, direction-side ones take the fp32 kernels."""
+    def _tc_shape_ok(self, num_samples, states_x, states_d):
         sx = 0 if states_x is None else states_x.shape[-1]
-        return (self.precision == "bf16" and not torch.is_grad_enabled() and num_samples >= 32
+        return (self.precision == "bf16" and num_samples >= 32
                 and self.density_inputs == 3 + sx and self.color_inputs == 3 and states_d is None)
+
+    def _fused_ok(self, num_samples, states_x, states_d):
+        """bf16 tcgen05 render path (no graph recorded): position-side conditional inputs are supported,
+        direction-side ones take the fp32 kernels."""
+        return self._tc_shape_ok(num_samples, states_x, states_d) and not self._wants_grad()
+
+    def _wants_grad(self):
+        return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+
+    def _train_tc_ok(self, num_samples, states_x, states_d):
+        """bf16 tcgen05 path with a graph: the same shapes, when a gradient can be asked for."""
+        return self._tc_shape_ok(num_samples, states_x, states_d) and self._wants_grad()
 
     def render_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
                     randomly_sample=False, density_noise_std=0.0):

@@ -1,6 +1,10 @@
 """Host-side operators over the C ABI (include/nerf_b200.h).  PyTorch supplies device
 memory, streams and autograd plumbing only; all arithmetic is in libnerf_b200.so."""
+import atexit
+import collections
 import ctypes
+import json
+import os
 
 import torch
 
@@ -15,6 +19,22 @@ HIDDEN = 256
 # nerf_composite_fwd takes the warp-per-ray kernels below this many rays and the thread-per-ray tile kernels from it on
 # (csrc/composite.cu); the two sum in different orders
 COMPOSITE_WARP_BELOW = 1 << 14
+
+# Calls per kernel family made by this process (which path ran is a testable fact): NERF_B200_STATS=<file> dumps
+# them as JSON at exit, so a test that runs an unmodified reference entry point in a subprocess can assert that
+# its `render_rays / loss.backward()` loop reached the tcgen05 kernels.
+COUNTERS = collections.Counter()
+
+
+def _dump_counters():
+    path = os.environ.get("NERF_B200_STATS")
+    if path:
+        with open(path, "w") as f:
+            json.dump(dict(COUNTERS), f)
+
+
+atexit.register(_dump_counters)
+
 
 def _f32c(t):
     if t is None:
@@ -181,6 +201,7 @@ class _G1MLP(torch.autograd.Function):
         check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), p, samples_per_ray, dx, dd, precision,
                                     int(need_grad), ptr(sigma), ptr(rgb), ptr(ws), nbytes, stream()),
               "nerf_g1_mlp_fwd")
+        COUNTERS["g1_mlp_fwd_fp32"] += 1
         ctx.save_for_backward(ex, ed, flat, ws)
         ctx.cfg = (samples_per_ray, dx, dd, precision, [tuple(q.shape) for q in params], nbytes)
         return sigma, rgb
@@ -237,6 +258,64 @@ def g1_pack_weights(flat, dx=3, dd=3):
     return packed
 
 
+class _G1TrainTC(torch.autograd.Function):
+    """t [B,S], sigma [B,S], rgb [B,S,3] = sample -> encode -> MLP on tcgen05 with every unit's output kept
+    as bf16 slab images (`nerf_g1_train_fwd_tc`); backward = the tcgen05 data-gradient kernel, the
+    weight-gradient GEMM and the unfold (`nerf_g1_train_bwd_tc`).  This is the node behind
+    `pixels = nerf.render_rays(...); loss.backward()` of the reference loop
+    (train_conditional_nerf.py:120-135, example.ipynb cell 8) when precision = "bf16": the gradients
+    come back as 44 views of one flat buffer in state_dict order."""
+
+    @staticmethod
+    def forward(ctx, flat, rays_o, rays_d, t_base, t_in, u, states_x, cfg, *params):
+        dx, s, near, far, norm, norm_dir, jitter, seed, ray_base = cfg
+        L = lib()
+        b = rays_o.shape[0]
+        dev = rays_o.device
+        n = L.nerf_g1_train_workspace_bytes(b, s, dx)
+        if n <= 0:
+            raise ValueError("nerf_g1_train_workspace_bytes: bad argument")
+        ws = torch.empty(n, dtype=torch.uint8, device=dev)
+        packed = torch.empty(L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev)
+        packed_bwd = torch.empty(L.nerf_g1_packed_bwd_bytes(dx, 3), dtype=torch.uint8, device=dev)
+        st = stream()
+        check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(packed), st), "nerf_g1_pack_weights")
+        check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(packed_bwd), st), "nerf_g1_pack_weights_bwd")
+        t = torch.empty(b, s, device=dev); sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
+        check(L.nerf_g1_train_fwd_tc(ptr(packed), dx, 3, ptr(rays_o), ptr(rays_d), b, s, float(near), float(far),
+                                     ptr(t_base), ptr(t_in), ptr(u), int(jitter), seed, ray_base, float(norm), int(norm_dir),
+                                     ptr(states_x), ptr(t), ptr(sigma), ptr(rgb), ptr(ws), n, st), "nerf_g1_train_fwd_tc")
+        COUNTERS["g1_train_fwd_tc"] += 1
+        ctx.save_for_backward(flat, ws, packed, packed_bwd)
+        ctx.cfg = (dx, b, s, n, [tuple(q.shape) for q in params])
+        ctx.mark_non_differentiable(t)
+        return t, sigma, rgb
+
+    @staticmethod
+    def backward(ctx, _g_t, d_sigma, d_rgb):
+        flat, ws, packed, packed_bwd = ctx.saved_tensors
+        dx, b, s, n, shapes = ctx.cfg
+        dev = flat.device
+        d_sigma = _f32c(d_sigma) if d_sigma is not None else torch.zeros(b, s, device=dev)
+        d_rgb = _f32c(d_rgb) if d_rgb is not None else torch.zeros(b, s, 3, device=dev)
+        grads = torch.empty_like(flat)                          # overwritten by the unfold kernel
+        check(lib().nerf_g1_train_bwd_tc(ptr(packed), ptr(packed_bwd), ptr(flat), dx, 3, ptr(d_sigma), ptr(d_rgb), b, s,
+                                         ptr(grads), ptr(ws), n, 0, stream()), "nerf_g1_train_bwd_tc")
+        COUNTERS["g1_train_bwd_tc"] += 1
+        off, _ = g1_param_layout(dx, 3)
+        views = tuple(grads[o:o + _numel(sh)].view(sh) for o, sh in zip(off, shapes))
+        return (None,) * 8 + views
+
+
+def g1_train_tc(flat, params, rays_o, rays_d, num_samples, near, far, normalize_position, normalize_direction=True,
+                t_base=None, t_in=None, u=None, states_x=None, jitter=False, seed=0, ray_id_base=0):
+    """Differentiable (w.r.t. the 44 parameters) tcgen05 forward: -> t, sigma [B,S], rgb [B,S,3]."""
+    states_x = _f32c(states_x)
+    dx = 3 if states_x is None else 3 + states_x.shape[-1]
+    cfg = (dx, int(num_samples), near, far, normalize_position, normalize_direction, jitter, seed, ray_id_base)
+    return _G1TrainTC.apply(flat, _f32c(rays_o), _f32c(rays_d), _f32c(t_base), _f32c(t_in), _f32c(u), states_x, cfg, *params)
+
+
 def g1_mlp_tc_debug(packed, rays_o, rays_d, t, normalize_position, normalize_direction=True, dbg_layer=-1):
     rays_o, rays_d, t = _f32c(rays_o), _f32c(rays_d), _f32c(t)
     b, s = t.shape
@@ -282,4 +361,5 @@ def g1_render_fused(packed, num_samples, near, far, normalize_position, normaliz
                                      ptr(states_x), n_states, int(rays_per_state),
                                      g("pixels"), g("depth"), g("acc"), g("weights"), g("t"), g("sigma"), g("rgb"),
                                      ptr(ws), nbytes, stream()), "nerf_g1_render_fused")
+    COUNTERS["g1_render_fused"] += 1
     return out

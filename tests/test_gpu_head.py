@@ -96,7 +96,7 @@ def test_head_vs_oracle_large(head_model, head_ref):
     with torch.no_grad():
         wi, ws = om.render_rays(o, d, 65, u=u, noise=noise)
     with torch.no_grad():
-        gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+        gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, randomly_sample=True, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
     assert not gi.requires_grad
     assert np.abs(gi.cpu().numpy() - wi.numpy()).max() <= 1e-3
     np.testing.assert_allclose(gi.cpu().numpy(), wi.numpy(), rtol=0, atol=2e-5)
@@ -134,8 +134,8 @@ def test_head_tc_render_vs_fp32(head_model, head_model_bf16):
     o = (torch.randn(301, 3, generator=g) * 2).cuda(); d = torch.randn(301, 3, generator=g).cuda()
     u = torch.rand(301, 48, generator=g).cuda()
     with torch.no_grad():
-        wi, ws = head_model.render_rays(o, d, 48, u=u)
-    gi, gs = head_model_bf16.render_rays(o, d, 48, u=u)
+        wi, ws = head_model.render_rays(o, d, 48, randomly_sample=True, u=u)
+    gi, gs = head_model_bf16.render_rays(o, d, 48, randomly_sample=True, u=u)
     assert gi.shape == wi.shape and gs.shape == ws.shape
     err = (gi - wi).abs().max().item()
     mse = ((gi - wi) ** 2).mean().item()
@@ -174,7 +174,7 @@ def test_head_backward_vs_reference(head_model, head_ref):
     o, d = _cuda(head_ref["head_ro"]), _cuda(head_ref["head_rd"])
     target, labels = _cuda(gr["target"]), _cuda(gr["labels"])
     cases = (("det", dict(randomly_sample=False, density_noise_std=0.0)),
-             ("noisy", dict(u=_cuda(gr["noisy_u"]), noise=_cuda(gr["noisy_noise"]), density_noise_std=1.0)))
+             ("noisy", dict(randomly_sample=True, u=_cuda(gr["noisy_u"]), noise=_cuda(gr["noisy_noise"]), density_noise_std=1.0)))
     for tag, kw in cases:
         head_model.zero_grad()
         img, seg = head_model.render_rays(o, d, 16, **kw)
@@ -214,7 +214,7 @@ def test_head_backward_vs_oracle_large(head_model, head_ref, branch):
     wi, ws = om.render_rays(o, d, 65, u=u, noise=noise)
     loss_of(wi, ws, target, labels).backward()
     head_model.zero_grad()
-    gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
+    gi, gs = head_model.render_rays(o.cuda(), d.cuda(), 65, randomly_sample=True, u=u.cuda(), noise=noise.cuda(), density_noise_std=1.0)
     loss_of(gi, gs, target.cuda(), labels.cuda()).backward()
     for (k, p), (_, q) in zip(head_model.named_parameters(), om.named_parameters()):
         err = _rel_l2(p.grad.cpu().numpy(), q.grad.numpy())
@@ -259,3 +259,36 @@ def test_head_backward_abi_edges():
     assert L.nerf_head_mlp_bwd(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), 56, pp, x.data_ptr(), 1 << 20, None) == -1
     assert L.nerf_head_mlp_bwd(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), 64, pp, x.data_ptr(), 16, None) == -3
     assert L.nerf_head_mlp_fwd_train(pp, x.data_ptr(), 8, 96, 54, x.data_ptr(), x.data_ptr(), 16, None) == -3
+
+
+def test_head_rng_follows_torch_like_the_reference(head_model):
+    """nerf/model.py:432,652: every jittered call draws a fresh torch.rand (so two calls differ and torch.manual_seed
+    reproduces them), torch.randn is consumed even with density_noise_std == 0, `u` is ignored unless randomly_sample,
+    and a jittered render_image does not depend on chunking or on shard boundaries."""
+    g = torch.Generator().manual_seed(41)
+    o = (torch.randn(50, 3, generator=g) * 2).cuda(); d = torch.randn(50, 3, generator=g).cuda()
+    with torch.no_grad():
+        torch.manual_seed(7)
+        a, _ = head_model.render_rays(o, d, 32, randomly_sample=True)
+        b, _ = head_model.render_rays(o, d, 32, randomly_sample=True)
+        torch.manual_seed(7)
+        a2, _ = head_model.render_rays(o, d, 32, randomly_sample=True)
+        assert not torch.equal(a, b) and torch.equal(a, a2)
+        # RNG consumption of one deterministic call = rand is NOT drawn, randn IS (reference :652-654)
+        torch.manual_seed(9); head_model.render_rays(o, d, 32); after = torch.rand(1, device="cuda")
+        torch.manual_seed(9); torch.randn(50, 31, device="cuda"); want = torch.rand(1, device="cuda")
+        assert torch.equal(after, want)
+        u = torch.rand(50, 32, device="cuda")
+        t0 = head_model.sample_along_rays(o, d, 32, randomly_sample=False)
+        assert torch.equal(head_model.sample_along_rays(o, d, 32, randomly_sample=False, u=u), t0)
+        assert not torch.equal(head_model.sample_along_rays(o, d, 32, randomly_sample=True, u=u), t0)
+        cam_o = torch.tensor([[0.0, 0.0, 4.0]], device="cuda"); cam_r = torch.eye(3, device="cuda")[None]
+        kw = dict(randomly_sample=True, seed=123)
+        full, _ = head_model.render_image(cam_o, cam_r, 20, 30, 40.0, 24, **kw)
+        head_model.max_chunk_rays, keep = 100, head_model.max_chunk_rays
+        try:
+            small, _ = head_model.render_image(cam_o, cam_r, 20, 30, 40.0, 24, max_chunk_size=64, **kw)
+            part, _ = head_model.render_image(cam_o, cam_r, 20, 30, 40.0, 24, ray_begin=150, ray_end=420, **kw)
+        finally:
+            head_model.max_chunk_rays = keep
+        assert torch.equal(small, full) and torch.equal(part, full.reshape(-1, 3)[150:420])

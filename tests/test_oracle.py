@@ -140,3 +140,19 @@ def test_head_gradients_vs_reference(head_ref):
         for k, p in m.named_parameters():
             want = gr[f"{tag}_grad/{k}"]
             np.testing.assert_allclose(p.grad.numpy(), want, rtol=1e-4, atol=1e-6 * max(1.0, np.abs(want).max()), err_msg=f"{tag} {k}")
+
+
+def test_hierarchical_sampler_known_answers():
+    """oracle.g1.sample_pdf against the hand-derived vectors of tests/golden/make_pdf_kat.py (NeRF section 5.2; the
+    algorithm the reference promises at nerf/model.py:191-193, 503-505 and never implements)."""
+    from conftest import load_golden
+    from oracle import g1
+    kat = load_golden("pdf_kat.npz")
+    for name in kat["names"]:
+        t = torch.from_numpy(kat[f"{name}_t"])[None]; w = torch.from_numpy(kat[f"{name}_w"])[None]
+        u = kat[f"{name}_u"]
+        want = kat[f"{name}_fine"]
+        fine = g1.sample_pdf(t, w, len(want), u=None if u.size == 0 else torch.from_numpy(u)[None])[0].numpy()
+        np.testing.assert_allclose(fine, want, rtol=0, atol=1e-5 if name == "C" else 5e-6, err_msg=str(name))
+        merged = np.sort(np.concatenate([t[0].numpy(), fine]))
+        np.testing.assert_allclose(merged, kat[f"{name}_merged"], rtol=0, atol=1e-5)
