@@ -304,10 +304,10 @@ def run_ours(args):
             t_all = torch.cat([torch.rand(512, 3, generator=torch.Generator().manual_seed(900 + r)) for r in range(world)]).to(dev)
             u_all = torch.cat([torch.rand(512, s, generator=torch.Generator().manual_seed(950 + r)) for r in range(world)]).to(dev)
             sl = slice(512 * rank, 512 * (rank + 1))
-            tr_dp = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision)
+            tr_dp = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision, fused_exchange=False)
             tr_dp.step(o_all[sl].contiguous(), d_all[sl].contiguous(), t_all[sl].contiguous(), u=u_all[sl].contiguous(), apply_update=False)
             g_dp = tr_dp.flat_grad.clone() / world                          # what Adam sees (grad_scale = 1/world)
-            tr_one = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision, process_group=None)
+            tr_one = Trainer(model, num_samples=s, density_noise_std=0.0, precision=args.precision, fused_exchange=False)
             tr_one.world = 1                                               # same kernels, no exchange
             tr_one.step(o_all, d_all, t_all, u=u_all, apply_update=False)
             rel = float(((g_dp - tr_one.flat_grad).norm() / tr_one.flat_grad.norm()).item())
@@ -350,7 +350,8 @@ def run_ours(args):
     def _other_precision():
         other = "fp32" if args.precision == "bf16" else "bf16"
         m3 = NeRF(normalize_position=6.0, precision=other).to(dev); m3.load_state_dict(sd)
-        tr3 = Trainer(m3, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=1234)
+        tr3 = Trainer(m3, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=1234,
+                      fused_exchange=False)
         tr3.world = 1
 
         def it(i):
@@ -437,16 +438,15 @@ def run_ours(args):
     else:
         t = ops.sample_linear(NEAR, FAR, s, b, dev, jitter=True, seed=1)
         ex, ed, _ = ops.encode_g1(o, d, t, 6.0)
-        prec = ops.PRECISIONS[args.precision]
-        nbytes = L.nerf_g1_mlp_workspace_bytes(b * s, 3, 3, prec, 1)
+        nbytes = L.nerf_g1_mlp_workspace_bytes(b * s, 3, 3, 1)
         ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
         sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
         dsig = torch.randn(b, s, device=dev); drgb = torch.randn(b, s, 3, device=dev)
         grads = torch.zeros_like(flat)
 
         def mlp_only(i):
-            _lib.check(L.nerf_g1_mlp_fwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, 1, P(sigma), P(rgb), P(ws), nbytes, _lib.stream()), "fwd")
-            _lib.check(L.nerf_g1_mlp_bwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, prec, P(dsig), P(drgb), P(grads), P(ws), nbytes, _lib.stream()), "bwd")
+            _lib.check(L.nerf_g1_mlp_fwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, 1, P(sigma), P(rgb), P(ws), nbytes, _lib.stream()), "fwd")
+            _lib.check(L.nerf_g1_mlp_bwd(P(flat), P(ex), P(ed), b * s, s, 3, 3, P(dsig), P(drgb), P(grads), P(ws), nbytes, _lib.stream()), "bwd")
         for i in range(3):
             mlp_only(i)
         ms_mlp = float(np.mean(timed_steps(mlp_only, max(K // 2, 3), flush)))
@@ -669,6 +669,8 @@ def run_ours(args):
             "render_d3": d3,
             "train_c4": c4["train"], "render_c4": c4["render"],
             "dp_check": dp_check, "allreduce": allreduce_us,
+            "exchange": (trainer.exchange.describe() if trainer.exchange is not None else
+                         ("ncclAllReduce(flat gradient) + adam_kernel" if world > 1 else "none (one GPU): adam_kernel")),
             "kernels": kernels,
             "loss": loss_val,
         }

@@ -35,9 +35,10 @@ extern "C" {
 #define NERF_PE_D_OCTAVES 6
 #define NERF_G1_LAYERS 10
 
-/* precision of the MLP contraction */
-#define NERF_PREC_FP32 0 /* fp32 FFMA tiles: the <=1e-3 parity mode            */
-#define NERF_PREC_BF16 1 /* tcgen05 kind::f16 (bf16 in, fp32 accumulate in TMEM) */
+/* The MLP contraction comes in two forms, each with its own entry points:
+ *   fp32 FFMA tiles on explicit encodings (the <= 1e-3 parity mode): nerf_g1_mlp_fwd / nerf_g1_mlp_bwd;
+ *   bf16 tcgen05 kind::f16 (fp32 accumulate in TMEM) fused with the encoder: nerf_g1_render_fused,
+ *   nerf_g1_train_fwd_tc / nerf_g1_train_bwd_tc. */
 
 int nerf_abi_version(void);
 /* Human readable name of the last CUDA error seen by this library (thread local). */
@@ -138,21 +139,21 @@ int nerf_composite_bwd(const float* sigma, const float* rgb, const float* points
 int64_t nerf_g1_param_layout(int Dx, int Dd, int64_t* offsets_host);
 
 /* Workspace (bytes) needed by nerf_g1_mlp_fwd for P points. */
-int64_t nerf_g1_mlp_workspace_bytes(int64_t P, int Dx, int Dd, int precision, int save_for_backward);
+int64_t nerf_g1_mlp_workspace_bytes(int64_t P, int Dx, int Dd, int save_for_backward);
 
 /* The coordinate MLP of SURVEY A.3 (block_0 -> cat -> block_1 -> density;
  * cat dir -> block_2 -> color): ex [P,20 Dx], ed [P/S,12 Dd] (one row per ray)
  * -> sigma [P], rgb [P,3].  params = flat vector above.  With
  * save_for_backward != 0 the workspace keeps what nerf_g1_mlp_bwd needs. */
 int nerf_g1_mlp_fwd(const float* params, const float* ex, const float* ed, int64_t P, int S,
-                    int Dx, int Dd, int precision, int save_for_backward,
+                    int Dx, int Dd, int save_for_backward,
                     float* sigma, float* rgb, void* workspace, int64_t workspace_bytes,
                     void* stream);
 
 /* Backward: d_sigma [P], d_rgb [P,3] -> ACCUMULATES into grads (flat, same layout
  * as params).  Uses the workspace written by the matching forward call. */
 int nerf_g1_mlp_bwd(const float* params, const float* ex, const float* ed, int64_t P, int S,
-                    int Dx, int Dd, int precision, const float* d_sigma, const float* d_rgb,
+                    int Dx, int Dd, const float* d_sigma, const float* d_rgb,
                     float* grads, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* ----------------------------------------------------------------- fused --- */
@@ -314,6 +315,20 @@ int nerf_head_mlp_bwd(const float* const* params_host, const float* feat, int64_
 int nerf_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq,
                    int64_t n, int64_t step, float lr, float beta1, float beta2, float eps,
                    float grad_scale, void* stream);
+
+/* The data-parallel exchange step (one all-reduce of the flat gradient per step, then the same Adam on every
+ * rank -- train_conditional_nerf.py:130-135 run on several GPUs) as ONE kernel over NVLink / NVSwitch peer memory:
+ * cross-GPU barrier -> all-reduce -> Adam.  The gradient sits in symmetric memory (the same allocation on every rank, peer
+ * mapped).  grads_mc: this rank's MULTICAST mapping of that allocation (NVLS: the sum is read with multimem.ld_reduce) or
+ * NULL (one-shot all-reduce with P2P loads); grads_peers / flags_peers: DEVICE arrays [world] of every rank's mapping of
+ * the gradient ALLOCATION and of the allocation holding a zero-initialised flag block of `world` uint64; grad_offset /
+ * flag_offset: element offsets (float / uint64) of the buffer to reduce and of the flag block inside those allocations
+ * (callers alternate between two gradient buffers by epoch parity); epoch: 1, 2, 3 ... (same on every rank).
+ * n (elements, multiple of 4) and the remaining arguments as nerf_adam_step.  All ranks must make the call. */
+int nerf_dp_allreduce_adam(const float* grads_mc, const float* const* grads_peers, uint64_t* const* flags_peers,
+                           int64_t grad_offset, int64_t flag_offset, int rank, int world, uint64_t epoch,
+                           float* params, float* exp_avg, float* exp_avg_sq, int64_t n, int64_t step,
+                           float lr, float beta1, float beta2, float eps, float grad_scale, void* stream);
 
 /* mean((pixels - target)^2) and its gradient w.r.t. pixels
  * (train_conditional_nerf.py:132): loss_out [1] (overwritten), g_pixels [B,3]. */

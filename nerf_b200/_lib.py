@@ -30,9 +30,9 @@ SIGNATURES = {
     "nerf_composite_fwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p]),
     "nerf_composite_bwd": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "nerf_g1_param_layout": (c_l, [c_i, c_i, ctypes.POINTER(c_l)]),
-    "nerf_g1_mlp_workspace_bytes": (c_l, [c_l, c_i, c_i, c_i, c_i]),
-    "nerf_g1_mlp_fwd": (c_i, [c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_l, c_p]),
-    "nerf_g1_mlp_bwd": (c_i, [c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_l, c_p]),
+    "nerf_g1_mlp_workspace_bytes": (c_l, [c_l, c_i, c_i, c_i]),
+    "nerf_g1_mlp_fwd": (c_i, [c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_i, c_p, c_p, c_p, c_l, c_p]),
+    "nerf_g1_mlp_bwd": (c_i, [c_p, c_p, c_p, c_l, c_i, c_i, c_i, c_p, c_p, c_p, c_p, c_l, c_p]),
     "nerf_g1_packed_bytes": (c_l, [c_i, c_i]),
     "nerf_g1_pack_weights": (c_i, [c_p, c_i, c_i, c_p, c_p]),
     "nerf_g1_render_workspace_bytes": (c_l, [c_l, c_i, c_i, c_l]),
@@ -59,6 +59,7 @@ SIGNATURES = {
     "nerf_head_composite_bwd": (c_i, [c_p, c_i, c_i, c_p, c_p, c_f, c_l, c_i, c_p, c_p, c_p, c_p, c_i, c_p]),
     "nerf_head_mlp_bwd": (c_i, [c_p, c_p, c_l, c_i, c_i, c_p, c_i, c_p, c_p, c_l, c_p]),
     "nerf_adam_step": (c_i, [c_p, c_p, c_p, c_p, c_l, c_l, c_f, c_f, c_f, c_f, c_f, c_p]),
+    "nerf_dp_allreduce_adam": (c_i, [c_p, c_p, c_p, c_l, c_l, c_i, c_i, c_u64, c_p, c_p, c_p, c_l, c_l, c_f, c_f, c_f, c_f, c_f, c_p]),
     "nerf_mse_loss": (c_i, [c_p, c_p, c_l, c_p, c_p, c_p]),
     "nerf_composite_mse_train": (c_i, [c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_u64, c_l, c_p, c_p, c_p, c_p, c_p]),
 }

@@ -44,9 +44,8 @@ static int64_t carve(int64_t P, int save, void* base, Fp32Ws* ws) {
     return o * (int64_t)sizeof(float);
 }
 
-extern "C" int64_t nerf_g1_mlp_workspace_bytes(int64_t P, int Dx, int Dd, int precision, int save_for_backward) {
+extern "C" int64_t nerf_g1_mlp_workspace_bytes(int64_t P, int Dx, int Dd, int save_for_backward) {
     if (P < 0 || Dx < 3 || Dd < 3) return NERF_ERR_BAD_ARG;
-    (void)precision;
     return carve(P, save_for_backward, nullptr, nullptr);
 }
 

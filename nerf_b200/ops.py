@@ -195,10 +195,10 @@ class _G1MLP(torch.autograd.Function):
     def forward(ctx, ex, ed, samples_per_ray, dx, dd, precision, flat, *params):
         p = ex.shape[0]
         need_grad = any(ctx.needs_input_grad)
-        nbytes = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, precision, int(need_grad))
+        nbytes = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, int(need_grad))
         ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=ex.device)
         sigma = torch.empty(p, device=ex.device); rgb = torch.empty(p, 3, device=ex.device)
-        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), p, samples_per_ray, dx, dd, precision,
+        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), p, samples_per_ray, dx, dd,
                                     int(need_grad), ptr(sigma), ptr(rgb), ptr(ws), nbytes, stream()),
               "nerf_g1_mlp_fwd")
         COUNTERS["g1_mlp_fwd_fp32"] += 1
@@ -214,7 +214,7 @@ class _G1MLP(torch.autograd.Function):
         grads = torch.zeros_like(flat)
         d_sigma = _f32c(d_sigma) if d_sigma is not None else torch.zeros(p, device=ex.device)
         d_rgb = _f32c(d_rgb) if d_rgb is not None else torch.zeros(p, 3, device=ex.device)
-        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), p, s, dx, dd, precision, ptr(d_sigma),
+        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), p, s, dx, dd, ptr(d_sigma),
                                     ptr(d_rgb), ptr(grads), ptr(ws), nbytes, stream()), "nerf_g1_mlp_bwd")
         off, _ = g1_param_layout(dx, dd)
         views = tuple(grads[o:o + _numel(sh)].view(sh) for o, sh in zip(off, shapes))

@@ -13,7 +13,7 @@ from ._lib import check, lib, ptr, stream
 class Trainer:
     def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, near=2.0, far=6.0,
                  num_samples=64, density_noise_std=1.0, randomly_sample=True, seed=0,
-                 precision=None, process_group=None):
+                 precision=None, process_group=None, fused_exchange=True):
         self.model = model
         self.lr, self.betas, self.eps = lr, betas, eps
         self.near, self.far, self.num_samples = near, far, num_samples
@@ -23,7 +23,13 @@ class Trainer:
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
         flat = model.flat_parameters()
-        self.flat_grad = torch.zeros_like(flat)
+        # data-parallel exchange: ONE kernel (barrier + all-reduce over NVLink peer memory + Adam, parallel.FusedExchange)
+        # when symmetric memory is available, else ncclAllReduce of the flat gradient followed by the Adam launch
+        self.exchange = None
+        if self.world > 1 and fused_exchange:
+            from .parallel import FusedExchange
+            self.exchange = FusedExchange.create(flat.numel(), flat.device, process_group)
+        self.flat_grad = self.exchange.buffer() if self.exchange else torch.zeros_like(flat)
         self.exp_avg = torch.zeros_like(flat)
         self.exp_avg_sq = torch.zeros_like(flat)
         self.step_count = 0
@@ -34,7 +40,7 @@ class Trainer:
 
     def _workspace(self, p):
         dx, dd = self.model.density_inputs, self.model.color_inputs
-        n = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, self.precision, 1)
+        n = lib().nerf_g1_mlp_workspace_bytes(p, dx, dd, 1)
         if self._ws is None or self._ws.numel() < n:
             self._ws = torch.empty(n, dtype=torch.uint8, device=self.model.flat_parameters().device)
         return self._ws, n
@@ -101,17 +107,30 @@ class Trainer:
                                      ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
               "nerf_g1_train_bwd_tc")
         launches += 3                                               # bwd, wgrad, unfold (memset not counted)
-        if self.world > 1:
-            dist.all_reduce(self.flat_grad, group=self.group)
-        if apply_update:
-            self.step_count += 1
-            ops.adam_step(flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.step_count, self.lr,
-                          self.betas, self.eps, grad_scale=1.0 / self.world)
-            launches += 1
+        launches += self._exchange_and_update(flat, apply_update)
         self.rays_seen += b
         self.kernel_launches = launches
         self.last_pixels = z["pixels"]
         return z["loss"]
+
+    def _exchange_and_update(self, flat, apply_update):
+        """[all-reduce of the flat gradient] + Adam.  Returns the number of OUR kernels launched.  With the fused
+        exchange `self.flat_grad` keeps this rank's LOCAL gradient (the sum exists only inside the kernel) and the next
+        step writes the other symmetric buffer; `apply_update=False` (tests) always takes the NCCL all-reduce."""
+        if self.exchange is not None and apply_update and self.world > 1:
+            self.step_count += 1
+            self.exchange.allreduce_adam(flat, self.exp_avg, self.exp_avg_sq, self.step_count, self.lr, self.betas, self.eps)
+            self.last_grad = self.flat_grad
+            self.flat_grad = self.exchange.buffer()
+            return 1
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, group=self.group)        # one NCCL all-reduce of 2.55 MB
+        if apply_update:
+            self.step_count += 1
+            ops.adam_step(flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.step_count, self.lr,
+                          self.betas, self.eps, grad_scale=1.0 / self.world)
+            return 1
+        return 0
 
     def step(self, rays_o, rays_d, target, states_x=None, states_d=None, u=None, noise=None,
              apply_update=True):
@@ -135,7 +154,7 @@ class Trainer:
         launches += 2
         ws, nbytes = self._workspace(b * s)
         sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
-        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd, self.precision, 1,
+        check(lib().nerf_g1_mlp_fwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd, 1,
                                     ptr(sigma), ptr(rgb), ptr(ws), nbytes, stream()), "nerf_g1_mlp_fwd")
         launches += 12
         if noise is not None:
@@ -153,17 +172,11 @@ class Trainer:
               "nerf_composite_bwd")
         launches += 3
         self.flat_grad.zero_()
-        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd, self.precision,
+        check(lib().nerf_g1_mlp_bwd(ptr(flat), ptr(ex), ptr(ed), b * s, s, dx, dd,
                                     ptr(d_sigma), ptr(d_rgb), ptr(self.flat_grad), ptr(ws), nbytes, stream()),
               "nerf_g1_mlp_bwd")
         launches += 29
-        if self.world > 1:
-            dist.all_reduce(self.flat_grad, group=self.group)        # one NCCL all-reduce of 2.55 MB
-        if apply_update:
-            self.step_count += 1
-            ops.adam_step(flat, self.flat_grad, self.exp_avg, self.exp_avg_sq, self.step_count, self.lr,
-                          self.betas, self.eps, grad_scale=1.0 / self.world)
-            launches += 1
+        launches += self._exchange_and_update(flat, apply_update)
         self.rays_seen += b
         self.kernel_launches = launches
         self.last_pixels = pixels
