@@ -59,8 +59,9 @@ __device__ __forceinline__ void sincospi_fast(float w, float& s, float& c) {
     s = __sinf(3.14159265358979f * r); c = __cosf(3.14159265358979f * r);
 }
 
-// positional encoding of NV values -> one [128 x 64] bf16 slab row (features beyond NV*2*L are zero)
-template <int NV, int L>
+// positional encoding of NV values -> one [128 x 64] bf16 slab row (features beyond NV*2*L are zero).
+// X3 (fused_tc_x3.cu): the row is written twice, hi = bf16(f) here and lo = bf16(f - hi) one slab further.
+template <int NV, int L, bool X3 = false>
 __device__ __forceinline__ void write_pe_row(uint32_t slab_addr, uint32_t row, const float (&v)[NV]) {
     float f[64];
 #pragma unroll
@@ -82,12 +83,22 @@ __device__ __forceinline__ void write_pe_row(uint32_t slab_addr, uint32_t row, c
         uint4 q = make_uint4(tc::pack_bf16x2(f[c16 * 8 + 0], f[c16 * 8 + 1]), tc::pack_bf16x2(f[c16 * 8 + 2], f[c16 * 8 + 3]),
                              tc::pack_bf16x2(f[c16 * 8 + 4], f[c16 * 8 + 5]), tc::pack_bf16x2(f[c16 * 8 + 6], f[c16 * 8 + 7]));
         store_row_chunk(slab_addr, row, c16, q);
+        if (X3) {
+            uint32_t lo[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t h = (&q.x)[i];
+                lo[i] = tc::pack_bf16x2(f[c16 * 8 + 2 * i] - __uint_as_float(h << 16), f[c16 * 8 + 2 * i + 1] - __uint_as_float(h & 0xffff0000u));
+            }
+            store_row_chunk(slab_addr + TC_SLAB_BYTES, row, c16, make_uint4(lo[0], lo[1], lo[2], lo[3]));
+        }
     }
 }
 
 struct RowState { float d[3]; int64_t p; bool valid; };
 
 // ray-gen + stratified sample + position encoding for one point row of a tile
+template <bool X3 = false>
 __device__ __forceinline__ void encode_row(const FusedArgs& a, int tile, uint32_t row, uint32_t pe_addr, RowState& st) {
     int64_t p = (int64_t)tile * 128 + row;
     st.p = p; st.valid = p < a.P;
@@ -130,9 +141,10 @@ __device__ __forceinline__ void encode_row(const FusedArgs& a, int tile, uint32_
 #pragma unroll
         for (int c = 0; c < 3; ++c) v[c] = __fdiv_rn(__fadd_rn(o[c], __fmul_rn(st.d[c], t)), a.norm);
     }
-    write_pe_row<3, NERF_PE_X_OCTAVES>(pe_addr, row, v);
+    write_pe_row<3, NERF_PE_X_OCTAVES, X3>(pe_addr, row, v);
 }
 
+template <bool X3 = false>
 __device__ __forceinline__ void encode_dir_row(const FusedArgs& a, uint32_t row, uint32_t pe_addr, const RowState& st) {
     float v[3] = {st.d[0], st.d[1], st.d[2]};
     if (a.normalize_dir) {
@@ -140,7 +152,7 @@ __device__ __forceinline__ void encode_dir_row(const FusedArgs& a, uint32_t row,
         float inv = n > 0.f ? 1.0f / n : 0.f;
         v[0] *= inv; v[1] *= inv; v[2] *= inv;
     }
-    write_pe_row<3, NERF_PE_D_OCTAVES>(pe_addr, row, v);
+    write_pe_row<3, NERF_PE_D_OCTAVES, X3>(pe_addr, row, v);
 }
 
 // ReLU + LayerNorm (no affine: folded into the consumer) for one unit of one tile slot; the

@@ -79,6 +79,24 @@ static inline int64_t tc_packed_vec_offset(const PackLayout& L) { return L.weigh
 static inline int64_t tc_packed_state_w_offset(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES; }
 static inline int64_t tc_packed_total(const PackLayout& L) { return L.weight_bytes + TC_VEC_BYTES + ((2ll * 256 * L.EXs * 4 + 1023) & ~1023ll); }
 
+// ---- fp32-grade forward ("bf16x3", fused_tc_x3.cu): every operand is split a = a_hi + a_lo (two bf16), and
+// a w ~ a_hi w_hi + a_lo w_hi + a_hi w_lo (fp32 accumulate; the dropped lo*lo term is ~2^-18 relative).  Weight image:
+// per (unit, n-half) [bias block, 4 KB, units without an encoding slab] + 2 nk groups of K = 32:
+// [4 k-cores hi | 4 k-cores lo] = 16 KB, one contiguous bulk copy per ring stage.  Dx = Dd = 3 only.
+#define X3_GROUP_BYTES 16384
+struct X3Layout { int nk[10]; int64_t unit_off[10]; int64_t half_bytes[10]; int64_t weight_bytes; };
+static inline void make_x3_layout(X3Layout& X) {
+    PackLayout L; make_pack_layout(3, 3, L);
+    int64_t o = 0;
+    for (int l = 0; l < 10; ++l) {
+        X.nk[l] = L.nk[l];
+        X.half_bytes[l] = (tc_unit_has_bias_block(l) ? TF_BIAS_KCORES * TF_KCORE_BYTES : 0) + 2ll * L.nk[l] * X3_GROUP_BYTES;
+        X.unit_off[l] = o; o += 2 * X.half_bytes[l];
+    }
+    X.weight_bytes = o;
+}
+static inline int64_t tc_packed_x3_total(const X3Layout& X) { return X.weight_bytes + TC_VEC_BYTES; }
+
 // ---- workspace of the bf16 training step (tc_train.cu): byte offsets, all 1024-aligned ----
 #define TC_GW_LD 336                   // dW' row: 256 hidden + 64 encoding + 16 x (column sum of dz = db')
 struct TrainLayout {

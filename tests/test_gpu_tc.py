@@ -68,7 +68,7 @@ def test_tc_sigma_rgb_and_pixels(g1_oracle, g1_ref, packed, model_bf16):
     assert np.array_equal(r["t"].cpu().numpy(), g1_ref["kat_t"])            # fused sampler: bit-exact bins
     perr = (r["pixels"].cpu() - want["pixels"]).abs()
     print("pixel max/mean err (bf16)", perr.max().item(), perr.mean().item())
-    assert perr.max().item() < 0.05 and perr.mean().item() < 5e-3
+    assert perr.max().item() < 0.01 and perr.mean().item() < 1.5e-3           # measured on B200: 2.7e-3 / 4.3e-4
 
 
 def test_tc_render_image_psnr(model_bf16, g1_ref):
@@ -109,7 +109,8 @@ def test_tc_ragged_shapes_vs_fp32(model_bf16, nerf_pth_state_dict, b, s):
     assert torch.equal(a["t"], w["t"])
     err = (a["pixels"] - w["pixels"]).abs()
     assert torch.isfinite(a["pixels"]).all()
-    assert err.max().item() < 0.06, err.max().item()
+    print(f"ragged b={b} s={s}: bf16 vs fp32 pixel max err {err.max().item():.2e}")
+    assert err.max().item() < 0.03, err.max().item()
 
 
 def test_tc_hierarchical(model_bf16, g1_ref):
@@ -117,7 +118,7 @@ def test_tc_hierarchical(model_bf16, g1_ref):
         r = model_bf16.render_rays_hierarchical(_cuda(g1_ref["kat_o"]), _cuda(g1_ref["kat_d"]), 2.0, 6.0, 64, 128)
     err = np.abs(r["pixels"].cpu().numpy() - g1_ref["kat_hier_pixels"])
     print("hierarchical bf16 pixel err max/mean", err.max(), err.mean())
-    assert err.max() < 0.06 and err.mean() < 6e-3
+    assert err.max() < 0.01 and err.mean() < 1.5e-3                            # measured on B200: 2.1e-3 / 4.0e-4
 
 
 def test_d3_ray_subsets_vs_oracle(model_bf16, nerf_pth_state_dict, g1_oracle):
@@ -144,8 +145,8 @@ def test_d3_ray_subsets_vs_oracle(model_bf16, nerf_pth_state_dict, g1_oracle):
         se16 += ((got16 - want) ** 2).sum().item(); n += want.numel()
     psnr16 = -10 * np.log10(se16 / n)
     print(f"D3 subsets vs oracle: fp32 max|diff| {worst32:.2e}; bf16 max|diff| {worst16:.2e}, {psnr16:.1f} dB")
-    assert worst32 <= 2e-3            # fp32 mode (the fine samples sit on an ill-conditioned inverse cdf: 2e-3, as the 64-ray fixture)
-    assert worst16 <= 0.05 and psnr16 >= 40.0
+    assert worst32 <= 1e-4            # fp32 mode: the north star's bar is 1e-3; measured on B200 4.8e-7
+    assert worst16 <= 0.03 and psnr16 >= 50.0     # bf16: measured 2.0e-2 (one edge pixel whose fine samples move) / 58.1 dB
 
 
 def test_tc_render_d3_full_size_properties(model_bf16):
