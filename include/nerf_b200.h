@@ -198,6 +198,24 @@ int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                          float* out_t, float* out_sigma, float* out_rgb,
                          void* workspace, int64_t workspace_bytes, void* stream);
 
+/* fp32-grade form of nerf_g1_render_fused for the reference's fp32 arithmetic (nn.Linear = fp32 addmm,
+ * nerf/model.py:525-542) on the tensor cores: every GEMM operand is split into two bf16 parts and each product is
+ * formed as hi*hi + lo*hi + hi*lo with fp32 accumulation in TMEM (~2^-17 relative; csrc/fused_tc_x3.cu).
+ * nerf_g1_pack_weights_x3: flat fp32 parameters (Dx = Dd = 3) -> the hi/lo weight image of nerf_g1_packed_x3_bytes().
+ * nerf_g1_render_fused_x3: arguments as nerf_g1_render_fused without the conditional inputs and the host noise;
+ * workspace = nerf_g1_render_workspace_bytes(B, S, 3, 0). */
+int64_t nerf_g1_packed_x3_bytes(void);
+int nerf_g1_pack_weights_x3(const float* params, void* packed, void* stream);
+int nerf_g1_render_fused_x3(const void* packed, const float* rays_o, const float* rays_d,
+                            const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                            float focal, int64_t ray_begin, int64_t B, int S,
+                            float near_plane, float far_plane, const float* t_base, const float* t_in,
+                            const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                            float noise_std, float normalize_position, int normalize_direction,
+                            float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
+                            float* out_t, float* out_sigma, float* out_rgb,
+                            void* workspace, int64_t workspace_bytes, void* stream);
+
 /* Test hook: the tcgen05 MLP alone on explicit rays and sample positions t [B,S]; when dbg
  * != NULL the normalised output of unit dbg_layer (fp32, [B*S,256]) is written there.
  * scratch_t [B,S] is overwritten. */

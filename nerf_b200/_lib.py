@@ -39,6 +39,11 @@ SIGNATURES = {
     "nerf_g1_render_fused": (c_i, [c_p, c_i, c_i, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_f, c_l, c_l, c_i,
                                    c_f, c_f, c_p, c_p, c_p, c_i, c_u64, c_l, c_p, c_f, c_f, c_i, c_p, c_l, c_l,
                                    c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_p]),
+    "nerf_g1_packed_x3_bytes": (c_l, []),
+    "nerf_g1_pack_weights_x3": (c_i, [c_p, c_p, c_p]),
+    "nerf_g1_render_fused_x3": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_f, c_l, c_l, c_i,
+                                      c_f, c_f, c_p, c_p, c_p, c_i, c_u64, c_l, c_f, c_f, c_i,
+                                      c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_p]),
     "nerf_g1_mlp_tc_debug": (c_i, [c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_i, c_p, c_p, c_p, c_p, c_i, c_p]),
     "nerf_tc_wgrad_debug": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_p]),
     "nerf_g1_train_workspace_bytes": (c_l, [c_l, c_i, c_i]),

@@ -302,7 +302,9 @@ extern "C" int64_t nerf_g1_render_workspace_bytes(int64_t B, int S, int Dx, int6
     return n;
 }
 
-extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
+int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st);      // fused_tc_x3.cu
+
+static int render_fused_impl(bool x3, const void* packed, int Dx, int Dd,
                                     const float* rays_o, const float* rays_d,
                                     const float* cam_o, const float* cam_r, int n_cams, int H, int W,
                                     float focal, int64_t ray_begin, int64_t B, int S,
@@ -316,6 +318,7 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
                                     void* workspace, int64_t workspace_bytes, void* stream) {
     if (!packed || B < 0 || S < 32 || S > 4096) return (S > 0 && S < 32) ? NERF_ERR_UNSUPPORTED : NERF_ERR_BAD_ARG;
     if (!rays_o != !rays_d || Dx < 3 || Dx > 16) return NERF_ERR_BAD_ARG;
+    if (x3 && (Dx != 3 || Dd != 3)) return NERF_ERR_UNSUPPORTED;
     if (B == 0) return NERF_OK;                                   // zero rays: nothing to do (empty tensors carry null pointers)
     if (Dx == 3) n_states = 0;
     else if (!states_x || n_states <= 0 || rays_per_state <= 0 ||
@@ -345,7 +348,7 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
     a.near_plane = near_plane; a.far_plane = far_plane; a.norm = normalize_position; a.normalize_dir = normalize_direction;
     a.out_t = out_t ? out_t : ws_t; a.out_sigma = out_sigma ? out_sigma : ws_sigma; a.out_rgb = out_rgb ? out_rgb : ws_rgb;
     a.dbg = nullptr; a.dbg_layer = -1;
-    int rc = launch_fused(packed, Dx, Dd, a, st); if (rc) return rc;
+    int rc = x3 ? launch_fused_x3(packed, a, st) : launch_fused(packed, Dx, Dd, a, st); if (rc) return rc;
     if (noise) return NERF_ERR_UNSUPPORTED;   // host-supplied noise is added by the binding on out_sigma before compositing
     if (noise_std != 0.0f) { rc = nerf_add_density_noise(a.out_sigma, S, B, noise_std, seed, ray_id_base, stream); if (rc) return rc; }
     if (out_pixels || out_depth || out_acc || out_weights) {
@@ -355,6 +358,38 @@ extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd,
         if (rc) return rc;
     }
     return NERF_OK;
+}
+
+extern "C" int nerf_g1_render_fused(const void* packed, int Dx, int Dd, const float* rays_o, const float* rays_d,
+                                    const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                    float focal, int64_t ray_begin, int64_t B, int S,
+                                    float near_plane, float far_plane, const float* t_base, const float* t_in,
+                                    const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                    const float* noise, float noise_std, float normalize_position, int normalize_direction,
+                                    const float* states_x, int64_t n_states, int64_t rays_per_state,
+                                    float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
+                                    float* out_t, float* out_sigma, float* out_rgb,
+                                    void* workspace, int64_t workspace_bytes, void* stream) {
+    return render_fused_impl(false, packed, Dx, Dd, rays_o, rays_d, cam_o, cam_r, n_cams, H, W, focal, ray_begin, B, S, near_plane, far_plane,
+                             t_base, t_in, u, jitter, seed, ray_id_base, noise, noise_std, normalize_position, normalize_direction,
+                             states_x, n_states, rays_per_state, out_pixels, out_depth, out_acc, out_weights, out_t, out_sigma, out_rgb,
+                             workspace, workspace_bytes, stream);
+}
+
+// The same pass with fp32-grade operands (three bf16 products per term, fused_tc_x3.cu); `packed` from nerf_g1_pack_weights_x3.
+extern "C" int nerf_g1_render_fused_x3(const void* packed, const float* rays_o, const float* rays_d,
+                                       const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                       float focal, int64_t ray_begin, int64_t B, int S,
+                                       float near_plane, float far_plane, const float* t_base, const float* t_in,
+                                       const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                       float noise_std, float normalize_position, int normalize_direction,
+                                       float* out_pixels, float* out_depth, float* out_acc, float* out_weights,
+                                       float* out_t, float* out_sigma, float* out_rgb,
+                                       void* workspace, int64_t workspace_bytes, void* stream) {
+    return render_fused_impl(true, packed, 3, 3, rays_o, rays_d, cam_o, cam_r, n_cams, H, W, focal, ray_begin, B, S, near_plane, far_plane,
+                             t_base, t_in, u, jitter, seed, ray_id_base, nullptr, noise_std, normalize_position, normalize_direction,
+                             nullptr, 0, 1, out_pixels, out_depth, out_acc, out_weights, out_t, out_sigma, out_rgb,
+                             workspace, workspace_bytes, stream);
 }
 
 // test/debug entry: the MLP alone on explicit rays + t, optionally dumping the normalised

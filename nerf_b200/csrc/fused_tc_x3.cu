@@ -1,0 +1,280 @@
+// fp32-grade forward on the tensor cores ("bf16x3"): ray-gen + sample + encode + G1 MLP, the same persistent
+// CTA-pair kernel as fused_tc.cu, with every GEMM operand split into two bf16 parts,
+//     a = a_hi + a_lo,  w = w_hi + w_lo,   a w  ~=  a_hi w_hi + a_lo w_hi + a_hi w_lo      (fp32 accumulate in TMEM),
+// i.e. three tcgen05.mma (kind::f16) per K = 16 step.  The dropped a_lo w_lo term is ~2^-18 of the product, so the
+// contraction carries ~16-17 significant bits -- the reference's arithmetic is fp32 `addmm`
+// (/root/reference/nerf/model.py:525-542) and tcgen05 has no fp32 MMA.  LayerNorm statistics, heads and the
+// encodings stay fp32 as in the bf16 kernel; bias' still rides in the accumulator as three bf16 parts.
+//
+// Shared memory is the bf16 kernel's layout, used by ONE 128-point tile per CTA instead of two:
+//   SM_ACT  [hi: 4 slabs | lo: 4 slabs]   (the second tile slot's 64 KB hold the lo parts)
+//   SM_PE   [hi slab | lo slab]
+//   ring    3 x 20 KB: [bias block 4 KB (first stage of a unit without an encoding slab)] [4 k-cores hi | 4 k-cores lo]
+// so a ring stage covers K = 32 (two K-steps, six MMAs).  One accumulator (256 TMEM columns): the MMAs of unit l+1
+// depend on the whole epilogue of unit l of the same tile, so tensor pipe and epilogue alternate; the price of
+// fp32-grade operands here is ~3x the MMAs and no tile ping-pong.
+//   warp 0    TMA producer      warp 1    MMA issuer (leader) / weight-arrival relay (peer)
+//   warps 2-5 encoder + epilogue (thread = point row = TMEM lane)
+#include "tc_fused_kernel.cuh"
+
+#define X3_THREADS 192
+
+// ReLU + LayerNorm epilogue of one unit (the arithmetic of epilogue_unit in tc_fused_kernel.cuh); pass 2 writes the
+// normalised row twice: hi = bf16(n), lo = bf16(n - hi).   MODE: 0 plain, 1 unit 7 (+ density), 2 unit 9 (+ colour, no store)
+template <int MODE>
+__device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, uint32_t taddr, uint32_t act_addr, uint32_t row,
+                                              uint32_t vec_addr, const RowState& st) {
+    const uint32_t hsum_addr = vec_addr + (SM_HSUM - SM_VEC);
+    uint32_t r0[32], r1[32];
+    float2 s2 = make_float2(0.f, 0.f), q2 = s2, s3 = s2, q3 = s2;
+    float2 hp0 = s2, hp1 = s2, hp2 = s2, hp0b = s2, hp1b = s2, hp2b = s2;
+    auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            float2 z0 = f2(rc[j], rc[j + 1]), z1 = f2(rc[j + 2], rc[j + 3]);
+            z0.x = fmaxf(z0.x, 0.f); z0.y = fmaxf(z0.y, 0.f); z1.x = fmaxf(z1.x, 0.f); z1.y = fmaxf(z1.y, 0.f);
+            s2 = __fadd2_rn(s2, z0); s3 = __fadd2_rn(s3, z1);
+            q2 = __ffma2_rn(z0, z0, q2); q3 = __ffma2_rn(z1, z1, q3);
+            if (MODE == 1) {
+                const float4 w = tc::lds128(vec_addr + (ch * 32 + j) * 4);
+                hp0 = __ffma2_rn(z0, make_float2(w.x, w.y), hp0); hp0b = __ffma2_rn(z1, make_float2(w.z, w.w), hp0b);
+            } else if (MODE == 2) {
+                const float4 w0 = tc::lds128(vec_addr + (256 + ch * 32 + j) * 4);
+                const float4 w1 = tc::lds128(vec_addr + (512 + ch * 32 + j) * 4);
+                const float4 w2 = tc::lds128(vec_addr + (768 + ch * 32 + j) * 4);
+                hp0 = __ffma2_rn(z0, make_float2(w0.x, w0.y), hp0); hp0b = __ffma2_rn(z1, make_float2(w0.z, w0.w), hp0b);
+                hp1 = __ffma2_rn(z0, make_float2(w1.x, w1.y), hp1); hp1b = __ffma2_rn(z1, make_float2(w1.z, w1.w), hp1b);
+                hp2 = __ffma2_rn(z0, make_float2(w2.x, w2.y), hp2); hp2b = __ffma2_rn(z1, make_float2(w2.z, w2.w), hp2b);
+            }
+        }
+    };
+    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+#pragma unroll 1
+    for (int c2 = 0; c2 < 4; ++c2) {
+        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
+        pass1(r0, 2 * c2);
+        tc::tmem_ld_wait();
+        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
+        pass1(r1, 2 * c2 + 1);
+        tc::tmem_ld_wait();
+    }
+    s2 = __fadd2_rn(s2, s3); q2 = __fadd2_rn(q2, q3);
+    const float mean = (s2.x + s2.y) * (1.0f / 256.f);
+    const float var = fmaxf((q2.x + q2.y) * (1.0f / 256.f) - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + NERF_LN_EPS);
+    const float shift = -mean * rstd;
+    const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
+    if (MODE == 1 || MODE == 2) {
+        const float4 hbias = tc::lds128(vec_addr + (TC_VEC_HEADB - TC_VEC_HEADW) * 4);
+        const float4 hwsum = tc::lds128(hsum_addr);
+        hp0 = __fadd2_rn(hp0, hp0b); hp1 = __fadd2_rn(hp1, hp1b); hp2 = __fadd2_rn(hp2, hp2b);
+        if (st.valid) {
+            if (MODE == 1) a.out_sigma[st.p] = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.x, hbias.x));
+            else {
+                a.out_rgb[st.p * 3] = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.y, hbias.y));
+                a.out_rgb[st.p * 3 + 1] = fmaf(rstd, hp1.x + hp1.y, fmaf(shift, hwsum.z, hbias.z));
+                a.out_rgb[st.p * 3 + 2] = fmaf(rstd, hp2.x + hp2.y, fmaf(shift, hwsum.w, hbias.w));
+            }
+        }
+    }
+    if (MODE == 2) return;                                         // unit 9 feeds only the colour head
+    auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
+        uint32_t hi[16], lo[16];
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+            float2 y = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, shift2);
+            y.x = fmaxf(y.x, shift); y.y = fmaxf(y.y, shift);      // = relu(z) rstd + shift  (rstd > 0)
+            const __nv_bfloat162 h = __float22bfloat162_rn(y);
+            const float2 hf = __bfloat1622float2(h);
+            const __nv_bfloat162 l2 = __float22bfloat162_rn(make_float2(y.x - hf.x, y.y - hf.y));
+            hi[j / 2] = *reinterpret_cast<const uint32_t*>(&h); lo[j / 2] = *reinterpret_cast<const uint32_t*>(&l2);
+        }
+        const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            store_row_chunk(slab, row, (ch & 1) * 4 + i, make_uint4(hi[i * 4], hi[i * 4 + 1], hi[i * 4 + 2], hi[i * 4 + 3]));
+            store_row_chunk(slab + 65536, row, (ch & 1) * 4 + i, make_uint4(lo[i * 4], lo[i * 4 + 1], lo[i * 4 + 2], lo[i * 4 + 3]));
+        }
+    };
+    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+#pragma unroll 1
+    for (int c2 = 0; c2 < 4; ++c2) {
+        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
+        pass2(r0, 2 * c2);
+        tc::tmem_ld_wait();
+        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
+        pass2(r1, 2 * c2 + 1);
+        tc::tmem_ld_wait();
+    }
+}
+
+__global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedArgs a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = tc::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* sm = smem_raw + (base - raw);
+    float* vec_s = reinterpret_cast<float*>(sm + SM_VEC);
+    const uint32_t bar0 = base + SM_BAR;
+    auto ring_full = [&](int s) { return bar0 + 8u * s; };
+    auto ring_empty = [&](int s) { return bar0 + 8u * (TC_RING + s); };
+    const uint32_t act_ready = bar0 + 8u * (2 * TC_RING), acc_ready = bar0 + 8u * (2 * TC_RING + 1);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 2));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int G = gridDim.x / 2, me = blockIdx.x / 2;
+    const int n_units = (a.n_tiles + 1) / 2;                       // tile pairs; this CTA takes tile 2 * unit + rank
+    const int n_my = (me < n_units) ? (n_units - me + G - 1) / G : 0;
+
+    for (int i = threadIdx.x; i < TC_SMVEC_FLOATS; i += X3_THREADS) vec_s[i] = a.vec[TC_VEC_HEADW + i];
+    if (warp < 4) {
+        float sw = 0.f;
+        for (int i = lane; i < 256; i += 32) sw += a.vec[TC_VEC_HEADW + warp * 256 + i];
+        sw = warp_sum(sw);
+        if (lane == 0) reinterpret_cast<float*>(sm + SM_HSUM)[warp] = sw;
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), leader ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
+        tc::mbar_init(act_ready, 8); tc::mbar_init(acc_ready, 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 256);
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer: this CTA's n-half of every K = 32 group, hi and lo together =====================
+        uint32_t it = 0;
+        for (int q = 0; q < n_my; ++q)
+            for (int l = 0; l < 10; ++l) {
+                const uint32_t blk_bytes = tc_unit_has_bias_block(l) ? TF_BIAS_KCORES * TF_KCORE_BYTES : 0;
+                const uint8_t* src = a.stages + a.unit_off[l] + (size_t)rank * a.half_kcores[l] * TF_KCORE_BYTES;
+                for (int j = 0; j < 2 * a.nk[l]; ++j, ++it) {
+                    const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                    const uint32_t bytes = X3_GROUP_BYTES + (j == 0 ? blk_bytes : 0);
+                    tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
+                    if (tc::elect_one()) {
+                        tc::mbar_arrive_expect_tx(ring_full(slot), bytes);
+                        tc::tma_load_1d(base + SM_RING + slot * TF_SLOT_BYTES, src, bytes, ring_full(slot));
+                    }
+                    __syncwarp();
+                    src += bytes;
+                }
+            }
+    } else if (warp == 1) {
+        if (leader) {
+            // ===================== MMA issuer: three products per K-step =====================
+            const uint32_t idesc = tc::umma_idesc_bf16(256, 256);
+            constexpr uint32_t hi_a = (1024u >> 4) | (1u << 14) | (2u << 29);             // SW128 K-major slabs
+            constexpr uint32_t hi_b = (TF_B_SBO >> 4) | (1u << 14);                       // no-swizzle k-cores
+            auto lo_a = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
+            const uint32_t ring_lo = (((base + SM_RING) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
+            auto mma = [&](uint32_t alo, uint32_t blo, uint32_t acc) {
+                tc::umma_bf16_2cta(tmem_base, ((uint64_t)hi_a << 32) | alo, ((uint64_t)hi_b << 32) | blo, idesc, acc);
+            };
+            const uint32_t act_lo = lo_a(base + SM_ACT), pe_lo = lo_a(base + SM_PE);
+            constexpr uint32_t ACT_LO_PART = 65536u >> 4, PE_LO_PART = TC_SLAB_BYTES >> 4;   // hi -> lo distance, in descriptor units
+            uint32_t it = 0, act_it = 0;
+            for (int q = 0; q < n_my; ++q)
+                for (int l = 0; l < 10; ++l) {
+                    tc::mbar_wait_spin(act_ready, act_it & 1, a.wait_hint); ++act_it;
+                    tc::tcgen05_fence_after();
+                    const bool blk = tc_unit_has_bias_block(l);
+                    const int ng = 2 * a.nk[l];
+                    for (int j = 0; j < ng; ++j, ++it) {
+                        const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                        const int slab = j >> 1;
+                        const bool enc = (l == 0 || slab >= 4);
+                        const uint32_t a_hi = (enc ? pe_lo : act_lo + slab * (TC_SLAB_BYTES >> 4)) + (j & 1) * 4;   // 32 columns = 64 B = 4 units
+                        const uint32_t a_lo = a_hi + (enc ? PE_LO_PART : ACT_LO_PART);
+                        uint32_t blo = ring_lo + slot * (TF_SLOT_BYTES >> 4);
+                        tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
+                        if (tc::elect_one()) {
+                            uint32_t acc = (j != 0) ? 1u : 0u;
+                            if (blk && j == 0) {                   // acc = b': hi slab columns 48..63 (ones at 60..62) x bias block
+                                mma(pe_lo + 3 * 2, blo, 0); acc = 1u;
+                                blo += (TF_BIAS_KCORES * TF_KCORE_BYTES) >> 4;
+                            }
+#pragma unroll
+                            for (int kk = 0; kk < 2; ++kk) {
+                                const uint32_t bh = blo + kk * (2 * TF_KCORE_BYTES >> 4), bl = bh + (4 * TF_KCORE_BYTES >> 4);
+                                mma(a_hi + kk * 2, bh, acc);
+                                mma(a_lo + kk * 2, bh, 1u);
+                                mma(a_hi + kk * 2, bl, 1u);
+                                acc = 1u;
+                            }
+                            tc::umma_commit_2cta(ring_empty(slot));
+                            if (j == ng - 1) tc::umma_commit_2cta(acc_ready);
+                        }
+                        __syncwarp();
+                    }
+                }
+        } else if (lane == 0) {
+            // ===================== peer relay: "my weight half has landed" -> leader's full barrier =====================
+            uint32_t it = 0;
+            for (int q = 0; q < n_my; ++q)
+                for (int l = 0; l < 10; ++l)
+                    for (int j = 0; j < 2 * a.nk[l]; ++j, ++it) {
+                        const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
+                        tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
+                        tc::mbar_arrive_cluster(tc::mapa(ring_full(slot), 0));
+                    }
+        }
+    } else {
+        // ===================== encoder + epilogue =====================
+        const uint32_t row = (warp & 3) * 32 + lane;                 // TMEM lane quarter = warp % 4
+        const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16);
+        const uint32_t act_addr = base + SM_ACT, pe_addr = base + SM_PE;
+        const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
+        auto signal_act = [&]() {
+            tc::fence_proxy_async_smem();
+            tc::tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
+        };
+        uint32_t acc_it = 0;
+        for (int q = 0; q < n_my; ++q) {
+            const int unit = me + q * G;
+            const int tile = 2 * unit + (int)rank;
+            RowState st;
+            encode_row<true>(a, tile, row, pe_addr, st);
+            signal_act();
+            for (int l = 0; l < 10; ++l) {
+                tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;
+                tc::tcgen05_fence_after();
+                if (l == 7) epilogue_unit_x3<1>(a, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 9) epilogue_unit_x3<2>(a, taddr, act_addr, row, base + SM_VEC, st);
+                else epilogue_unit_x3<0>(a, taddr, act_addr, row, base + SM_VEC, st);
+                if (l == 4) encode_dir_row<true>(a, row, pe_addr, st);     // unit 4 was the last reader of the position slabs
+                if (l < 9) signal_act();
+            }
+        }
+    }
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 256); }
+}
+
+// launches the x3 kernel on a.n_tiles tiles; `packed` = the image of nerf_g1_pack_weights_x3
+int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st) {
+    X3Layout X; make_x3_layout(X);
+    for (int l = 0; l < 10; ++l) { a.nk[l] = X.nk[l]; a.unit_off[l] = X.unit_off[l]; a.half_kcores[l] = (int)(X.half_bytes[l] / TF_KCORE_BYTES); }
+    a.stages = (const uint8_t*)packed;
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + X.weight_bytes);
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    a.wait_hint = wait_hint; a.prof = nullptr; a.ray_bias = nullptr;
+    NERF_CUDA(nerf_smem_opt_in<g1_fused_x3_kernel>(TC_SMEM_BYTES));
+    const int sms = nerf_num_sms();
+    const int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(X3_THREADS); cfg.dynamicSmemBytes = TC_SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel, a));
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}

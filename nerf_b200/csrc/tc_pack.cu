@@ -99,6 +99,73 @@ __global__ void pack_state_weights_kernel(const float* __restrict__ params, Pack
     sw[i] = params[L.off_W[l] + (size_t)n * L.Kt[l] + (u ? 256 : 0) + 2 * NERF_PE_X_OCTAVES * 3 + k];
 }
 
+// ---- fp32-grade image (fused_tc_x3.cu): the same folded weights, split hi = bf16(w'), lo = bf16(w' - hi) ----
+// folded weight of unit l, output feature n, K index kk of the unit's slab sequence [hidden 256 | encoding 64]
+__device__ __forceinline__ float folded_weight(const float* __restrict__ params, const PackLayout& L, const float* __restrict__ vec,
+                                               int l, int n, int kk) {
+    const int Kt = L.Kt[l];
+    const float* W = params + L.off_W[l];
+    const int hid = (l == 0) ? 0 : 256;
+    if (kk < hid) return W[(size_t)n * Kt + kk] * params[L.off_gamma[l - 1] + kk];
+    const int k2 = kk - hid;
+    const int n_enc = (l == 8) ? L.ED : 2 * NERF_PE_X_OCTAVES * 3;
+    if (k2 < n_enc) return W[(size_t)n * Kt + hid + k2];
+    if (k2 >= TC_ONES_COL && k2 < TC_ONES_COL + 3) { float p3[3]; split_bias3(vec[TC_VEC_BIAS + l * 256 + n], p3); return p3[k2 - TC_ONES_COL]; }
+    return 0.f;
+}
+// one thread per 16-byte row of a k-core: (unit, n-half, k-core of the half's sequence, n)
+__global__ void pack_stage_x3_kernel(const float* __restrict__ params, PackLayout L, X3Layout X, const float* __restrict__ vec,
+                                     uint8_t* __restrict__ packed) {
+    const int l = blockIdx.y;
+    const bool blk = tc_unit_has_bias_block(l);
+    const int cores = (int)(X.half_bytes[l] / TF_KCORE_BYTES);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * cores * 128) return;
+    const int r = i & 127, kc = (i >> 7) % cores, nh = (i >> 7) / cores;
+    const int n = nh * 128 + r;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    bool lo_part = false;
+    if (blk && kc < TF_BIAS_KCORES) {
+        if (kc == 1) { float p3[3]; split_bias3(vec[TC_VEC_BIAS + l * 256 + n], p3); v[4] = p3[0]; v[5] = p3[1]; v[6] = p3[2]; }
+    } else {
+        const int c = kc - (blk ? TF_BIAS_KCORES : 0);              // group g = c / 8: [4 k-cores hi | 4 k-cores lo]
+        const int g = c >> 3, kq = c & 3;
+        lo_part = (c & 4) != 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = folded_weight(params, L, vec, l, n, g * 32 + kq * 8 + j);
+    }
+    if (lo_part) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = v[j] - __bfloat162float(__float2bfloat16_rn(v[j]));
+    }
+    uint8_t* dst = packed + X.unit_off[l] + (size_t)nh * X.half_bytes[l] + (size_t)kc * TF_KCORE_BYTES + (r >> 3) * TF_B_SBO + (r & 7) * 16;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(tc::pack_bf16x2(v[0], v[1]), tc::pack_bf16x2(v[2], v[3]),
+                                                tc::pack_bf16x2(v[4], v[5]), tc::pack_bf16x2(v[6], v[7]));
+}
+
+extern "C" int64_t nerf_g1_packed_x3_bytes(void) {
+    X3Layout X; make_x3_layout(X);
+    return tc_packed_x3_total(X);
+}
+
+extern "C" int nerf_g1_pack_weights_x3(const float* params, void* packed, void* stream) {
+    if (!params || !packed) return NERF_ERR_BAD_ARG;
+    PackLayout L; int rc = make_pack_layout(3, 3, L); if (rc) return rc;
+    X3Layout X; make_x3_layout(X);
+    cudaStream_t st = (cudaStream_t)stream;
+    float* vec = reinterpret_cast<float*>((uint8_t*)packed + X.weight_bytes);
+    const int warps = 10 * 256 + 4;
+    pack_vectors_kernel<<<(warps * 32 + 255) / 256, 256, 0, st>>>(params, L, vec);
+    NERF_CUDA_CHECK_LAUNCH();
+    int64_t max_cores = 0;
+    for (int l = 0; l < 10; ++l) max_cores = X.half_bytes[l] / TF_KCORE_BYTES > max_cores ? X.half_bytes[l] / TF_KCORE_BYTES : max_cores;
+    pack_stage_x3_kernel<<<dim3((unsigned)((2 * max_cores * 128 + 255) / 256), 10), 256, 0, st>>>(params, L, X, vec, (uint8_t*)packed);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
 extern "C" int64_t nerf_g1_packed_bytes(int Dx, int Dd) {
     PackLayout L;
     if (make_pack_layout(Dx, Dd, L) != NERF_OK) return NERF_ERR_BAD_ARG;

@@ -217,7 +217,8 @@ class NeRF(nn.Module):
             return dict(pixels=pixels, depth=depth, acc=acc, weights=weights, t=t, density=sigma.unsqueeze(-1), color=rgb)
         if self._fused_ok(num_samples, states_x, states_d) and noise is None:
             # tcgen05 path: one persistent kernel for sample+encode+MLP, then the compositing kernel
-            packed = ops.g1_pack_weights(self.flat_parameters(), self.density_inputs, 3)
+            x3 = self.precision == "bf16x3"
+            packed = self._packed(x3)
             sl = lambda x, i, j: None if x is None else x[i:j]
             step = max(b, 1) if states_x is None else 1 << 17      # conditional: 2 KB of bias rows per ray in the workspace
             outs = []
@@ -227,7 +228,7 @@ class NeRF(nn.Module):
                                                 rays_o=rays_o[i:j], rays_d=rays_d[i:j], t_in=sl(t, i, j), u=sl(u, i, j),
                                                 t_base=self._ladder(near, far, num_samples, rays_o.device),
                                                 want=("pixels", "depth", "acc", "weights", "t", "sigma", "rgb"),
-                                                states_x=sl(states_x, i, j)))
+                                                states_x=sl(states_x, i, j), x3=x3))
             out = outs[0] if len(outs) == 1 else {k: torch.cat([o[k] for o in outs], dim=0) for k in outs[0]}
             out["density"] = out.pop("sigma").unsqueeze(-1); out["color"] = out.pop("rgb")
             return out
@@ -245,9 +246,20 @@ class NeRF(nn.Module):
         return (self.precision == "bf16" and num_samples >= 32
                 and self.density_inputs == 3 + sx and self.color_inputs == 3 and states_d is None)
 
+    def _x3_ok(self, num_samples, states_x, states_d):
+        """fp32-grade tensor-core forward (hi/lo operand split, csrc/fused_tc_x3.cu): unconditional model, no graph"""
+        return (self.precision == "bf16x3" and num_samples >= 32 and self.density_inputs == 3 and self.color_inputs == 3
+                and states_x is None and states_d is None and not self._wants_grad())
+
+    def _packed(self, x3):
+        flat = self.flat_parameters()
+        return ops.g1_pack_weights_x3(flat) if x3 else ops.g1_pack_weights(flat, self.density_inputs, 3)
+
     def _fused_ok(self, num_samples, states_x, states_d):
-        """bf16 tcgen05 render path (no graph recorded): position-side conditional inputs are supported,
-        direction-side ones take the fp32 kernels."""
+        """tcgen05 render path (no graph recorded).  bf16: position-side conditional inputs are supported,
+        direction-side ones take the fp32 kernels; bf16x3: the unconditional model."""
+        if self._x3_ok(num_samples, states_x, states_d):
+            return True
         return self._tc_shape_ok(num_samples, states_x, states_d) and not self._wants_grad()
 
     def _wants_grad(self):
@@ -293,7 +305,8 @@ class NeRF(nn.Module):
         chunk = self.max_chunk_rays if max_chunk_size is None else int(max_chunk_size)
         outs = []
         if self._fused_ok(num_samples, states_x, states_d) and num_fine == 0:
-            packed = ops.g1_pack_weights(self.flat_parameters(), self.density_inputs, 3)
+            x3 = self.precision == "bf16x3"
+            packed = self._packed(x3)
             if states_x is not None:                        # one state row per camera (train_conditional_nerf.py:141-153)
                 states_x = states_x.float().reshape(-1, states_x.shape[-1]).expand(bc, -1).contiguous()
             big = 1 << 20                                   # rays per launch (bounds the t/sigma/rgb workspace)
@@ -304,7 +317,7 @@ class NeRF(nn.Module):
                                         camera=(camera_o, camera_r, image_h, image_w, focal_length),
                                         ray_begin=i, num_rays=j - i,
                                         t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",),
-                                        states_x=states_x, rays_per_state=image_h * image_w)
+                                        states_x=states_x, rays_per_state=image_h * image_w, x3=x3)
                 outs.append(r["pixels"])
             img = torch.cat(outs, dim=0)
             return img.reshape(bc, image_h, image_w, 3) if full else img

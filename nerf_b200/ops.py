@@ -11,8 +11,11 @@ import torch
 from . import _lib
 from ._lib import check, lib, ptr, stream
 
-PREC_FP32, PREC_BF16 = 0, 1
-PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16}
+# precision of the MLP contraction: "fp32" = FFMA tiles (the <= 1e-3 parity mode, forward and backward); "bf16" = tcgen05
+# kind::f16 (forward, backward, training); "bf16x3" = fp32-grade operands on tcgen05 (hi/lo split, three products per term):
+# the fused forward / render only -- its graph-recording path is the fp32 FFMA one
+PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
+PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
 HIDDEN = 256
 
 
@@ -316,6 +319,13 @@ def g1_train_tc(flat, params, rays_o, rays_d, num_samples, near, far, normalize_
     return _G1TrainTC.apply(flat, _f32c(rays_o), _f32c(rays_d), _f32c(t_base), _f32c(t_in), _f32c(u), states_x, cfg, *params)
 
 
+def g1_pack_weights_x3(flat):
+    """fp32 flat parameters -> hi/lo bf16 weight image of the fp32-grade tensor-core forward (csrc/fused_tc_x3.cu)."""
+    packed = torch.empty(lib().nerf_g1_packed_x3_bytes(), dtype=torch.uint8, device=flat.device)
+    check(lib().nerf_g1_pack_weights_x3(ptr(flat), ptr(packed), stream()), "nerf_g1_pack_weights_x3")
+    return packed
+
+
 def g1_mlp_tc_debug(packed, rays_o, rays_d, t, normalize_position, normalize_direction=True, dbg_layer=-1):
     rays_o, rays_d, t = _f32c(rays_o), _f32c(rays_d), _f32c(t)
     b, s = t.shape
@@ -332,7 +342,7 @@ def g1_mlp_tc_debug(packed, rays_o, rays_d, t, normalize_position, normalize_dir
 def g1_render_fused(packed, num_samples, near, far, normalize_position, normalize_direction=True,
                     rays_o=None, rays_d=None, camera=None, ray_begin=0, num_rays=None,
                     t_base=None, t_in=None, u=None, jitter=False, seed=0, ray_id_base=0, noise_std=0.0,
-                    want=("pixels", "depth", "acc", "weights", "t"), states_x=None, rays_per_state=1):
+                    want=("pixels", "depth", "acc", "weights", "t"), states_x=None, rays_per_state=1, x3=False):
     """One fused pass.  camera = (cam_o [n,3], cam_r [n,3,3], H, W, focal) when rays are not given.
     states_x [n,Sx] (conditional model, `packed` built with density_inputs = 3 + Sx): one row per
     `rays_per_state` consecutive rays (camera mode: flattened ray ids)."""
@@ -354,6 +364,17 @@ def g1_render_fused(packed, num_samples, near, far, normalize_position, normaliz
     nbytes = lib().nerf_g1_render_workspace_bytes(b, s, dx, n_states)
     ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
     g = lambda k: ptr(out.get(k))
+    if x3:                                                          # fp32-grade operands: `packed` from g1_pack_weights_x3
+        if states_x is not None:
+            raise ValueError("the bf16x3 forward has no conditional inputs")
+        check(lib().nerf_g1_render_fused_x3(ptr(packed), ptr(rays_o), ptr(rays_d), ptr(cam_o), ptr(cam_r), n_cams, h, w,
+                                            float(focal), ray_begin, b, s, float(near), float(far), ptr(t_base), ptr(_f32c(t_in)),
+                                            ptr(_f32c(u)), int(jitter), seed, ray_id_base, float(noise_std),
+                                            float(normalize_position), int(normalize_direction),
+                                            g("pixels"), g("depth"), g("acc"), g("weights"), g("t"), g("sigma"), g("rgb"),
+                                            ptr(ws), nbytes, stream()), "nerf_g1_render_fused_x3")
+        COUNTERS["g1_render_fused_x3"] += 1
+        return out
     check(lib().nerf_g1_render_fused(ptr(packed), dx, 3, ptr(rays_o), ptr(rays_d), ptr(cam_o), ptr(cam_r), n_cams, h, w,
                                      float(focal), ray_begin, b, s, float(near), float(far), ptr(t_base), ptr(_f32c(t_in)),
                                      ptr(_f32c(u)), int(jitter), seed, ray_id_base, None, float(noise_std),

@@ -19,6 +19,8 @@ class Trainer:
         self.near, self.far, self.num_samples = near, far, num_samples
         self.noise_std, self.jitter, self.seed = density_noise_std, randomly_sample, seed
         self.precision = ops.PRECISIONS[precision or model.precision]
+        if self.precision == ops.PREC_BF16X3:            # fp32-grade tensor-core operands exist for the forward only:
+            self.precision = ops.PREC_FP32               # the training step of that mode is the fp32 FFMA one
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
