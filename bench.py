@@ -503,6 +503,28 @@ def run_ours(args):
     render_tflops = render_rps * SAMPLES * FLOP_PER_POINT_FWD / 1e12
     rncu = ncu_counters(NCU_RENDER, ("g1_fused_tc_kernel",)).get("g1_fused_tc_kernel", {})
 
+    # ---- fp32-grade render on the tensor cores (precision="bf16x3", hi/lo operand split) beside the fp32 FFMA render ----
+    def _render_fp32_grade():
+        mx = NeRF(normalize_position=6.0, precision="bf16x3").to(dev); mx.load_state_dict(sd)
+        mf = NeRF(normalize_position=6.0, precision="fp32").to(dev); mf.load_state_dict(sd)
+        out = {}
+        with torch.no_grad():
+            for tag, m_, hw_ in (("bf16x3", mx, 800), ("fp32_ffma", mf, 200)):
+                f_ = TINY_NERF_FOCAL * hw_ / 100
+                m_.render_image(cam_o, cam_r, hw_, hw_, f_, NEAR, FAR, SAMPLES)
+                ms_ = float(np.mean(timed_steps(lambda i: m_.render_image(cam_o, cam_r, hw_, hw_, f_, NEAR, FAR, SAMPLES), 2, flush)))
+                rps_ = hw_ * hw_ / (ms_ * 1e-3)
+                out[tag] = {"value": rps_, "unit": "rays/s", "workload": f"{hw_}x{hw_} x {SAMPLES} samples render_image, one GPU",
+                            "mlp_tflops": rps_ * SAMPLES * FLOP_PER_POINT_FWD / 1e12}
+            a_ = mx.render_image(cam_o, cam_r, 100, 100, TINY_NERF_FOCAL, NEAR, FAR, SAMPLES)
+            b_ = mf.render_image(cam_o, cam_r, 100, 100, TINY_NERF_FOCAL, NEAR, FAR, SAMPLES)
+        out["max_abs_pixel_diff_100x100"] = float((a_ - b_).abs().max().item())
+        out["speedup"] = out["bf16x3"]["value"] / out["fp32_ffma"]["value"]
+        out["note"] = ("fp32-mode accuracy (<= 1e-3 pixels, north star) on tcgen05: every GEMM operand split into two bf16 parts, "
+                       "hi*hi + lo*hi + hi*lo with fp32 accumulation (csrc/fused_tc_x3.cu); forward / render only")
+        return out
+    render_fp32_grade = safe("render_fp32_grade", _render_fp32_grade) if (world == 1 or args.all_sections) else None
+
     # ---- D3 / config 3: 800x800, 64 coarse + 128 fine, RAY-SHARDED over the ranks, frame gathered ----
     d3 = None
     render_sharded = None
@@ -665,6 +687,7 @@ def run_ours(args):
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak,
                        "frac_tensor_burst": render_tflops / peaks["tensor_burst"], "tensor_pipe_pct_ncu": rncu.get("tensor_pipe_pct"),
                        "ncu_source": rncu.get("source")},
+            "render_fp32_grade": render_fp32_grade,
             "render_sharded": render_sharded,
             "render_d3": d3,
             "train_c4": c4["train"], "render_c4": c4["render"],
