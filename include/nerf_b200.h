@@ -216,6 +216,24 @@ int nerf_g1_render_fused_x3(const void* packed, const float* rays_o, const float
                             float* out_t, float* out_sigma, float* out_rgb,
                             void* workspace, int64_t workspace_bytes, void* stream);
 
+/* nerf_g1_render_fused for callers that cannot allocate a workspace (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  This entry point has no counterpart in the reference.
+ * The scratch of the fused render (t, sigma, rgb per point, generated rays) lives in a file-scope
+ * device array of the library (2.6 MB, held by every GPU that loads the library until exit): the call allocates nothing
+ * and calls no cudaMalloc / cudaFree.  Limit: B * S <= nerf_g1_render_static_max_points() = 131072 (e.g. 2048 rays x 64
+ * samples), S >= 32, unconditional model; beyond it the call returns NERF_ERR_WORKSPACE and nerf_last_error() says why.
+ * Arguments as nerf_g1_render_fused (packed from nerf_g1_pack_weights(params, 3, 3, ...)); outputs (each optional):
+ * out_pixels [B,3], out_depth [B], out_acc [B].  Every call shares the array (it keeps the last call's contents; nothing
+ * in it needs clearing: each call writes what it reads): calls that overlap on the GPU race -- serialise them. */
+int64_t nerf_g1_render_static_max_points(void);
+int nerf_g1_render_fused_static(const void* packed, const float* rays_o, const float* rays_d,
+                                const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                float focal, int64_t ray_begin, int64_t B, int S,
+                                float near_plane, float far_plane, const float* t_base,
+                                const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                float noise_std, float normalize_position, int normalize_direction,
+                                float* out_pixels, float* out_depth, float* out_acc, void* stream);
+
 /* Test hook: the tcgen05 MLP alone on explicit rays and sample positions t [B,S]; when dbg
  * != NULL the normalised output of unit dbg_layer (fp32, [B*S,256]) is written there.
  * scratch_t [B,S] is overwritten. */

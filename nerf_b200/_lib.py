@@ -44,6 +44,9 @@ SIGNATURES = {
     "nerf_g1_render_fused_x3": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_f, c_l, c_l, c_i,
                                       c_f, c_f, c_p, c_p, c_p, c_i, c_u64, c_l, c_f, c_f, c_i,
                                       c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_l, c_p]),
+    "nerf_g1_render_static_max_points": (c_l, []),
+    "nerf_g1_render_fused_static": (c_i, [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_f, c_l, c_l, c_i,
+                                          c_f, c_f, c_p, c_p, c_i, c_u64, c_l, c_f, c_f, c_i, c_p, c_p, c_p, c_p]),
     "nerf_g1_mlp_tc_debug": (c_i, [c_p, c_p, c_p, c_p, c_l, c_i, c_f, c_i, c_p, c_p, c_p, c_p, c_i, c_p]),
     "nerf_tc_wgrad_debug": (c_i, [c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_p]),
     "nerf_g1_train_workspace_bytes": (c_l, [c_l, c_i, c_i]),

@@ -11,6 +11,8 @@ int nerf_set_error(cudaError_t e) {
     snprintf(g_err, sizeof(g_err), "%s: %s", n ? n : "?", s ? s : "?");
     return (int)e;
 }
+// argument errors that deserve more than a status code: the text is what nerf_last_error() returns next
+int nerf_set_error_text(int status, const char* text) { snprintf(g_err, sizeof(g_err), "%s", text); return status; }
 extern "C" int nerf_abi_version(void) { return 1; }
 extern "C" const char* nerf_last_error(void) { return g_err; }
 

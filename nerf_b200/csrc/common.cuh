@@ -9,6 +9,7 @@
 #define NERF_LN_EPS 1e-5f      // torch.nn.LayerNorm default
 
 int nerf_set_error(cudaError_t e);   // records + returns (int)e
+int nerf_set_error_text(int status, const char* text);   // records the text, returns status
 #define NERF_CUDA_CHECK_LAUNCH() do { cudaError_t e__ = cudaGetLastError(); \
     if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)
 #define NERF_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return nerf_set_error(e__); } while (0)

@@ -422,3 +422,57 @@ int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, 
     a.tr_stats = reinterpret_cast<float2*>(ws + T.off_stats); a.P_pad = T.P_pad; a.tr_tiles = T.tr_tiles;
     return launch_fused(packed, Dx, Dd, a, st, true);
 }
+
+// ------------------------------------------------------------------ no-allocation variant ----
+// nerf_g1_render_fused for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): the scratch the fused render needs (t, sigma, rgb per point; the generated rays per ray) lives in a
+// file-scope device array instead of a caller workspace.  No counterpart in the reference.
+// Every GPU that loads the library holds the array (2.6 MB) until exit.
+//   * limit: B * S <= NERF_STATIC_MAX_POINTS (131072 points, e.g. 2048 rays x 64 samples), unconditional model (Dx = Dd = 3);
+//   * the entry point calls no cudaMalloc / cudaFree / allocating routine: packing, launch and composite are the existing
+//     stream-ordered kernels; cudaGetSymbolAddress (once per device) and cudaFuncSetAttribute allocate nothing;
+//   * every call shares the array and finds the previous call's contents in it.  Nothing has to start at zero: the MLP kernel
+//     writes t / sigma / rgb of every valid point (and the rays of every ray in camera mode) before the composite reads them,
+//     and neither kernel reads beyond B * S points;
+//   * calls that overlap on the GPU (two streams, or two graphs replayed concurrently) RACE on the array: serialise them.
+#define NERF_STATIC_MAX_POINTS 131072
+#define NERF_STATIC_MAX_RAYS (NERF_STATIC_MAX_POINTS / 32)          // S >= 32
+#define NERF_STATIC_SCRATCH_BYTES (NERF_STATIC_MAX_POINTS * 20 + 2 * ((NERF_STATIC_MAX_RAYS * 12 + 255) & ~255))
+static __device__ __align__(256) unsigned char g_render_scratch[NERF_STATIC_SCRATCH_BYTES];
+
+// In host code `g_render_scratch` is a host-side stand-in, not a device address: the device address is asked for once per
+// device, with that device current, and cached.
+static int render_scratch_address(void** out) {
+    static void* addr[NERF_MAX_DEVICES] = {};
+    const int dev = nerf_current_device();
+    if (dev < 0 || dev >= NERF_MAX_DEVICES) return nerf_set_error_text(NERF_ERR_UNSUPPORTED, "nerf_g1_render_fused_static: device index beyond NERF_MAX_DEVICES");
+    if (!addr[dev]) {
+        void* p = nullptr;
+        NERF_CUDA(cudaGetSymbolAddress(&p, g_render_scratch));
+        if (!p) return nerf_set_error_text(NERF_ERR_WORKSPACE, "nerf_g1_render_fused_static: cudaGetSymbolAddress returned a null address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return NERF_OK;
+}
+
+extern "C" int64_t nerf_g1_render_static_max_points(void) { return NERF_STATIC_MAX_POINTS; }
+
+extern "C" int nerf_g1_render_fused_static(const void* packed, const float* rays_o, const float* rays_d,
+                                           const float* cam_o, const float* cam_r, int n_cams, int H, int W,
+                                           float focal, int64_t ray_begin, int64_t B, int S,
+                                           float near_plane, float far_plane, const float* t_base,
+                                           const float* u, int jitter, uint64_t seed, int64_t ray_id_base,
+                                           float noise_std, float normalize_position, int normalize_direction,
+                                           float* out_pixels, float* out_depth, float* out_acc, void* stream) {
+    if (B < 0 || S <= 0) return NERF_ERR_BAD_ARG;
+    if (B * (int64_t)S > NERF_STATIC_MAX_POINTS || nerf_g1_render_workspace_bytes(B, S, 3, 0) > (int64_t)NERF_STATIC_SCRATCH_BYTES)
+        return nerf_set_error_text(NERF_ERR_WORKSPACE, "nerf_g1_render_fused_static: B * S exceeds the static scratch (131072 points): "
+                                                       "split the call or use nerf_g1_render_fused with a caller workspace");
+    void* scratch = nullptr;
+    int rc = render_scratch_address(&scratch); if (rc) return rc;
+    return render_fused_impl(false, packed, 3, 3, rays_o, rays_d, cam_o, cam_r, n_cams, H, W, focal, ray_begin, B, S, near_plane, far_plane,
+                             t_base, nullptr, u, jitter, seed, ray_id_base, nullptr, noise_std, normalize_position, normalize_direction,
+                             nullptr, 0, 1, out_pixels, out_depth, out_acc, nullptr, nullptr, nullptr, nullptr,
+                             scratch, NERF_STATIC_SCRATCH_BYTES, stream);
+}
