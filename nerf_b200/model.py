@@ -310,15 +310,30 @@ class NeRF(nn.Module):
             if states_x is not None:                        # one state row per camera (train_conditional_nerf.py:141-153)
                 states_x = states_x.float().reshape(-1, states_x.shape[-1]).expand(bc, -1).contiguous()
             big = 1 << 20                                   # rays per launch (bounds the t/sigma/rgb workspace)
-            for i in range(ray_begin, ray_end, big):
-                j = min(i + big, ray_end)
+            # Launches are cut on multiples of `big` in the FRAME's ray ids, whatever the shard.  The composite inside the fused
+            # call picks its kernel by the launch's ray count (warp-per-ray below ops.COMPOSITE_WARP_BELOW, thread-per-ray
+            # from it on; they sum in different orders), so a shard piece shorter than that inside a frame piece that is not
+            # is widened to the threshold (rays are independent of their neighbours in both kernels) and sliced: a shard is
+            # bit-identical to the slice of the frame at any world size.
+            thr = ops.COMPOSITE_WARP_BELOW
+            i = ray_begin
+            while i < ray_end:
+                c0 = (i // big) * big
+                c1 = min(c0 + big, total)
+                j = min(c1, ray_end)
+                lo, hi = i, j
+                if hi - lo < thr <= c1 - c0:
+                    lo = max(c0, min(lo, c1 - thr)); hi = lo + thr
                 r = ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position,
                                         self.normalize_direction,
                                         camera=(camera_o, camera_r, image_h, image_w, focal_length),
-                                        ray_begin=i, num_rays=j - i,
+                                        ray_begin=lo, num_rays=hi - lo,
                                         t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",),
                                         states_x=states_x, rays_per_state=image_h * image_w, x3=x3)
-                outs.append(r["pixels"])
+                outs.append(r["pixels"][i - lo:j - lo])
+                i = j
+            if not outs:                                    # an empty shard (more ranks than rays)
+                return torch.empty(0, 3, device=camera_o.device)
             img = torch.cat(outs, dim=0)
             return img.reshape(bc, image_h, image_w, 3) if full else img
         # Chunks are cut on multiples of `chunk` in the FRAME's ray ids, whatever the shard: a shard then runs the frame's own chunks.

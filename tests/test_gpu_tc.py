@@ -121,6 +121,32 @@ def test_tc_hierarchical(model_bf16, g1_ref):
     assert err.max() < 0.01 and err.mean() < 1.5e-3                            # measured on B200: 2.1e-3 / 4.0e-4
 
 
+@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+def test_single_pass_shards_cross_the_composite_kernel_threshold(nerf_pth_state_dict, precision):
+    """A 200 x 200 frame (40 000 rays: the thread-per-ray composite) rendered as 8 shards of 5 000 rays (each below
+    ops.COMPOSITE_WARP_BELOW, where a launch of its own would take the warp-per-ray composite and sum in another order):
+    every shard must equal the slice of the frame bit for bit -- what `scripts/dp_check.py` found unequal on 8 GPUs."""
+    from oracle import g1
+    from nerf_b200 import ops
+    from nerf_b200.model import NeRF
+    from nerf_b200.parallel import shard_range
+    m = NeRF(normalize_position=6.0, precision=precision).cuda(); m.load_state_dict(nerf_pth_state_dict)
+    pose = g1.pose_spherical(30.0, -30.0, 4.0311).cuda()
+    co, cr = pose[None, :3, 3].contiguous(), pose[None, :3, :3].contiguous()
+    hw, focal = 200, g1.TINY_NERF_FOCAL * 2
+    assert hw * hw >= ops.COMPOSITE_WARP_BELOW > hw * hw // 8
+    with torch.no_grad():
+        frame = m.render_image(co, cr, hw, hw, focal, 2.0, 6.0, 64).reshape(-1, 3)
+        for world in (8, 3):
+            for r in range(world):
+                lo, hi = shard_range(hw * hw, r, world)
+                part = m.render_image(co, cr, hw, hw, focal, 2.0, 6.0, 64, ray_begin=lo, ray_end=hi)
+                assert torch.equal(part, frame[lo:hi]), (world, r, (part - frame[lo:hi]).abs().max().item())
+        assert m.render_image(co, cr, hw, hw, focal, 2.0, 6.0, 64, ray_begin=77, ray_end=77).shape == (0, 3)
+        tail = m.render_image(co, cr, hw, hw, focal, 2.0, 6.0, 64, ray_begin=hw * hw - 10, ray_end=hw * hw)
+        assert torch.equal(tail, frame[-10:])
+
+
 def test_d3_ray_subsets_vs_oracle(model_bf16, nerf_pth_state_dict, g1_oracle):
     """D3 (800 x 800, 64 coarse + 128 fine) against the ORACLE's hierarchical render on ray subsets of the frame: four
     runs of 64 consecutive ray ids (image centre, object edge, a corner, a row boundary), rendered as shards of the
