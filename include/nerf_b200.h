@@ -68,7 +68,7 @@ int nerf_gather_pixel_rays(const float* images, const float* poses, int pose_row
 
 /* G1 sampler: linspace(near, far, S) with the stratified jitter of
  * NeRF.sample_along_rays (nerf/model.py:422-433).  u [B,S] uniforms in [0,1)
- * or NULL; if u is NULL and jitter != 0 the uniforms come from Philox4x32-10
+ * or NULL; if u is NULL and jitter != 0 the uniforms come from Philox4x32-7
  * keyed by (seed, ray_id_base + ray, sample).  t_base [S] (device) optionally
  * supplies the un-jittered ladder (the host binding passes torch.linspace's own
  * output so the bins are bit-identical to the reference's); NULL = computed in
@@ -84,7 +84,7 @@ int nerf_sample_geometric(float box_diag, const float* t_base, int S, int64_t B,
                           float* t_out, void* stream);
 
 /* density noise of the training pass (nerf/model.py:652-654): sigma [B,S] +=
- * N(0,1)*std in place, Philox4x32-10 keyed by (seed, ray_id_base + ray, sample). */
+ * N(0,1)*std in place, Philox4x32-7 keyed by (seed, ray_id_base + ray, sample). */
 int nerf_add_density_noise(float* sigma, int S, int64_t B, float std, uint64_t seed,
                            int64_t ray_id_base, void* stream);
 

@@ -48,7 +48,11 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// ---- Philox4x32-10 (counter based; keyed by (seed), counter = (ray, sample)) ----
+// ---- Philox4x32-7 (counter based; keyed by (seed), counter = (ray, sample)) ----
+// Seven rounds: the Crush-resistant variant of Salmon et al. (Random123, SC'11; ten rounds are their safety-margin
+// default).  Every round is two 32 x 32 -> 64 multiplies on the fma pipe, which is what bound the in-kernel-jitter sampler
+// at 0.50 of the HBM peak with ten; the streams are checked as distributions in tests/test_gpu_train_parity.py.
+#define NERF_PHILOX_ROUNDS 7
 __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
     uint32_t hi0 = __umulhi(M0, c[0]), lo0 = M0 * c[0];
@@ -60,7 +64,7 @@ __device__ __forceinline__ void philox4x32(uint64_t seed, uint64_t ctr_lo, uint3
     uint32_t c[4] = {(uint32_t)ctr_lo, (uint32_t)(ctr_lo >> 32), ctr_hi, 0u};
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll
-    for (int i = 0; i < 10; ++i) { philox_round(c, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+    for (int i = 0; i < NERF_PHILOX_ROUNDS; ++i) { philox_round(c, k0, k1); k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
     out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; out[3] = c[3];
 }
 // uniform in [0,1) with 24 random bits (same grid as torch.rand for fp32)

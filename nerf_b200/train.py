@@ -10,6 +10,74 @@ from . import ops
 from ._lib import check, lib, ptr, stream
 
 
+class HostBatchPipeline:
+    """Host -> device input pipeline for the training loop: batches arrive in PINNED host memory and are copied into
+    one of `depth` device buffers on a copy stream while the previous step computes (what a DataLoader with
+    pin_memory + non_blocking copies does for the reference's loop, train_conditional_nerf.py:100-104); the loss of
+    each step is read back into pinned memory on a second stream.  Every step still moves its own batch and its own
+    loss across PCIe; only the waiting overlaps.
+
+        pipe = HostBatchPipeline(device, like=host_batch)
+        pipe.submit(host_batches[0])
+        for i in range(n):
+            if i + 1 < n: pipe.submit(host_batches[i + 1])     # copy of the next batch runs under this step
+            o, d, target = pipe.get()                          # current stream waits for this batch's copy only
+            loss = trainer.step(o, d, target)
+            pipe.done(loss)                                    # frees the buffer; schedules the loss read-back
+        pipe.losses()                                          # pinned host tensor with the losses read back so far
+    """
+
+    def __init__(self, device, like, depth=2, max_losses=1 << 16):
+        self.bufs = [torch.empty(like.shape, dtype=like.dtype, device=device) for _ in range(depth)]
+        self.copied = [torch.cuda.Event() for _ in range(depth)]
+        self.freed = [torch.cuda.Event() for _ in range(depth)]
+        self.h2d, self.d2h = torch.cuda.Stream(device), torch.cuda.Stream(device)
+        self.host_losses = torch.zeros(max_losses).pin_memory()
+        self.stepped, self.loss_read = torch.cuda.Event(), torch.cuda.Event()
+        self.head = self.tail = self.n_losses = 0
+        self.pending = [False] * depth
+
+    def submit(self, host_batch):
+        k = self.head % len(self.bufs)
+        if self.pending[k]:
+            raise RuntimeError("HostBatchPipeline: more batches in flight than buffers")
+        with torch.cuda.stream(self.h2d):
+            if self.head >= len(self.bufs):
+                self.h2d.wait_event(self.freed[k])             # the step that read this buffer has been issued and finished
+            self.bufs[k].copy_(host_batch, non_blocking=True)
+            self.copied[k].record(self.h2d)
+        self.pending[k] = True
+        self.head += 1
+
+    def get(self):
+        k = self.tail % len(self.bufs)
+        if not self.pending[k]:
+            raise RuntimeError("HostBatchPipeline: get() without a submitted batch")
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self.copied[k])
+        if self.n_losses:
+            cur.wait_event(self.loss_read)                     # the trainer reuses ONE device loss buffer: the previous read-back
+        return tuple(self.bufs[k])                             # (long finished by now) precedes the step that overwrites it
+
+    def done(self, loss=None):
+        k = self.tail % len(self.bufs)
+        cur = torch.cuda.current_stream()
+        self.freed[k].record(cur)
+        self.pending[k] = False
+        self.tail += 1
+        if loss is not None:
+            self.stepped.record(cur)
+            with torch.cuda.stream(self.d2h):
+                self.d2h.wait_event(self.stepped)
+                self.host_losses[self.n_losses % self.host_losses.numel():][:1].copy_(loss.detach().reshape(1), non_blocking=True)
+                self.loss_read.record(self.d2h)
+            self.n_losses += 1
+
+    def losses(self):
+        self.d2h.synchronize()
+        return self.host_losses[:min(self.n_losses, self.host_losses.numel())]
+
+
 class Trainer:
     def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, near=2.0, far=6.0,
                  num_samples=64, density_noise_std=1.0, randomly_sample=True, seed=0,
