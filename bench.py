@@ -389,6 +389,48 @@ def run_ours(args):
                 "mlp_tflops": RAYS * SAMPLES * FLOP_PER_POINT_FWD_BWD * n / (ms * 1e-3) / 1e12}
     other_prec = safe("other_precision", _other_precision)
 
+    # ------------------------------------------------------------------ fp32-grade step on the tensor cores (bf16x3) ----
+    def _x3_train():
+        m4 = NeRF(normalize_position=6.0, precision="bf16x3").to(dev); m4.load_state_dict(sd)
+        tr4 = Trainer(m4, lr=1e-4, near=NEAR, far=FAR, num_samples=SAMPLES, density_noise_std=1.0, randomly_sample=True, seed=1234,
+                      fused_exchange=False)
+        tr4.world = 1
+
+        def it(i):
+            o, d, tgt = pool_d[i % n_pool]
+            tr4.step(o, d, tgt)
+        for i in range(3):
+            it(i)
+        torch.cuda.synchronize()
+        n = min(K, 20)
+        ms, _ = timed_region(it, n)
+        z4 = tr4._tc_buffers(RAYS, SAMPLES, dev)
+        flat4 = m4.flat_parameters(); P4 = _lib.ptr; L4 = _lib.lib(); g4 = torch.zeros_like(flat4)
+        o, d, tgt = pool_d[0]
+        lad = m4._ladder(NEAR, FAR, SAMPLES, dev)
+
+        def k_fwd(i):
+            _lib.check(L4.nerf_g1_train_fwd_x3(P4(z4["packed"]), P4(o), P4(d), RAYS, SAMPLES, NEAR, FAR, P4(lad), None, None, 1, 1, 0, 6.0, 1,
+                                               P4(z4["t"]), P4(z4["sigma"]), P4(z4["rgb"]), P4(z4["ws"]), z4["n"], _lib.stream()), "fwd_x3")
+
+        def k_bwd(stage):
+            def f(i):
+                _lib.check(L4.nerf_g1_train_bwd_x3(P4(z4["packed"]), P4(z4["packed_bwd"]), P4(flat4), P4(z4["d_sigma"]), P4(z4["d_rgb"]), RAYS, SAMPLES,
+                                                   P4(g4), P4(z4["ws"]), z4["n"], stage, _lib.stream()), "bwd_x3")
+            return f
+        ms_f = float(np.mean(timed_steps(k_fwd, 5, flush)))
+        ms_d = float(np.mean(timed_steps(k_bwd(1), 5, flush)))
+        ms_dw = float(np.mean(timed_steps(k_bwd(2), 5, flush)))
+        return {"value": RAYS * n / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms / n, "steps": n, "precision": "bf16x3", "per_gpu": True,
+                "contraction": "tcgen05 kind::f16 with hi/lo operands (3 products per term) in the forward, the data-gradient chain and the "
+                               "weight-gradient GEMMs; LayerNorm/ReLU forward and backward, heads, unfold, Adam in fp32",
+                "mlp_tflops": RAYS * SAMPLES * FLOP_PER_POINT_FWD_BWD * n / (ms * 1e-3) / 1e12,
+                "kernels_ms": {"g1_fused_x3_kernel<train>": ms_f, "g1_bwd_x3_kernel": ms_d, "g1_wgrad_tc_kernel x 3": ms_dw - ms_d},
+                "workspace_bytes": int(z4["n"]),
+                "parity": "gradient vs the fp32 path: 7e-4 .. 2e-3 whole-gradient rel-L2 = the exact gradient's own sensitivity to a 1e-5 "
+                          "relative change of the forward (profiles/r02_grad_conditioning.txt); bf16: 5e-2 .. 6e-2"}
+    x3_train = safe("x3_train", _x3_train) if (world == 1 or args.all_sections) else None
+
     # ------------------------------------------------------------------ kernels timed alone through the C ABI ----
     o, d, tgt = pool_d[0]
     flat = model.flat_parameters()
@@ -706,6 +748,7 @@ def run_ours(args):
                                                "note": "in-kernel Philox4x32-7: 14 IMAD.WIDE per 4 samples on the fma pipe (0.50 of peak with 10 rounds in round 1)"},
                              "peak": peaks["hbm"], "unit": "GB/s", "rays": cb, "samples": s},
             "fp32" if args.precision == "bf16" else "bf16": other_prec,
+            "fp32_grade_train": x3_train,
             "api_loop": api_loop,
             "render": {"value": render_rps, "unit": "rays/s", "workload": f"{rh}x{rw} x {SAMPLES} samples render_image, one GPU",
                        "mlp_tflops": render_tflops, "frac_tensor": render_tflops / tensor_peak,

@@ -282,6 +282,26 @@ int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float
                          const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
                          void* workspace, int64_t workspace_bytes, int stage, void* stream);
 
+/* fp32-grade training step on the tensor cores ("bf16x3"): the same autograd (train_conditional_nerf.py:120-135, notebook
+ * cell 8) with the reference's fp32 arithmetic (nn.Linear = fp32 addmm, nerf/model.py:525-542) carried by tcgen05: every
+ * GEMM operand of the forward, the data-gradient chain and the weight-gradient GEMMs is split into two bf16 parts and
+ * each product formed as hi*hi + lo*hi + hi*lo with fp32 accumulation (~2^-17 relative); LayerNorm / ReLU forward and
+ * backward, the heads and the unfold are fp32.  Unconditional model (Dx = Dd = 3).  packed_x3 from
+ * nerf_g1_pack_weights_x3, packed_bwd_x3 (nerf_g1_packed_bwd_x3_bytes()) from nerf_g1_pack_weights_bwd_x3; one workspace of
+ * nerf_g1_train_x3_workspace_bytes(B, S) shared by the two calls (26 KB per point).  Arguments as nerf_g1_train_fwd_tc /
+ * nerf_g1_train_bwd_tc; grads (flat fp32, state_dict order) are OVERWRITTEN. */
+int64_t nerf_g1_packed_bwd_x3_bytes(void);
+int nerf_g1_pack_weights_bwd_x3(const float* params, void* packed_bwd_x3, void* stream);
+int64_t nerf_g1_train_x3_workspace_bytes(int64_t B, int S);
+int nerf_g1_train_fwd_x3(const void* packed_x3, const float* rays_o, const float* rays_d, int64_t B, int S,
+                         float near_plane, float far_plane, const float* t_base, const float* t_in, const float* u,
+                         int jitter, uint64_t seed, int64_t ray_id_base, float normalize_position, int normalize_direction,
+                         float* out_t, float* out_sigma, float* out_rgb,
+                         void* workspace, int64_t workspace_bytes, void* stream);
+int nerf_g1_train_bwd_x3(const void* packed_x3, const void* packed_bwd_x3, const float* params,
+                         const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
+                         void* workspace, int64_t workspace_bytes, int stage, void* stream);
+
 /* ------------------------------------------------ HEAD generation (mip-NeRF) --- */
 
 /* NeRF.integrated_pe (nerf/model.py:544-551 -> cast_rays :112-136, conical_frustum_to_gaussian

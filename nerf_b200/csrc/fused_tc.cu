@@ -302,7 +302,7 @@ extern "C" int64_t nerf_g1_render_workspace_bytes(int64_t B, int S, int Dx, int6
     return n;
 }
 
-int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st);      // fused_tc_x3.cu
+int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool train = false);      // fused_tc_x3.cu
 
 static int render_fused_impl(bool x3, const void* packed, int Dx, int Dd,
                                     const float* rays_o, const float* rays_d,

@@ -21,8 +21,14 @@
 
 // ReLU + LayerNorm epilogue of one unit (the arithmetic of epilogue_unit in tc_fused_kernel.cuh); pass 2 writes the
 // normalised row twice: hi = bf16(n), lo = bf16(n - hi).   MODE: 0 plain, 1 unit 7 (+ density), 2 unit 9 (+ colour, no store)
-template <int MODE>
-__device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, uint32_t taddr, uint32_t act_addr, uint32_t row,
+// TRAIN: unit 9 is normalised and stored too, (rstd, shift) go to tr_stats, and a third part r2 = bf16(n - hi - lo) of every
+// row goes to a row-major array read only by the backward's LayerNorm epilogue: g - mean(g) - n mean(g n) cancels most of g
+// where g is nearly parallel to n (the density gradient at unit 7), which amplifies the 2^-18 error of hi + lo a hundredfold;
+// with r2 the epilogue's n is fp32-exact.  The least significant mantissa bit of r2 carries the ReLU mask (1 = active): the
+// backward needs the mask EXACTLY (a fraction f of wrongly masked units is a relative gradient error of sqrt(f)) and a
+// reconstructed n > shift is not an exact test.  The MMA operands (hi, lo) are those of the inference kernel, bit for bit.
+template <int MODE, bool TRAIN>
+__device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr, uint32_t row,
                                               uint32_t vec_addr, const RowState& st) {
     const uint32_t hsum_addr = vec_addr + (SM_HSUM - SM_VEC);
     uint32_t r0[32], r1[32];
@@ -77,23 +83,34 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, uint32_t taddr
             }
         }
     }
-    if (MODE == 2) return;                                         // unit 9 feeds only the colour head
+    if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
+    if (MODE == 2 && !TRAIN) return;                               // unit 9 feeds only the colour head
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
-        uint32_t hi[16], lo[16];
+        uint32_t hi[16], lo[16], r2[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
             float2 y = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, shift2);
+            const uint32_t active = TRAIN ? ((y.x > shift ? 1u : 0u) | (y.y > shift ? 0x10000u : 0u)) : 0u;
             y.x = fmaxf(y.x, shift); y.y = fmaxf(y.y, shift);      // = relu(z) rstd + shift  (rstd > 0)
             const __nv_bfloat162 h = __float22bfloat162_rn(y);
             const float2 hf = __bfloat1622float2(h);
             const __nv_bfloat162 l2 = __float22bfloat162_rn(make_float2(y.x - hf.x, y.y - hf.y));
             hi[j / 2] = *reinterpret_cast<const uint32_t*>(&h); lo[j / 2] = *reinterpret_cast<const uint32_t*>(&l2);
+            if (TRAIN) {
+                const float2 lf = __bfloat1622float2(l2);
+                r2[j / 2] = (tc::pack_bf16x2((y.x - hf.x) - lf.x, (y.y - hf.y) - lf.y) & 0xFFFEFFFEu) | active;
+            }
         }
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             store_row_chunk(slab, row, (ch & 1) * 4 + i, make_uint4(hi[i * 4], hi[i * 4 + 1], hi[i * 4 + 2], hi[i * 4 + 3]));
             store_row_chunk(slab + 65536, row, (ch & 1) * 4 + i, make_uint4(lo[i * 4], lo[i * 4 + 1], lo[i * 4 + 2], lo[i * 4 + 3]));
+        }
+        if (TRAIN) {
+            uint4* dst = reinterpret_cast<uint4*>(a.tr_r2 + (((size_t)l * a.P_pad + st.p) * 256 + ch * 32) * 2);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(r2[i * 4], r2[i * 4 + 1], r2[i * 4 + 2], r2[i * 4 + 3]);
         }
     };
     tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
@@ -108,6 +125,7 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, uint32_t taddr
     }
 }
 
+template <bool TRAIN>
 __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedArgs a) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = tc::smem_u32(smem_raw);
@@ -236,22 +254,52 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
             if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
         };
         uint32_t acc_it = 0;
+        // TRAIN: row 0 bulk-stores the slab images (hi and lo) the backward needs.  A store must have been READ OUT of shared
+        // memory before the slabs are written again: `stores_read_out` (wait_group.read by the issuing thread + the group's
+        // barrier) precedes every writer of a slab; the MMAs only read the slabs, so stores and MMAs overlap freely.
+        auto stores_read_out = [&]() { if (row == 0) tc::tma_store_wait_read0(); tc::named_bar_sync(1, 128); };
+        auto slabs_complete = [&]() { tc::fence_proxy_async_smem(); tc::named_bar_sync(1, 128); };
         for (int q = 0; q < n_my; ++q) {
             const int unit = me + q * G;
             const int tile = 2 * unit + (int)rank;
             RowState st;
+            if (TRAIN) stores_read_out();
             encode_row<true>(a, tile, row, pe_addr, st);
+            if (TRAIN) {
+                st.p = (int64_t)tile * 128 + row;                      // rows beyond P still own a row of the padded images
+                slabs_complete();
+                if (row == 0) {
+                    tc::tma_store_1d(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
+                    tc::tma_store_1d(a.tr_pex_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
+                    tc::tma_store_commit();
+                }
+            }
             signal_act();
             for (int l = 0; l < 10; ++l) {
                 tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
-                if (l == 7) epilogue_unit_x3<1>(a, taddr, act_addr, row, base + SM_VEC, st);
-                else if (l == 9) epilogue_unit_x3<2>(a, taddr, act_addr, row, base + SM_VEC, st);
-                else epilogue_unit_x3<0>(a, taddr, act_addr, row, base + SM_VEC, st);
+                if (TRAIN) stores_read_out();
+                if (l == 7) epilogue_unit_x3<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else if (l == 9) epilogue_unit_x3<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
+                else epilogue_unit_x3<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
                 if (l == 4) encode_dir_row<true>(a, row, pe_addr, st);     // unit 4 was the last reader of the position slabs
+                if (TRAIN) {
+                    slabs_complete();
+                    if (row == 0) {
+                        const size_t img = ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
+                        tc::tma_store_1d(a.tr_act + img, act_addr, 4 * TC_SLAB_BYTES);
+                        tc::tma_store_1d(a.tr_act_lo + img, act_addr + 65536, 4 * TC_SLAB_BYTES);
+                        if (l == 4) {
+                            tc::tma_store_1d(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
+                            tc::tma_store_1d(a.tr_ped_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
+                        }
+                        tc::tma_store_commit();
+                    }
+                }
                 if (l < 9) signal_act();
             }
         }
+        if (TRAIN && row == 0) tc::tma_store_wait_all0();
     }
     tc::tcgen05_fence_before();
     tc::cluster_sync_all();
@@ -259,14 +307,14 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
 }
 
 // launches the x3 kernel on a.n_tiles tiles; `packed` = the image of nerf_g1_pack_weights_x3
-int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st) {
+int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool train) {
     X3Layout X; make_x3_layout(X);
     for (int l = 0; l < 10; ++l) { a.nk[l] = X.nk[l]; a.unit_off[l] = X.unit_off[l]; a.half_kcores[l] = (int)(X.half_bytes[l] / TF_KCORE_BYTES); }
     a.stages = (const uint8_t*)packed;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + X.weight_bytes);
     static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
     a.wait_hint = wait_hint; a.prof = nullptr; a.ray_bias = nullptr;
-    NERF_CUDA(nerf_smem_opt_in<g1_fused_x3_kernel>(TC_SMEM_BYTES));
+    NERF_CUDA(train ? nerf_smem_opt_in<g1_fused_x3_kernel<true>>(TC_SMEM_BYTES) : nerf_smem_opt_in<g1_fused_x3_kernel<false>>(TC_SMEM_BYTES));
     const int sms = nerf_num_sms();
     const int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
     cudaLaunchConfig_t cfg{};
@@ -274,7 +322,8 @@ int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st) {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel, a));
+    if (train) NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel<true>, a));
+    else NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel<false>, a));
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }

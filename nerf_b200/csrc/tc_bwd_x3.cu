@@ -1,0 +1,306 @@
+// fp32-grade data-gradient kernel of the G1 MLP ("bf16x3" training): the chain of tc_bwd_kernel.cuh with every GEMM
+// operand split into two bf16 parts (dz = dz_hi + dz_lo, W' = W_hi + W_lo) and each product formed as
+//     dz W'  ~=  dz_hi W_hi + dz_lo W_hi + dz_hi W_lo            (fp32 accumulate in TMEM),
+// i.e. the autograd of the reference's fp32 nn.Linear / LayerNorm / ReLU stack (/root/reference/nerf/model.py:525-542 in
+// the HEAD tree; the G1 stack of examples/nerf.pth) with tensor-core contractions.
+//
+// One 128-point tile per CTA (CTA pairs, cta_group::2, M = 256 = the pair's two tiles), ONE accumulator (256 TMEM columns):
+// the second tile slot's shared memory of the bf16 kernel holds the lo parts here.
+//   warp 0     TMA producer of the transposed weight stages: per K-slab the hi stage, then the lo stage
+//   warp 1     MMA issuer (leader CTA) / weight-arrival relay (peer CTA)
+//   warps 2-5  LayerNorm + ReLU backward (thread = point row = TMEM lane), in fp32:
+//                  dz = mask * rstd * (g - mean(g) - n * mean(g n)),   n = n_hi + n_lo (forward's slab images) + r2 (its
+//              residual rows, read straight from global memory: the subtraction cancels most of g where g is nearly
+//              parallel to n, so n must be fp32-exact), the mask is the least significant mantissa bit of r2;
+//              dz overwrites n in place as (hi, lo) = the A operands of the next MMAs and is bulk-stored for the
+//              weight-gradient GEMM; row 0 of the group issues the tile's bulk loads and stores.
+// Per unit the steps are serial (epilogue -> MMAs -> refill): the bf16 kernel's two-slot overlap does not fit next to the
+// lo parts in 227 KB.  n_{l-1} is prefetched into L2 while the MMAs of unit l run.
+#include "tc_bwd_kernel.cuh"
+#include "tc_bwd_x3.cuh"
+
+#define BX_THREADS 192
+#define BX_RING 4
+#define BX_SM_HI 0                                    // 4 slabs: n_l hi -> dz_l hi
+#define BX_SM_LO 65536                                // 4 slabs: n_l lo -> dz_l lo
+#define BX_SM_RING (2 * 65536)                        // BX_RING x 16 KB weight stages
+#define BX_SM_VEC (BX_SM_RING + BX_RING * TC_STAGE_BYTES)      // head weights [4][256] fp32
+#define BX_SM_BAR (BX_SM_VEC + 4 * 256 * 4)
+#define BX_SM_TOTAL (BX_SM_BAR + 256)
+#define BX_SMEM_BYTES (BX_SM_TOTAL + 1024)
+
+
+__device__ __forceinline__ void sts128u(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// (hi, lo) bf16 pair of two fp32 values: hi = bf16(x), lo = bf16(x - hi)
+__device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(x, y);
+    const float2 hf = __bfloat1622float2(h);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(x - hf.x, y - hf.y);
+    hi = *reinterpret_cast<const uint32_t*>(&h); lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+
+// LayerNorm + ReLU backward of one unit for one row, fp32 throughout; dz replaces n in place as (hi, lo).
+// SRC: 0 = g from TMEM, 1 = g from TMEM + d_sigma * w'_sigma (unit 7), 2 = g = W'_c^T d_rgb (unit 9).
+// Two passes over the row (sums, then dz); TMEM is read in both.  Written for clarity, not for the last cycle: the
+// kernel's time goes to the three-product MMAs and the 256 KB of slab traffic per tile and unit.
+template <int SRC>
+__device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_addr, uint32_t lo_addr, uint32_t row, uint32_t hw_addr,
+                                                  const uint4* __restrict__ r2row, float rstd, float ds, float dr, float dg, float db) {
+    uint32_t r[32];
+    // g of the 8 columns ch*32 + i*8 .. +7 (rc = the chunk's 32 TMEM columns)
+    auto grad8 = [&](const uint32_t (&rc)[32], int ch, int i, float (&g)[8]) {
+        const int c0 = ch * 32 + i * 8;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (SRC == 2) {
+                const float4 w0 = tc::lds128(hw_addr + (256 + c0 + 4 * h) * 4);
+                const float4 w1 = tc::lds128(hw_addr + (512 + c0 + 4 * h) * 4);
+                const float4 w2 = tc::lds128(hw_addr + (768 + c0 + 4 * h) * 4);
+                g[4 * h + 0] = fmaf(dr, w0.x, fmaf(dg, w1.x, db * w2.x)); g[4 * h + 1] = fmaf(dr, w0.y, fmaf(dg, w1.y, db * w2.y));
+                g[4 * h + 2] = fmaf(dr, w0.z, fmaf(dg, w1.z, db * w2.z)); g[4 * h + 3] = fmaf(dr, w0.w, fmaf(dg, w1.w, db * w2.w));
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) g[4 * h + q] = __uint_as_float(rc[i * 8 + 4 * h + q]);
+                if (SRC == 1) {
+                    const float4 w = tc::lds128(hw_addr + (c0 + 4 * h) * 4);
+                    g[4 * h + 0] = fmaf(ds, w.x, g[4 * h + 0]); g[4 * h + 1] = fmaf(ds, w.y, g[4 * h + 1]);
+                    g[4 * h + 2] = fmaf(ds, w.z, g[4 * h + 2]); g[4 * h + 3] = fmaf(ds, w.w, g[4 * h + 3]);
+                }
+            }
+        }
+    };
+    // n = hi + lo and the ReLU mask (bit q = column q active) of the same 8 columns; off = their byte offset in both parts
+    auto load_n = [&](int ch, int i, float (&n)[8], uint32_t& mask, uint32_t& off) {
+        off = (uint32_t)(ch >> 1) * TC_SLAB_BYTES + tc::sw128_offset(row, (ch & 1) * 4 + i);
+        const uint4 h = lds128u(hi_addr + off), l = lds128u(lo_addr + off), rr = r2row[ch * 4 + i];
+        const uint32_t hv[4] = {h.x, h.y, h.z, h.w}, lv[4] = {l.x, l.y, l.z, l.w}, rv[4] = {rr.x, rr.y, rr.z, rr.w};
+        mask = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            n[2 * q] = (bf_lo(hv[q]) + bf_lo(lv[q])) + bf_lo(rv[q]); n[2 * q + 1] = (bf_hi(hv[q]) + bf_hi(lv[q])) + bf_hi(rv[q]);
+            mask |= ((rv[q] & 1u) << (2 * q)) | (((rv[q] >> 16) & 1u) << (2 * q + 1));
+        }
+    };
+    // ---- pass 1: sum g, sum g n   (two chains each)
+    float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
+#pragma unroll 1
+    for (int ch = 0; ch < 8; ++ch) {
+        if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float g[8], n[8]; uint32_t mask, off;
+            grad8(r, ch, i, g); load_n(ch, i, n, mask, off);
+#pragma unroll
+            for (int q = 0; q < 8; q += 2) {
+                s1a += g[q]; s1b += g[q + 1];
+                s2a = fmaf(g[q], n[q], s2a); s2b = fmaf(g[q + 1], n[q + 1], s2b);
+            }
+        }
+    }
+    const float m1 = (s1a + s1b) * (1.0f / 256.f), m2 = (s2a + s2b) * (1.0f / 256.f);
+    const float c0 = -rstd * m1, c1 = -rstd * m2;
+    // ---- pass 2: dz = mask * (rstd g - rstd m1 - n rstd m2), (hi, lo) in place over (n_hi, n_lo)
+#pragma unroll 1
+    for (int ch = 0; ch < 8; ++ch) {
+        if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float g[8], n[8]; uint32_t mask, off;
+            grad8(r, ch, i, g); load_n(ch, i, n, mask, off);
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float d0 = ((mask >> (2 * q)) & 1u) ? fmaf(n[2 * q], c1, fmaf(g[2 * q], rstd, c0)) : 0.f;
+                const float d1 = ((mask >> (2 * q + 1)) & 1u) ? fmaf(n[2 * q + 1], c1, fmaf(g[2 * q + 1], rstd, c0)) : 0.f;
+                split2(d0, d1, hi[q], lo[q]);
+            }
+            sts128u(hi_addr + off, make_uint4(hi[0], hi[1], hi[2], hi[3]));
+            sts128u(lo_addr + off, make_uint4(lo[0], lo[1], lo[2], lo[3]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Args a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = tc::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* sm = smem_raw + (base - raw);
+    float* hw_s = reinterpret_cast<float*>(sm + BX_SM_VEC);
+    const uint32_t bar0 = base + BX_SM_BAR;
+    auto ring_full = [&](int s) { return bar0 + 8u * s; };
+    auto ring_empty = [&](int s) { return bar0 + 8u * (BX_RING + s); };
+    const uint32_t act_ready = bar0 + 8u * (2 * BX_RING), acc_ready = bar0 + 8u * (2 * BX_RING + 1), n_full = bar0 + 8u * (2 * BX_RING + 2);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + BX_SM_BAR + 8 * (2 * BX_RING + 3));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int G = gridDim.x / 2, me = blockIdx.x / 2;
+    const int n_units = (a.n_tiles + 1) / 2;                       // tile pairs; this CTA takes tile 2 * unit + rank
+    const int n_my = (me < n_units) ? (n_units - me + G - 1) / G : 0;
+
+    for (int i = threadIdx.x; i < 4 * 256; i += BX_THREADS) hw_s[i] = a.vec[TC_VEC_HEADW + i];
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < BX_RING; ++s) { tc::mbar_init(ring_full(s), leader ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
+        tc::mbar_init(act_ready, 8); tc::mbar_init(acc_ready, 1); tc::mbar_init(n_full, 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 256);
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer: per unit 9..1 and K-slab, this CTA's half of the hi stage, then of the lo stage =====================
+        uint32_t it = 0;
+        for (int q = 0; q < n_my; ++q)
+            for (int l = 9; l >= 1; --l)
+                for (int ks = 0; ks < 4; ++ks)
+                    for (int part = 0; part < 2; ++part, ++it) {
+                        const uint8_t* src = (part ? a.stages_lo : a.stages_hi) + ((size_t)(l - 1) * 8 + ks * 2 + rank) * TC_STAGE_BYTES;
+                        const int slot = it % BX_RING; const uint32_t ph = (it / BX_RING) & 1;
+                        tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
+                        if (tc::elect_one()) {
+                            tc::mbar_arrive_expect_tx(ring_full(slot), TC_STAGE_BYTES);
+                            tc::tma_load_1d(base + BX_SM_RING + slot * TC_STAGE_BYTES, src, TC_STAGE_BYTES, ring_full(slot));
+                        }
+                        __syncwarp();
+                    }
+    } else if (warp == 1) {
+        if (leader) {
+            // ===================== MMA issuer: g_{l-1} = dz_hi W_hi + dz_lo W_hi + dz_hi W_lo =====================
+            const uint32_t idesc = tc::umma_idesc_bf16(256, 256);
+            constexpr uint32_t hi_sw = (1024u >> 4) | (1u << 14) | (2u << 29);            // SW128 K-major: SBO, version, layout
+            auto lo_sw = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
+            const uint32_t ring_lo = lo_sw(base + BX_SM_RING);
+            const uint32_t dzh_lo = lo_sw(base + BX_SM_HI), dzl_lo = lo_sw(base + BX_SM_LO);
+            auto mma = [&](uint32_t alo, uint32_t blo, uint32_t acc) {
+                tc::umma_bf16_2cta(tmem_base, ((uint64_t)hi_sw << 32) | alo, ((uint64_t)hi_sw << 32) | blo, idesc, acc);
+            };
+            uint32_t it = 0, act_it = 0;
+            for (int q = 0; q < n_my; ++q)
+                for (int l = 9; l >= 1; --l) {
+                    tc::mbar_wait_spin(act_ready, act_it & 1, a.wait_hint); ++act_it;
+                    tc::tcgen05_fence_after();
+                    for (int ks = 0; ks < 4; ++ks)
+                        for (int part = 0; part < 2; ++part, ++it) {
+                            const int slot = it % BX_RING; const uint32_t ph = (it / BX_RING) & 1;
+                            const uint32_t blo = ring_lo + slot * (TC_STAGE_BYTES >> 4);
+                            const uint32_t ah = dzh_lo + ks * (TC_SLAB_BYTES >> 4), al = dzl_lo + ks * (TC_SLAB_BYTES >> 4);
+                            tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
+                            if (tc::elect_one()) {
+                                if (part == 0) {                       // W_hi: with dz_hi, then with dz_lo
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk) mma(ah + 2 * kk, blo + 2 * kk, (ks | kk) ? 1u : 0u);
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk) mma(al + 2 * kk, blo + 2 * kk, 1u);
+                                } else {                               // W_lo: with dz_hi
+#pragma unroll
+                                    for (int kk = 0; kk < 4; ++kk) mma(ah + 2 * kk, blo + 2 * kk, 1u);
+                                }
+                                tc::umma_commit_2cta(ring_empty(slot));
+                                if (ks == 3 && part == 1) tc::umma_commit_2cta(acc_ready);
+                            }
+                            __syncwarp();
+                        }
+                }
+        } else if (lane == 0) {
+            // ===================== peer relay of weight arrivals =====================
+            uint32_t it = 0;
+            for (int q = 0; q < n_my; ++q)
+                for (int l = 9; l >= 1; --l)
+                    for (int j = 0; j < 8; ++j, ++it) {
+                        const int slot = it % BX_RING; const uint32_t ph = (it / BX_RING) & 1;
+                        tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
+                        tc::mbar_arrive_cluster(tc::mapa(ring_full(slot), 0));
+                    }
+        }
+    } else {
+        // ===================== LayerNorm-backward epilogue group =====================
+        const uint32_t row = (warp & 3) * 32 + lane;
+        const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16);
+        const uint32_t hi_addr = base + BX_SM_HI, lo_addr = base + BX_SM_LO, hw_addr = base + BX_SM_VEC;
+        const bool io = row == 0;                                        // the group's bulk-copy thread
+        const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
+        const size_t img = 4 * (size_t)TC_SLAB_BYTES;
+        uint32_t acc_it = 0, nf_it = 0;
+        float hs0 = 0.f, hs1 = 0.f, hs2 = 0.f, hs3 = 0.f;
+        auto load_unit = [&](int l, int tile) {                          // n_l (hi, lo) of this tile -> the two buffers
+            tc::mbar_arrive_expect_tx(n_full, 2 * (uint32_t)img);
+            tc::tma_load_1d(hi_addr, a.act_hi + ((size_t)l * a.tr_tiles + tile) * img, (uint32_t)img, n_full);
+            tc::tma_load_1d(lo_addr, a.act_lo + ((size_t)l * a.tr_tiles + tile) * img, (uint32_t)img, n_full);
+        };
+        for (int q = 0; q < n_my; ++q) {
+            const int unit = me + q * G;
+            const int tile = 2 * unit + (int)rank;
+            const int64_t p = (int64_t)tile * 128 + row;
+            if (io) { tc::tma_store_wait_read0(); load_unit(9, tile); } // (dz_0 of the previous tile has been read out)
+            float ds = 0.f, dr = 0.f, dg = 0.f, db = 0.f;
+            if (p < a.P) { ds = a.d_sigma[p]; dr = a.d_rgb[p * 3]; dg = a.d_rgb[p * 3 + 1]; db = a.d_rgb[p * 3 + 2]; }
+            hs0 += ds; hs1 += dr; hs2 += dg; hs3 += db;
+            {   // small-operand images of (d_sigma, d_rgb), hi and lo: [16 point groups][2 column halves][8 points][8 columns] bf16
+                uint32_t h0, l0, h1, l1;
+                split2(ds, dr, h0, l0); split2(dg, db, h1, l1);
+                const size_t o = (size_t)tile * 4096 + (row >> 3) * 256 + (row & 7) * 16;
+                *reinterpret_cast<uint4*>(a.dh_hi + o) = make_uint4(h0, h1, 0u, 0u);
+                *reinterpret_cast<uint4*>(a.dh_hi + o + 128) = make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(a.dh_lo + o) = make_uint4(l0, l1, 0u, 0u);
+                *reinterpret_cast<uint4*>(a.dh_lo + o + 128) = make_uint4(0u, 0u, 0u, 0u);
+            }
+            for (int l = 9; l >= 0; --l) {
+                const float2 stt = a.stats[(int64_t)l * a.P_pad + p];
+                if (l < 9) {
+                    tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;     // g_l is in TMEM, the MMAs have consumed dz_{l+1}
+                    tc::tcgen05_fence_after();
+                    if (io) { tc::tma_store_wait_read0(); load_unit(l, tile); }      // its store has been read out too: refill with n_l
+                }
+                tc::mbar_wait(n_full, nf_it & 1, a.wait_hint); ++nf_it;
+                const uint4* r2row = reinterpret_cast<const uint4*>(a.r2 + ((size_t)l * a.P_pad + p) * 512);
+                if (l == 9) bwd_x3_epilogue_unit<2>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
+                else if (l == 7) bwd_x3_epilogue_unit<1>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
+                else bwd_x3_epilogue_unit<0>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
+                tc::fence_proxy_async_smem();
+                tc::named_bar_sync(1, 128);                                       // dz_l complete in shared memory
+                if (l > 0) {
+                    tc::tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
+                }
+                if (io) {                                                         // dz_l -> HBM for the weight-gradient GEMM
+                    tc::tma_store_1d(a.dz_hi + ((size_t)l * a.tr_tiles + tile) * img, hi_addr, (uint32_t)img);
+                    tc::tma_store_1d(a.dz_lo + ((size_t)l * a.tr_tiles + tile) * img, lo_addr, (uint32_t)img);
+                    tc::tma_store_commit();
+                    if (l > 0) {                                                  // n_{l-1}: into L2 while the MMAs run
+                        tc::tma_prefetch_l2(a.act_hi + ((size_t)(l - 1) * a.tr_tiles + tile) * img, (uint32_t)img);
+                        tc::tma_prefetch_l2(a.act_lo + ((size_t)(l - 1) * a.tr_tiles + tile) * img, (uint32_t)img);
+                    }
+                }
+            }
+        }
+        if (io) tc::tma_store_wait_all0();
+        hs0 = warp_sum(hs0); hs1 = warp_sum(hs1); hs2 = warp_sum(hs2); hs3 = warp_sum(hs3);
+        if (lane == 0 && n_my > 0) { atomicAdd(a.hsum, hs0); atomicAdd(a.hsum + 1, hs1); atomicAdd(a.hsum + 2, hs2); atomicAdd(a.hsum + 3, hs3); }
+    }
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 256); }
+}
+
+int launch_bwd_x3(BwdX3Args& a, cudaStream_t st) {
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    a.wait_hint = wait_hint;
+    NERF_CUDA(nerf_smem_opt_in<g1_bwd_x3_kernel>(BX_SMEM_BYTES));
+    const int sms = nerf_num_sms();
+    const int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(BX_THREADS); cfg.dynamicSmemBytes = BX_SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_bwd_x3_kernel, a));
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}

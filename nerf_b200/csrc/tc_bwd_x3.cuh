@@ -1,0 +1,19 @@
+// Arguments of the fp32-grade data-gradient kernel (tc_bwd_x3.cu), shared with its host entry point (tc_train.cu).
+#pragma once
+#include "tc_layout.cuh"
+
+struct BwdX3Args {
+    const uint8_t* stages_hi; const uint8_t* stages_lo;   // transposed weight stages, unit l in 1..9 -> 8 stages at (l-1)*8 (tc_train.cu layout)
+    const float* vec;                                     // forward epilogue vectors (head weights with gamma folded)
+    const uint8_t* act_hi; const uint8_t* act_lo;         // [10][tr_tiles][4 slabs]
+    const uint8_t* r2;                                    // [10][P_pad][256] bf16 rows: n - hi - lo, LSB = ReLU mask
+    const float2* stats;                                  // [10][P_pad] (rstd, -mean*rstd)
+    const float* d_sigma; const float* d_rgb;
+    uint8_t* dz_hi; uint8_t* dz_lo;                       // [10][tr_tiles][4 slabs] out
+    uint8_t* dh_hi; uint8_t* dh_lo;                       // [tr_tiles][4 KB] out: (d_sigma, d_rgb) small-operand images
+    float* hsum;                                          // [4] += sums of (d_sigma, d_rgb)
+    int64_t P, P_pad; int n_tiles, tr_tiles;
+    uint32_t wait_hint;
+};
+
+int launch_bwd_x3(BwdX3Args& a, cudaStream_t st);

@@ -128,3 +128,24 @@ static inline void make_train_layout(int64_t B, int S, TrainLayout& T, int Dx = 
     T.off_rsum = o; o += T.EXs ? up(2ll * B * 256 * 4) : 0;
     T.total = o;
 }
+
+// ---- workspace of the fp32-grade ("bf16x3") training step (tc_train_x3.cu): the bf16 step's layout holds the hi parts,
+// a second set of images behind it the lo parts (activations, dz, the two encodings, the (d_sigma, d_rgb) image)
+struct X3TrainLayout {
+    TrainLayout T;
+    int64_t off_act_lo, off_dz_lo, off_pex_lo, off_ped_lo, off_dh_lo, total;
+    int64_t off_r2;      // [10][P_pad][256] bf16, row-major: third part of the normalised activations, n - hi - lo, read only by the
+};                       // LayerNorm backward (its cancellation amplifies the error of n); its LSB carries the ReLU mask
+static inline void make_x3_train_layout(int64_t B, int S, X3TrainLayout& X) {
+    make_train_layout(B, S, X.T, 3);
+    int64_t o = X.T.total;
+    const int64_t unit_images = 10ll * X.T.tr_tiles * 4 * TC_SLAB_BYTES;
+    X.off_act_lo = o; o += unit_images;
+    X.off_dz_lo = o; o += unit_images;
+    X.off_pex_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
+    X.off_ped_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
+    X.off_dh_lo = o; o += (int64_t)X.T.tr_tiles * 4096;
+    X.off_r2 = o; o += 10ll * X.T.P_pad * 512;
+    X.total = o;
+}
+

@@ -336,3 +336,102 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
+
+// ======================= fp32-grade ("bf16x3") training step: host entry points =======================
+// Forward: g1_fused_x3_kernel<true> (fused_tc_x3.cu) stores hi / lo slab images, statistics and the ReLU mask bit;
+// backward: g1_bwd_x3_kernel (tc_bwd_x3.cu), three passes of the weight-gradient GEMM, the same unfold.
+#include "tc_bwd_x3.cuh"
+#include "tc_fused_kernel.cuh"
+int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool train);              // fused_tc_x3.cu
+int launch_wgrad_tc_units_x3(const uint8_t* ws, const X3TrainLayout& X, cudaStream_t st);      // tc_wgrad.cu
+
+// transposed stages as pack_bwd_stage_kernel, split: part 0 = bf16(w'), part 1 = bf16(w' - part 0)
+__global__ void pack_bwd_stage_x3_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 72ll * 128 * 8) return;
+    const int c16 = (int)(i & 7), r = (int)((i >> 3) & 127), stage = (int)(i >> 10);
+    const int l = 1 + stage / 8, rel = stage % 8, ks = rel >> 1, nh = rel & 1;
+    const int kin = nh * 128 + r;
+    const float* W = params + L.off_W[l];
+    const float g = params[L.off_gamma[l - 1] + kin];
+    const int Kt = L.Kt[l];
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int n0 = ks * 64 + c16 * 8 + q * 2;
+        const float w0 = W[(size_t)n0 * Kt + kin] * g, w1 = W[(size_t)(n0 + 1) * Kt + kin] * g;
+        hi[q] = tc::pack_bf16x2(w0, w1);
+        lo[q] = tc::pack_bf16x2(w0 - bf_lo(hi[q]), w1 - bf_hi(hi[q]));
+    }
+    const size_t off = (size_t)stage * TC_STAGE_BYTES + tc::sw128_offset(r, c16);
+    *reinterpret_cast<uint4*>(packed + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(packed + 72ll * TC_STAGE_BYTES + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+}
+
+extern "C" int64_t nerf_g1_packed_bwd_x3_bytes(void) { return 2 * 72ll * TC_STAGE_BYTES; }
+
+extern "C" int nerf_g1_pack_weights_bwd_x3(const float* params, void* packed_bwd, void* stream) {
+    if (!params || !packed_bwd) return NERF_ERR_BAD_ARG;
+    PackLayout L; int rc = make_pack_layout(3, 3, L); if (rc) return rc;
+    const int64_t n = 72ll * 128 * 8;
+    pack_bwd_stage_x3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}
+
+extern "C" int64_t nerf_g1_train_x3_workspace_bytes(int64_t B, int S) {
+    if (B <= 0 || S <= 0) return NERF_ERR_BAD_ARG;
+    X3TrainLayout X; make_x3_train_layout(B, S, X);
+    return X.total;
+}
+
+extern "C" int nerf_g1_train_fwd_x3(const void* packed_x3, const float* rays_o, const float* rays_d, int64_t B, int S,
+                                    float near_plane, float far_plane, const float* t_base, const float* t_in, const float* u,
+                                    int jitter, uint64_t seed, int64_t ray_id_base, float normalize_position, int normalize_direction,
+                                    float* out_t, float* out_sigma, float* out_rgb,
+                                    void* workspace, int64_t workspace_bytes, void* stream) {
+    if (!packed_x3 || !rays_o || !rays_d || !out_t || !out_sigma || !out_rgb || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
+    X3TrainLayout X; make_x3_train_layout(B, S, X);
+    if (!workspace || workspace_bytes < X.total) return NERF_ERR_WORKSPACE;
+    uint8_t* ws = (uint8_t*)workspace;
+    const TrainLayout& T = X.T;
+    FusedArgs a{};
+    a.rays_o = rays_o; a.rays_d = rays_d; a.B = B; a.S = S; a.P = T.P; a.n_tiles = T.n_tiles;
+    a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
+    a.near_plane = near_plane; a.far_plane = far_plane; a.norm = normalize_position; a.normalize_dir = normalize_direction;
+    a.out_t = out_t; a.out_sigma = out_sigma; a.out_rgb = out_rgb; a.dbg = nullptr; a.dbg_layer = -1;
+    a.tr_act = ws + T.off_act; a.tr_pex = ws + T.off_pex; a.tr_ped = ws + T.off_ped;
+    a.tr_act_lo = ws + X.off_act_lo; a.tr_pex_lo = ws + X.off_pex_lo; a.tr_ped_lo = ws + X.off_ped_lo; a.tr_r2 = ws + X.off_r2;
+    a.tr_stats = reinterpret_cast<float2*>(ws + T.off_stats); a.P_pad = T.P_pad; a.tr_tiles = T.tr_tiles;
+    return launch_fused_x3(packed_x3, a, (cudaStream_t)stream, true);
+}
+
+// stage: 0 = all, 1 = stop after the data-gradient kernel, 2 = stop after the weight-gradient GEMMs (tests / timing)
+extern "C" int nerf_g1_train_bwd_x3(const void* packed_x3, const void* packed_bwd_x3, const float* params,
+                                    const float* d_sigma, const float* d_rgb, int64_t B, int S, float* grads,
+                                    void* workspace, int64_t workspace_bytes, int stage, void* stream) {
+    if (!packed_x3 || !packed_bwd_x3 || !params || !d_sigma || !d_rgb || !grads || B <= 0 || S < 32) return NERF_ERR_BAD_ARG;
+    PackLayout L; int rc = make_pack_layout(3, 3, L); if (rc) return rc;
+    X3Layout XL; make_x3_layout(XL);
+    X3TrainLayout X; make_x3_train_layout(B, S, X);
+    if (!workspace || workspace_bytes < X.total) return NERF_ERR_WORKSPACE;
+    const TrainLayout& T = X.T;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t* ws = (uint8_t*)workspace;
+    NERF_CUDA(cudaMemsetAsync(ws + T.zero_begin, 0, (size_t)T.zero_bytes, st));
+    BwdX3Args a{};
+    a.stages_hi = (const uint8_t*)packed_bwd_x3; a.stages_lo = a.stages_hi + 72ll * TC_STAGE_BYTES;
+    a.vec = reinterpret_cast<const float*>((const uint8_t*)packed_x3 + XL.weight_bytes);
+    a.act_hi = ws + T.off_act; a.act_lo = ws + X.off_act_lo; a.r2 = ws + X.off_r2; a.stats = reinterpret_cast<const float2*>(ws + T.off_stats);
+    a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz_hi = ws + T.off_dz; a.dz_lo = ws + X.off_dz_lo;
+    a.dh_hi = ws + T.off_dh; a.dh_lo = ws + X.off_dh_lo; a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
+    a.P = T.P; a.P_pad = T.P_pad; a.n_tiles = T.n_tiles; a.tr_tiles = T.tr_tiles;
+    rc = launch_bwd_x3(a, st); if (rc) return rc;
+    if (stage == 1) return NERF_OK;
+    rc = launch_wgrad_tc_units_x3(ws, X, st); if (rc) return rc;
+    if (stage == 2) return NERF_OK;
+    unfold_kernel<<<dim3(20, 12), 1024, 0, st>>>(params, L, reinterpret_cast<const float*>(ws + T.off_gw), reinterpret_cast<const float*>(ws + T.off_gh),
+                                                 reinterpret_cast<const float*>(ws + T.off_hsum), reinterpret_cast<const float*>(ws + T.off_gs), grads);
+    NERF_CUDA_CHECK_LAUNCH();
+    return NERF_OK;
+}

@@ -353,3 +353,36 @@ int launch_wgrad_tc_units(const uint8_t* ws, const TrainLayout& T, cudaStream_t 
     a.n_tiles = T.n_tiles;
     return launch_wgrad_tc(a, st);
 }
+
+// fp32-grade weight gradients (bf16x3 training): dZ^T X ~= dZ_hi^T X_hi + dZ_lo^T X_hi + dZ_hi^T X_lo -- three launches of the
+// same GEMM over the hi / lo slab images, accumulating into the same fp32 outputs.  The column sums of dZ (bias gradients)
+// come from the "ones" columns: dZ_hi in the first launch, dZ_lo in the second, not flushed in the third.
+int launch_wgrad_tc_units_x3(const uint8_t* ws, const X3TrainLayout& X, cudaStream_t st) {
+    const TrainLayout& T = X.T;
+    const size_t unit_bytes = (size_t)T.tr_tiles * 4 * TC_SLAB_BYTES;
+    uint8_t* w = const_cast<uint8_t*>(ws);
+    for (int pass = 0; pass < 3; ++pass) {
+        const bool dz_lo = pass == 1, x_lo = pass == 2;
+        const uint8_t* dz = ws + (dz_lo ? X.off_dz_lo : T.off_dz);
+        const uint8_t* act = ws + (x_lo ? X.off_act_lo : T.off_act);
+        const uint8_t* pex = ws + (x_lo ? X.off_pex_lo : T.off_pex);
+        const uint8_t* ped = ws + (x_lo ? X.off_ped_lo : T.off_ped);
+        WgradArgs a{};
+        for (int l = 0; l < 10; ++l) {
+            a.dz[l] = dz + l * unit_bytes;
+            a.xmain[l] = (l == 0) ? nullptr : act + (l - 1) * unit_bytes;
+            a.xenc[l] = (l == 0 || l == 4) ? pex : (l == 8 ? ped : nullptr);
+            a.out[l] = reinterpret_cast<float*>(w + T.off_gw) + (size_t)l * 256 * TC_GW_LD; a.ld[l] = TC_GW_LD; a.ones[l] = pass < 2;
+        }
+        // head pseudo-units: n_7 / n_9 (hi, lo) against the (d_sigma, d_rgb) images (hi, lo)
+        const uint8_t* nact = ws + (dz_lo ? X.off_act_lo : T.off_act);
+        for (int hd = 0; hd < 2; ++hd) {
+            a.dz[10 + hd] = nact + (hd == 0 ? 7 : 9) * unit_bytes;
+            a.xsmall[10 + hd] = ws + (x_lo ? X.off_dh_lo : T.off_dh);
+            a.out[10 + hd] = reinterpret_cast<float*>(w + T.off_gh) + (size_t)hd * 256 * 16; a.ld[10 + hd] = 16;
+        }
+        a.n_tiles = T.n_tiles;
+        int rc = launch_wgrad_tc(a, st); if (rc) return rc;
+    }
+    return NERF_OK;
+}

@@ -210,7 +210,7 @@ class NeRF(nn.Module):
             t, sigma, rgb = ops.g1_train_tc(self.flat_parameters(), list(self.parameters()), rays_o, rays_d, num_samples,
                                             near, far, self.normalize_position, self.normalize_direction,
                                             t_base=self._ladder(near, far, num_samples, rays_o.device), t_in=t, u=u,
-                                            states_x=states_x)
+                                            states_x=states_x, x3=self.precision == "bf16x3")
             if noise is not None:
                 sigma = sigma + noise.view(b, num_samples)
             pixels, depth, acc, weights = ops.composite(sigma, rgb, rays_o=rays_o, rays_d=rays_d, t=t)
@@ -247,7 +247,8 @@ class NeRF(nn.Module):
                 and self.density_inputs == 3 + sx and self.color_inputs == 3 and states_d is None)
 
     def _x3_ok(self, num_samples, states_x, states_d):
-        """fp32-grade tensor-core forward (hi/lo operand split, csrc/fused_tc_x3.cu): unconditional model, no graph"""
+        """fp32-grade tensor-core forward (hi/lo operand split, csrc/fused_tc_x3.cu): unconditional model, no graph
+        (with a graph: _train_tc_ok -> ops._G1TrainTC(x3=True))"""
         return (self.precision == "bf16x3" and num_samples >= 32 and self.density_inputs == 3 and self.color_inputs == 3
                 and states_x is None and states_d is None and not self._wants_grad())
 
@@ -266,8 +267,13 @@ class NeRF(nn.Module):
         return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
 
     def _train_tc_ok(self, num_samples, states_x, states_d):
-        """bf16 tcgen05 path with a graph: the same shapes, when a gradient can be asked for."""
-        return self._tc_shape_ok(num_samples, states_x, states_d) and self._wants_grad()
+        """tcgen05 path with a graph (bf16, or fp32-grade bf16x3 for the unconditional model): when a gradient can be asked for."""
+        if not self._wants_grad():
+            return False
+        if self.precision == "bf16x3":
+            return (num_samples >= 32 and self.density_inputs == 3 and self.color_inputs == 3
+                    and states_x is None and states_d is None)
+        return self._tc_shape_ok(num_samples, states_x, states_d)
 
     def render_rays(self, rays_o, rays_d, near, far, num_samples, states_x=None, states_d=None,
                     randomly_sample=False, density_noise_std=0.0):

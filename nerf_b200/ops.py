@@ -13,7 +13,7 @@ from ._lib import check, lib, ptr, stream
 
 # precision of the MLP contraction: "fp32" = FFMA tiles (the <= 1e-3 parity mode, forward and backward); "bf16" = tcgen05
 # kind::f16 (forward, backward, training); "bf16x3" = fp32-grade operands on tcgen05 (hi/lo split, three products per term):
-# the fused forward / render only -- its graph-recording path is the fp32 FFMA one
+# forward / render, and training (forward, data-gradient chain and weight-gradient GEMMs) of the unconditional model
 PREC_FP32, PREC_BF16, PREC_BF16X3 = 0, 1, 2
 PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "bf16x3": PREC_BF16X3}
 HIDDEN = 256
@@ -271,51 +271,70 @@ class _G1TrainTC(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, flat, rays_o, rays_d, t_base, t_in, u, states_x, cfg, *params):
-        dx, s, near, far, norm, norm_dir, jitter, seed, ray_base = cfg
+        dx, s, near, far, norm, norm_dir, jitter, seed, ray_base, x3 = cfg
         L = lib()
         b = rays_o.shape[0]
         dev = rays_o.device
-        n = L.nerf_g1_train_workspace_bytes(b, s, dx)
-        if n <= 0:
-            raise ValueError("nerf_g1_train_workspace_bytes: bad argument")
-        ws = torch.empty(n, dtype=torch.uint8, device=dev)
-        packed = torch.empty(L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev)
-        packed_bwd = torch.empty(L.nerf_g1_packed_bwd_bytes(dx, 3), dtype=torch.uint8, device=dev)
         st = stream()
-        check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(packed), st), "nerf_g1_pack_weights")
-        check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(packed_bwd), st), "nerf_g1_pack_weights_bwd")
         t = torch.empty(b, s, device=dev); sigma = torch.empty(b, s, device=dev); rgb = torch.empty(b, s, 3, device=dev)
-        check(L.nerf_g1_train_fwd_tc(ptr(packed), dx, 3, ptr(rays_o), ptr(rays_d), b, s, float(near), float(far),
-                                     ptr(t_base), ptr(t_in), ptr(u), int(jitter), seed, ray_base, float(norm), int(norm_dir),
-                                     ptr(states_x), ptr(t), ptr(sigma), ptr(rgb), ptr(ws), n, st), "nerf_g1_train_fwd_tc")
-        COUNTERS["g1_train_fwd_tc"] += 1
+        if x3:                                                  # fp32-grade operands (hi/lo split), unconditional model
+            n = L.nerf_g1_train_x3_workspace_bytes(b, s)
+            ws = torch.empty(n, dtype=torch.uint8, device=dev)
+            packed = g1_pack_weights_x3(flat)
+            packed_bwd = torch.empty(L.nerf_g1_packed_bwd_x3_bytes(), dtype=torch.uint8, device=dev)
+            check(L.nerf_g1_pack_weights_bwd_x3(ptr(flat), ptr(packed_bwd), st), "nerf_g1_pack_weights_bwd_x3")
+            check(L.nerf_g1_train_fwd_x3(ptr(packed), ptr(rays_o), ptr(rays_d), b, s, float(near), float(far), ptr(t_base), ptr(t_in),
+                                         ptr(u), int(jitter), seed, ray_base, float(norm), int(norm_dir),
+                                         ptr(t), ptr(sigma), ptr(rgb), ptr(ws), n, st), "nerf_g1_train_fwd_x3")
+            COUNTERS["g1_train_fwd_x3"] += 1
+        else:
+            n = L.nerf_g1_train_workspace_bytes(b, s, dx)
+            if n <= 0:
+                raise ValueError("nerf_g1_train_workspace_bytes: bad argument")
+            ws = torch.empty(n, dtype=torch.uint8, device=dev)
+            packed = torch.empty(L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev)
+            packed_bwd = torch.empty(L.nerf_g1_packed_bwd_bytes(dx, 3), dtype=torch.uint8, device=dev)
+            check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(packed), st), "nerf_g1_pack_weights")
+            check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(packed_bwd), st), "nerf_g1_pack_weights_bwd")
+            check(L.nerf_g1_train_fwd_tc(ptr(packed), dx, 3, ptr(rays_o), ptr(rays_d), b, s, float(near), float(far),
+                                         ptr(t_base), ptr(t_in), ptr(u), int(jitter), seed, ray_base, float(norm), int(norm_dir),
+                                         ptr(states_x), ptr(t), ptr(sigma), ptr(rgb), ptr(ws), n, st), "nerf_g1_train_fwd_tc")
+            COUNTERS["g1_train_fwd_tc"] += 1
         ctx.save_for_backward(flat, ws, packed, packed_bwd)
-        ctx.cfg = (dx, b, s, n, [tuple(q.shape) for q in params])
+        ctx.cfg = (dx, b, s, n, [tuple(q.shape) for q in params], x3)
         ctx.mark_non_differentiable(t)
         return t, sigma, rgb
 
     @staticmethod
     def backward(ctx, _g_t, d_sigma, d_rgb):
         flat, ws, packed, packed_bwd = ctx.saved_tensors
-        dx, b, s, n, shapes = ctx.cfg
+        dx, b, s, n, shapes, x3 = ctx.cfg
         dev = flat.device
         d_sigma = _f32c(d_sigma) if d_sigma is not None else torch.zeros(b, s, device=dev)
         d_rgb = _f32c(d_rgb) if d_rgb is not None else torch.zeros(b, s, 3, device=dev)
         grads = torch.empty_like(flat)                          # overwritten by the unfold kernel
-        check(lib().nerf_g1_train_bwd_tc(ptr(packed), ptr(packed_bwd), ptr(flat), dx, 3, ptr(d_sigma), ptr(d_rgb), b, s,
-                                         ptr(grads), ptr(ws), n, 0, stream()), "nerf_g1_train_bwd_tc")
-        COUNTERS["g1_train_bwd_tc"] += 1
+        if x3:
+            check(lib().nerf_g1_train_bwd_x3(ptr(packed), ptr(packed_bwd), ptr(flat), ptr(d_sigma), ptr(d_rgb), b, s,
+                                             ptr(grads), ptr(ws), n, 0, stream()), "nerf_g1_train_bwd_x3")
+            COUNTERS["g1_train_bwd_x3"] += 1
+        else:
+            check(lib().nerf_g1_train_bwd_tc(ptr(packed), ptr(packed_bwd), ptr(flat), dx, 3, ptr(d_sigma), ptr(d_rgb), b, s,
+                                             ptr(grads), ptr(ws), n, 0, stream()), "nerf_g1_train_bwd_tc")
+            COUNTERS["g1_train_bwd_tc"] += 1
         off, _ = g1_param_layout(dx, 3)
         views = tuple(grads[o:o + _numel(sh)].view(sh) for o, sh in zip(off, shapes))
         return (None,) * 8 + views
 
 
 def g1_train_tc(flat, params, rays_o, rays_d, num_samples, near, far, normalize_position, normalize_direction=True,
-                t_base=None, t_in=None, u=None, states_x=None, jitter=False, seed=0, ray_id_base=0):
-    """Differentiable (w.r.t. the 44 parameters) tcgen05 forward: -> t, sigma [B,S], rgb [B,S,3]."""
+                t_base=None, t_in=None, u=None, states_x=None, jitter=False, seed=0, ray_id_base=0, x3=False):
+    """Differentiable (w.r.t. the 44 parameters) tcgen05 forward: -> t, sigma [B,S], rgb [B,S,3].
+    x3: fp32-grade operands (hi/lo split) in the forward, the data-gradient chain and the weight-gradient GEMMs."""
     states_x = _f32c(states_x)
     dx = 3 if states_x is None else 3 + states_x.shape[-1]
-    cfg = (dx, int(num_samples), near, far, normalize_position, normalize_direction, jitter, seed, ray_id_base)
+    if x3 and dx != 3:
+        raise ValueError("the bf16x3 training path has no conditional inputs")
+    cfg = (dx, int(num_samples), near, far, normalize_position, normalize_direction, jitter, seed, ray_id_base, bool(x3))
     return _G1TrainTC.apply(flat, _f32c(rays_o), _f32c(rays_d), _f32c(t_base), _f32c(t_in), _f32c(u), states_x, cfg, *params)
 
 

@@ -87,8 +87,9 @@ class Trainer:
         self.near, self.far, self.num_samples = near, far, num_samples
         self.noise_std, self.jitter, self.seed = density_noise_std, randomly_sample, seed
         self.precision = ops.PRECISIONS[precision or model.precision]
-        if self.precision == ops.PREC_BF16X3:            # fp32-grade tensor-core operands exist for the forward only:
-            self.precision = ops.PREC_FP32               # the training step of that mode is the fp32 FFMA one
+        # bf16x3 (fp32-grade operands on tcgen05) trains the unconditional model; conditional models of that mode step in fp32
+        if self.precision == ops.PREC_BF16X3 and (model.density_inputs != 3 or model.color_inputs != 3):
+            self.precision = ops.PREC_FP32
         self.group = process_group
         self.world = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if self.world > 1 else 0
@@ -118,14 +119,16 @@ class Trainer:
     # ------------------------------------------------------------ bf16 (tcgen05) step ------
     def _tc_buffers(self, b, s, dev):
         dx = self.model.density_inputs
-        if self._tc is None or self._tc["key"] != (b, s):
+        x3 = self.precision == ops.PREC_BF16X3
+        if self._tc is None or self._tc["key"] != (b, s, x3):
             L = lib()
-            n = L.nerf_g1_train_workspace_bytes(b, s, dx)
+            n = L.nerf_g1_train_x3_workspace_bytes(b, s) if x3 else L.nerf_g1_train_workspace_bytes(b, s, dx)
             e = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
             self._tc = {
-                "key": (b, s), "n": n, "ws": torch.empty(n, dtype=torch.uint8, device=dev),
-                "packed": torch.empty(L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev),
-                "packed_bwd": torch.empty(L.nerf_g1_packed_bwd_bytes(dx, 3), dtype=torch.uint8, device=dev),
+                "key": (b, s, x3), "n": n, "ws": torch.empty(n, dtype=torch.uint8, device=dev),
+                "packed": torch.empty(L.nerf_g1_packed_x3_bytes() if x3 else L.nerf_g1_packed_bytes(dx, 3), dtype=torch.uint8, device=dev),
+                "packed_bwd": torch.empty(L.nerf_g1_packed_bwd_x3_bytes() if x3 else L.nerf_g1_packed_bwd_bytes(dx, 3),
+                                          dtype=torch.uint8, device=dev),
                 "t": e(b, s), "sigma": e(b, s), "rgb": e(b, s, 3), "d_sigma": e(b, s), "d_rgb": e(b, s, 3),
                 "pixels": e(b, 3), "g_pixels": e(b, 3), "loss": e(1),
             }
@@ -145,14 +148,24 @@ class Trainer:
         ray_base = self.rays_seen * self.world + self.rank * b
         dx = m.density_inputs
         sx = ops._f32c(states_x) if dx > 3 else None
-        check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(z["packed"]), st), "nerf_g1_pack_weights")
-        check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(z["packed_bwd"]), st), "nerf_g1_pack_weights_bwd")
-        check(L.nerf_g1_train_fwd_tc(ptr(z["packed"]), dx, 3, ptr(rays_o), ptr(rays_d), b, s, self.near, self.far,
-                                     ptr(m._ladder(self.near, self.far, s, dev)), None, ptr(u),
-                                     int(self.jitter and u is None), self.seed, ray_base,
-                                     float(m.normalize_position), int(m.normalize_direction), ptr(sx),
-                                     ptr(z["t"]), ptr(z["sigma"]), ptr(z["rgb"]), ptr(z["ws"]), z["n"], st),
-              "nerf_g1_train_fwd_tc")
+        x3 = self.precision == ops.PREC_BF16X3
+        ladder = m._ladder(self.near, self.far, s, dev)
+        if x3:
+            check(L.nerf_g1_pack_weights_x3(ptr(flat), ptr(z["packed"]), st), "nerf_g1_pack_weights_x3")
+            check(L.nerf_g1_pack_weights_bwd_x3(ptr(flat), ptr(z["packed_bwd"]), st), "nerf_g1_pack_weights_bwd_x3")
+            check(L.nerf_g1_train_fwd_x3(ptr(z["packed"]), ptr(rays_o), ptr(rays_d), b, s, self.near, self.far, ptr(ladder), None, ptr(u),
+                                         int(self.jitter and u is None), self.seed, ray_base,
+                                         float(m.normalize_position), int(m.normalize_direction),
+                                         ptr(z["t"]), ptr(z["sigma"]), ptr(z["rgb"]), ptr(z["ws"]), z["n"], st), "nerf_g1_train_fwd_x3")
+        else:
+            check(L.nerf_g1_pack_weights(ptr(flat), dx, 3, ptr(z["packed"]), st), "nerf_g1_pack_weights")
+            check(L.nerf_g1_pack_weights_bwd(ptr(flat), dx, 3, ptr(z["packed_bwd"]), st), "nerf_g1_pack_weights_bwd")
+            check(L.nerf_g1_train_fwd_tc(ptr(z["packed"]), dx, 3, ptr(rays_o), ptr(rays_d), b, s, self.near, self.far,
+                                         ptr(ladder), None, ptr(u),
+                                         int(self.jitter and u is None), self.seed, ray_base,
+                                         float(m.normalize_position), int(m.normalize_direction), ptr(sx),
+                                         ptr(z["t"]), ptr(z["sigma"]), ptr(z["rgb"]), ptr(z["ws"]), z["n"], st),
+                  "nerf_g1_train_fwd_tc")
         launches = 4 + (5 if dx > 3 else 0)     # conditional: state weights, PE(states), ray bias; dz ray sums, state gradients
         std = float(self.noise_std)
         if noise is not None:                   # host-supplied draw (parity mode)
@@ -173,10 +186,15 @@ class Trainer:
                                        ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
                   "nerf_composite_bwd")
             launches += 3
-        check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), dx, 3, ptr(z["d_sigma"]),
-                                     ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
-              "nerf_g1_train_bwd_tc")
-        launches += 3                                               # bwd, wgrad, unfold (memset not counted)
+        if x3:
+            check(L.nerf_g1_train_bwd_x3(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), ptr(z["d_sigma"]), ptr(z["d_rgb"]), b, s,
+                                         ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st), "nerf_g1_train_bwd_x3")
+            launches += 5                                           # bwd, 3 x wgrad, unfold
+        else:
+            check(L.nerf_g1_train_bwd_tc(ptr(z["packed"]), ptr(z["packed_bwd"]), ptr(flat), dx, 3, ptr(z["d_sigma"]),
+                                         ptr(z["d_rgb"]), b, s, ptr(self.flat_grad), ptr(z["ws"]), z["n"], 0, st),
+                  "nerf_g1_train_bwd_tc")
+            launches += 3                                           # bwd, wgrad, unfold (memset not counted)
         launches += self._exchange_and_update(flat, apply_update)
         self.rays_seen += b
         self.kernel_launches = launches
@@ -207,8 +225,8 @@ class Trainer:
         """One optimisation step on a ray batch resident on the device.  Returns the loss
         (1-element device tensor; reading it is the caller's device->host sync)."""
         m = self.model
-        if (self.precision == ops.PREC_BF16 and states_d is None and m.color_inputs == 3 and self.num_samples >= 32
-                and (m.density_inputs == 3 or states_x is not None)):
+        if (self.precision in (ops.PREC_BF16, ops.PREC_BF16X3) and states_d is None and m.color_inputs == 3 and self.num_samples >= 32
+                and (m.density_inputs == 3 or (states_x is not None and self.precision == ops.PREC_BF16))):
             return self._step_bf16(rays_o.contiguous(), rays_d.contiguous(), target.contiguous(), u, noise, apply_update,
                                    states_x=states_x)
         flat = m.flat_parameters()
