@@ -288,7 +288,7 @@ int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, const float
  * each product formed as hi*hi + lo*hi + hi*lo with fp32 accumulation (~2^-17 relative); LayerNorm / ReLU forward and
  * backward, the heads and the unfold are fp32.  Unconditional model (Dx = Dd = 3).  packed_x3 from
  * nerf_g1_pack_weights_x3, packed_bwd_x3 (nerf_g1_packed_bwd_x3_bytes()) from nerf_g1_pack_weights_bwd_x3; one workspace of
- * nerf_g1_train_x3_workspace_bytes(B, S) shared by the two calls (26 KB per point).  Arguments as nerf_g1_train_fwd_tc /
+ * nerf_g1_train_x3_workspace_bytes(B, S) shared by the two calls (21 KB per point).  Arguments as nerf_g1_train_fwd_tc /
  * nerf_g1_train_bwd_tc; grads (flat fp32, state_dict order) are OVERWRITTEN. */
 int64_t nerf_g1_packed_bwd_x3_bytes(void);
 int nerf_g1_pack_weights_bwd_x3(const float* params, void* packed_bwd_x3, void* stream);

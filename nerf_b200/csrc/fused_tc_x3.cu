@@ -21,12 +21,11 @@
 
 // ReLU + LayerNorm epilogue of one unit (the arithmetic of epilogue_unit in tc_fused_kernel.cuh); pass 2 writes the
 // normalised row twice: hi = bf16(n), lo = bf16(n - hi).   MODE: 0 plain, 1 unit 7 (+ density), 2 unit 9 (+ colour, no store)
-// TRAIN: unit 9 is normalised and stored too, (rstd, shift) go to tr_stats, and a third part r2 = bf16(n - hi - lo) of every
-// row goes to a row-major array read only by the backward's LayerNorm epilogue: g - mean(g) - n mean(g n) cancels most of g
-// where g is nearly parallel to n (the density gradient at unit 7), which amplifies the 2^-18 error of hi + lo a hundredfold;
-// with r2 the epilogue's n is fp32-exact.  The least significant mantissa bit of r2 carries the ReLU mask (1 = active): the
-// backward needs the mask EXACTLY (a fraction f of wrongly masked units is a relative gradient error of sqrt(f)) and a
-// reconstructed n > shift is not an exact test.  The MMA operands (hi, lo) are those of the inference kernel, bit for bit.
+// TRAIN: unit 9 is normalised and stored too, (rstd, shift) go to tr_stats, and the ReLU mask of the row goes to tr_mask as
+// 8 words (bit = column active): the backward needs the mask EXACTLY (a fraction f of wrongly masked units is a relative
+// gradient error of sqrt(f)) and a reconstructed hi + lo > shift is not an exact test.  The MMA operands (hi, lo) are those
+// of the inference kernel, bit for bit.  (A third residual part n - hi - lo for the LayerNorm backward was built and
+// measured: no change in any gradient -- the differences to the fp32 path are the gradient's conditioning)
 template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr, uint32_t row,
                                               uint32_t vec_addr, const RowState& st) {
@@ -86,20 +85,17 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
     if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
     if (MODE == 2 && !TRAIN) return;                               // unit 9 feeds only the colour head
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
-        uint32_t hi[16], lo[16], r2[16];
+        uint32_t hi[16], lo[16], mask = 0;
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
             float2 y = __ffma2_rn(f2(rc[j], rc[j + 1]), rstd2, shift2);
-            const uint32_t active = TRAIN ? ((y.x > shift ? 1u : 0u) | (y.y > shift ? 0x10000u : 0u)) : 0u;
+            if (TRAIN) mask |= (y.x > shift ? 1u << j : 0u) | (y.y > shift ? 2u << j : 0u);
             y.x = fmaxf(y.x, shift); y.y = fmaxf(y.y, shift);      // = relu(z) rstd + shift  (rstd > 0)
             const __nv_bfloat162 h = __float22bfloat162_rn(y);
             const float2 hf = __bfloat1622float2(h);
             const __nv_bfloat162 l2 = __float22bfloat162_rn(make_float2(y.x - hf.x, y.y - hf.y));
             hi[j / 2] = *reinterpret_cast<const uint32_t*>(&h); lo[j / 2] = *reinterpret_cast<const uint32_t*>(&l2);
-            if (TRAIN) {
-                const float2 lf = __bfloat1622float2(l2);
-                r2[j / 2] = (tc::pack_bf16x2((y.x - hf.x) - lf.x, (y.y - hf.y) - lf.y) & 0xFFFEFFFEu) | active;
-            }
+
         }
         const uint32_t slab = act_addr + (ch >> 1) * TC_SLAB_BYTES;
 #pragma unroll
@@ -107,11 +103,7 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
             store_row_chunk(slab, row, (ch & 1) * 4 + i, make_uint4(hi[i * 4], hi[i * 4 + 1], hi[i * 4 + 2], hi[i * 4 + 3]));
             store_row_chunk(slab + 65536, row, (ch & 1) * 4 + i, make_uint4(lo[i * 4], lo[i * 4 + 1], lo[i * 4 + 2], lo[i * 4 + 3]));
         }
-        if (TRAIN) {
-            uint4* dst = reinterpret_cast<uint4*>(a.tr_r2 + (((size_t)l * a.P_pad + st.p) * 256 + ch * 32) * 2);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) dst[i] = make_uint4(r2[i * 4], r2[i * 4 + 1], r2[i * 4 + 2], r2[i * 4 + 3]);
-        }
+        if (TRAIN) a.tr_mask[((size_t)l * a.P_pad + st.p) * 8 + ch] = mask;
     };
     tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
 #pragma unroll 1

@@ -9,9 +9,8 @@
 //   warp 0     TMA producer of the transposed weight stages: per K-slab the hi stage, then the lo stage
 //   warp 1     MMA issuer (leader CTA) / weight-arrival relay (peer CTA)
 //   warps 2-5  LayerNorm + ReLU backward (thread = point row = TMEM lane), in fp32:
-//                  dz = mask * rstd * (g - mean(g) - n * mean(g n)),   n = n_hi + n_lo (forward's slab images) + r2 (its
-//              residual rows, read straight from global memory: the subtraction cancels most of g where g is nearly
-//              parallel to n, so n must be fp32-exact), the mask is the least significant mantissa bit of r2;
+//                  dz = mask * rstd * (g - mean(g) - n * mean(g n)),   n = n_hi + n_lo (forward's slab images),
+//              the mask is the forward's exact bitmask (8 words per row and unit, fused_tc_x3.cu);
 //              dz overwrites n in place as (hi, lo) = the A operands of the next MMAs and is bulk-stored for the
 //              weight-gradient GEMM; row 0 of the group issues the tile's bulk loads and stores.
 // Per unit the steps are serial (epilogue -> MMAs -> refill): the bf16 kernel's two-slot overlap does not fit next to the
@@ -47,7 +46,7 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 // kernel's time goes to the three-product MMAs and the 256 KB of slab traffic per tile and unit.
 template <int SRC>
 __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_addr, uint32_t lo_addr, uint32_t row, uint32_t hw_addr,
-                                                  const uint4* __restrict__ r2row, float rstd, float ds, float dr, float dg, float db) {
+                                                  const uint32_t (&mw)[8], float rstd, float ds, float dr, float dg, float db) {
     uint32_t r[32];
     // g of the 8 columns ch*32 + i*8 .. +7 (rc = the chunk's 32 TMEM columns)
     auto grad8 = [&](const uint32_t (&rc)[32], int ch, int i, float (&g)[8]) {
@@ -74,14 +73,11 @@ __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_ad
     // n = hi + lo and the ReLU mask (bit q = column q active) of the same 8 columns; off = their byte offset in both parts
     auto load_n = [&](int ch, int i, float (&n)[8], uint32_t& mask, uint32_t& off) {
         off = (uint32_t)(ch >> 1) * TC_SLAB_BYTES + tc::sw128_offset(row, (ch & 1) * 4 + i);
-        const uint4 h = lds128u(hi_addr + off), l = lds128u(lo_addr + off), rr = r2row[ch * 4 + i];
-        const uint32_t hv[4] = {h.x, h.y, h.z, h.w}, lv[4] = {l.x, l.y, l.z, l.w}, rv[4] = {rr.x, rr.y, rr.z, rr.w};
-        mask = 0;
+        const uint4 h = lds128u(hi_addr + off), l = lds128u(lo_addr + off);
+        const uint32_t hv[4] = {h.x, h.y, h.z, h.w}, lv[4] = {l.x, l.y, l.z, l.w};
+        mask = (mw[ch] >> (i * 8)) & 0xFFu;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            n[2 * q] = (bf_lo(hv[q]) + bf_lo(lv[q])) + bf_lo(rv[q]); n[2 * q + 1] = (bf_hi(hv[q]) + bf_hi(lv[q])) + bf_hi(rv[q]);
-            mask |= ((rv[q] & 1u) << (2 * q)) | (((rv[q] >> 16) & 1u) << (2 * q + 1));
-        }
+        for (int q = 0; q < 4; ++q) { n[2 * q] = bf_lo(hv[q]) + bf_lo(lv[q]); n[2 * q + 1] = bf_hi(hv[q]) + bf_hi(lv[q]); }
     };
     // ---- pass 1: sum g, sum g n   (two chains each)
     float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
@@ -252,16 +248,21 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
             }
             for (int l = 9; l >= 0; --l) {
                 const float2 stt = a.stats[(int64_t)l * a.P_pad + p];
+                uint32_t mw[8];                                                   // the unit's ReLU mask of this row (requested before the waits)
+                {
+                    const uint4* mp = reinterpret_cast<const uint4*>(a.mask + ((size_t)l * a.P_pad + p) * 8);
+                    const uint4 m0 = mp[0], m1 = mp[1];
+                    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+                }
                 if (l < 9) {
                     tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;     // g_l is in TMEM, the MMAs have consumed dz_{l+1}
                     tc::tcgen05_fence_after();
                     if (io) { tc::tma_store_wait_read0(); load_unit(l, tile); }      // its store has been read out too: refill with n_l
                 }
                 tc::mbar_wait(n_full, nf_it & 1, a.wait_hint); ++nf_it;
-                const uint4* r2row = reinterpret_cast<const uint4*>(a.r2 + ((size_t)l * a.P_pad + p) * 512);
-                if (l == 9) bwd_x3_epilogue_unit<2>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
-                else if (l == 7) bwd_x3_epilogue_unit<1>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
-                else bwd_x3_epilogue_unit<0>(taddr, hi_addr, lo_addr, row, hw_addr, r2row, stt.x, ds, dr, dg, db);
+                if (l == 9) bwd_x3_epilogue_unit<2>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
+                else if (l == 7) bwd_x3_epilogue_unit<1>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
+                else bwd_x3_epilogue_unit<0>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
                 tc::fence_proxy_async_smem();
                 tc::named_bar_sync(1, 128);                                       // dz_l complete in shared memory
                 if (l > 0) {

@@ -6,7 +6,7 @@ struct BwdX3Args {
     const uint8_t* stages_hi; const uint8_t* stages_lo;   // transposed weight stages, unit l in 1..9 -> 8 stages at (l-1)*8 (tc_train.cu layout)
     const float* vec;                                     // forward epilogue vectors (head weights with gamma folded)
     const uint8_t* act_hi; const uint8_t* act_lo;         // [10][tr_tiles][4 slabs]
-    const uint8_t* r2;                                    // [10][P_pad][256] bf16 rows: n - hi - lo, LSB = ReLU mask
+    const uint32_t* mask;                                 // [10][P_pad][8] words: ReLU mask, bit = column active
     const float2* stats;                                  // [10][P_pad] (rstd, -mean*rstd)
     const float* d_sigma; const float* d_rgb;
     uint8_t* dz_hi; uint8_t* dz_lo;                       // [10][tr_tiles][4 slabs] out

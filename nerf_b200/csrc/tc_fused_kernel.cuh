@@ -42,7 +42,7 @@ struct FusedArgs {
     // encodings, plus (rstd, -mean*rstd) per point and unit, for the backward and wgrad kernels
     uint8_t* tr_act; uint8_t* tr_pex; uint8_t* tr_ped; float2* tr_stats; int64_t P_pad; int tr_tiles;
     uint8_t* tr_act_lo; uint8_t* tr_pex_lo; uint8_t* tr_ped_lo;   // fp32-grade training forward (fused_tc_x3.cu): the lo parts' images
-    uint8_t* tr_r2;                                               //   and the residual rows n - hi - lo (+ ReLU mask bit), [10][P_pad][256] bf16
+    uint32_t* tr_mask;                                            //   and the ReLU masks, [10][P_pad][8] words (bit = column active)
     const float* ray_bias;                        // conditional inputs: [2 (units 0, 4)][rb_rows][256] fp32 bias rows, or null;
     int64_t rb_rows, rb_ray0, rb_div;             //   ray r of this launch uses row (rb_ray0 + r) / rb_div (one row per ray, or per camera)
     long long* prof;                              // NERF_TC_PROF: clock64 stamps of CTA 0, second work unit

@@ -134,8 +134,8 @@ static inline void make_train_layout(int64_t B, int S, TrainLayout& T, int Dx = 
 struct X3TrainLayout {
     TrainLayout T;
     int64_t off_act_lo, off_dz_lo, off_pex_lo, off_ped_lo, off_dh_lo, total;
-    int64_t off_r2;      // [10][P_pad][256] bf16, row-major: third part of the normalised activations, n - hi - lo, read only by the
-};                       // LayerNorm backward (its cancellation amplifies the error of n); its LSB carries the ReLU mask
+    int64_t off_mask;    // [10][P_pad][8] uint32: the ReLU mask of every unit, one bit per column (bit c & 31 of word c >> 5)
+};
 static inline void make_x3_train_layout(int64_t B, int S, X3TrainLayout& X) {
     make_train_layout(B, S, X.T, 3);
     int64_t o = X.T.total;
@@ -145,7 +145,7 @@ static inline void make_x3_train_layout(int64_t B, int S, X3TrainLayout& X) {
     X.off_pex_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
     X.off_ped_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
     X.off_dh_lo = o; o += (int64_t)X.T.tr_tiles * 4096;
-    X.off_r2 = o; o += 10ll * X.T.P_pad * 512;
+    X.off_mask = o; o += 10ll * X.T.P_pad * 32;
     X.total = o;
 }
 
