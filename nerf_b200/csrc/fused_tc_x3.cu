@@ -9,15 +9,31 @@
 // Shared memory is the bf16 kernel's layout, used by ONE 128-point tile per CTA instead of two:
 //   SM_ACT  [hi: 4 slabs | lo: 4 slabs]   (the second tile slot's 64 KB hold the lo parts)
 //   SM_PE   [hi slab | lo slab]
-//   ring    3 x 20 KB: [bias block 4 KB (first stage of a unit without an encoding slab)] [4 k-cores hi | 4 k-cores lo]
+//   ring    3 x 16 KB [4 k-cores hi | 4 k-cores lo], then ONE 4 KB bias block (of the unit in flight; units without an
+//           encoding slab) and the 8 KB exchange buffer of the epilogue's thread pairs -- the bf16 kernel's 3 x 20 KB
 // so a ring stage covers K = 32 (two K-steps, six MMAs).  One accumulator (256 TMEM columns): the MMAs of unit l+1
 // depend on the whole epilogue of unit l of the same tile, so tensor pipe and epilogue alternate; the price of
 // fp32-grade operands here is ~3x the MMAs and no tile ping-pong.
 //   warp 0    TMA producer      warp 1    MMA issuer (leader) / weight-arrival relay (peer)
-//   warps 2-5 encoder + epilogue (thread = point row = TMEM lane)
+//   warps 2-9 encoder + epilogue, TWO threads per point row (warps w and w + 4 share a TMEM lane quarter; each takes 128
+//             of the row's 256 columns and the row sums are exchanged through shared memory).  With one tile slot and one
+//             thread per row there was one epilogue warp per SMSP and every dependent instruction's latency was exposed.
+// TRAIN: the slab images go to HBM as coalesced st.global copies by the same 256 threads while the MMAs of the next
+// unit run.  As bulk stores they shared the SM's one TMA queue (~32 B/cycle) with the weight stages, which then arrived
+// late: the measured unit time was 19k cycles against 6k of MMAs.
 #include "tc_fused_kernel.cuh"
+#include <stdio.h>
 
-#define X3_THREADS 192
+#define X3_THREADS 320
+#define X3_SM_BIAS (SM_RING + TC_RING * X3_GROUP_BYTES)                 // 4 KB
+#define X3_SM_XCH (X3_SM_BIAS + TF_BIAS_KCORES * TF_KCORE_BYTES)       // [128 rows][2 halves][8 floats]
+static_assert(X3_SM_XCH + 128 * 2 * 32 <= SM_VEC, "the x3 ring, bias block and exchange buffer take the bf16 kernel's ring bytes");
+
+__device__ __forceinline__ uint4 lds128v(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
 
 // ReLU + LayerNorm epilogue of one unit (the arithmetic of epilogue_unit in tc_fused_kernel.cuh); pass 2 writes the
 // normalised row twice: hi = bf16(n), lo = bf16(n - hi).   MODE: 0 plain, 1 unit 7 (+ density), 2 unit 9 (+ colour, no store)
@@ -26,9 +42,11 @@
 // gradient error of sqrt(f)) and a reconstructed hi + lo > shift is not an exact test.  The MMA operands (hi, lo) are those
 // of the inference kernel, bit for bit.  (A third residual part n - hi - lo for the LayerNorm backward was built and
 // measured: no change in any gradient -- the differences to the fp32 path are the gradient's conditioning)
+// This thread takes columns 128 * half .. + 127; both threads of a row form the same (rstd, shift) from the exchanged sums
+// (a + b = b + a in fp32), half 0 writes the row's outputs.
 template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr, uint32_t row,
-                                              uint32_t vec_addr, const RowState& st) {
+                                              uint32_t vec_addr, const RowState& st, int half, uint32_t xch_addr) {
     const uint32_t hsum_addr = vec_addr + (SM_HSUM - SM_VEC);
     uint32_t r0[32], r1[32];
     float2 s2 = make_float2(0.f, 0.f), q2 = s2, s3 = s2, q3 = s2;
@@ -53,36 +71,48 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
             }
         }
     };
-    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+    const int cb = 4 * half;                                       // this thread's first 32-column chunk
+    tc::tmem_ld32(taddr + cb * 32, r0); tc::tmem_ld_wait();
 #pragma unroll 1
-    for (int c2 = 0; c2 < 4; ++c2) {
-        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
-        pass1(r0, 2 * c2);
+    for (int c2 = 0; c2 < 2; ++c2) {
+        tc::tmem_ld32(taddr + (cb + 2 * c2 + 1) * 32, r1);
+        pass1(r0, cb + 2 * c2);
         tc::tmem_ld_wait();
-        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
-        pass1(r1, 2 * c2 + 1);
+        if (c2 < 1) tc::tmem_ld32(taddr + (cb + 2 * c2 + 2) * 32, r0);
+        pass1(r1, cb + 2 * c2 + 1);
         tc::tmem_ld_wait();
     }
     s2 = __fadd2_rn(s2, s3); q2 = __fadd2_rn(q2, q3);
-    const float mean = (s2.x + s2.y) * (1.0f / 256.f);
-    const float var = fmaxf((q2.x + q2.y) * (1.0f / 256.f) - mean * mean, 0.f);
+    hp0 = __fadd2_rn(hp0, hp0b); hp1 = __fadd2_rn(hp1, hp1b); hp2 = __fadd2_rn(hp2, hp2b);
+    float ps = s2.x + s2.y, pq = q2.x + q2.y, ph0 = hp0.x + hp0.y, ph1 = hp1.x + hp1.y, ph2 = hp2.x + hp2.y;
+    {   // the other half's sums (named barrier 2: the 256 epilogue threads)
+        const uint32_t mine = xch_addr + (row * 2 + half) * 32, other = xch_addr + (row * 2 + (half ^ 1)) * 32;
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(mine), "f"(ps), "f"(pq), "f"(ph0), "f"(ph1) : "memory");
+        if (MODE == 2) asm volatile("st.shared.f32 [%0], %1;" ::"r"(mine + 16), "f"(ph2) : "memory");
+        tc::named_bar_sync(2, 256);
+        float os, oq, oh0, oh1, oh2 = 0.f;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(os), "=f"(oq), "=f"(oh0), "=f"(oh1) : "r"(other) : "memory");
+        if (MODE == 2) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(oh2) : "r"(other + 16) : "memory");
+        ps += os; pq += oq; ph0 += oh0; ph1 += oh1; ph2 += oh2;
+    }
+    const float mean = ps * (1.0f / 256.f);
+    const float var = fmaxf(pq * (1.0f / 256.f) - mean * mean, 0.f);
     const float rstd = rsqrtf(var + NERF_LN_EPS);
     const float shift = -mean * rstd;
     const float2 rstd2 = make_float2(rstd, rstd), shift2 = make_float2(shift, shift);
     if (MODE == 1 || MODE == 2) {
         const float4 hbias = tc::lds128(vec_addr + (TC_VEC_HEADB - TC_VEC_HEADW) * 4);
         const float4 hwsum = tc::lds128(hsum_addr);
-        hp0 = __fadd2_rn(hp0, hp0b); hp1 = __fadd2_rn(hp1, hp1b); hp2 = __fadd2_rn(hp2, hp2b);
-        if (st.valid) {
-            if (MODE == 1) a.out_sigma[st.p] = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.x, hbias.x));
+        if (st.valid && half == 0) {
+            if (MODE == 1) a.out_sigma[st.p] = fmaf(rstd, ph0, fmaf(shift, hwsum.x, hbias.x));
             else {
-                a.out_rgb[st.p * 3] = fmaf(rstd, hp0.x + hp0.y, fmaf(shift, hwsum.y, hbias.y));
-                a.out_rgb[st.p * 3 + 1] = fmaf(rstd, hp1.x + hp1.y, fmaf(shift, hwsum.z, hbias.z));
-                a.out_rgb[st.p * 3 + 2] = fmaf(rstd, hp2.x + hp2.y, fmaf(shift, hwsum.w, hbias.w));
+                a.out_rgb[st.p * 3] = fmaf(rstd, ph0, fmaf(shift, hwsum.y, hbias.y));
+                a.out_rgb[st.p * 3 + 1] = fmaf(rstd, ph1, fmaf(shift, hwsum.z, hbias.z));
+                a.out_rgb[st.p * 3 + 2] = fmaf(rstd, ph2, fmaf(shift, hwsum.w, hbias.w));
             }
         }
     }
-    if (TRAIN) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
+    if (TRAIN && half == 0) a.tr_stats[(int64_t)l * a.P_pad + st.p] = make_float2(rstd, shift);
     if (MODE == 2 && !TRAIN) return;                               // unit 9 feeds only the colour head
     auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
         uint32_t hi[16], lo[16], mask = 0;
@@ -105,14 +135,14 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
         }
         if (TRAIN) a.tr_mask[((size_t)l * a.P_pad + st.p) * 8 + ch] = mask;
     };
-    tc::tmem_ld32(taddr, r0); tc::tmem_ld_wait();
+    tc::tmem_ld32(taddr + cb * 32, r0); tc::tmem_ld_wait();
 #pragma unroll 1
-    for (int c2 = 0; c2 < 4; ++c2) {
-        tc::tmem_ld32(taddr + (2 * c2 + 1) * 32, r1);
-        pass2(r0, 2 * c2);
+    for (int c2 = 0; c2 < 2; ++c2) {
+        tc::tmem_ld32(taddr + (cb + 2 * c2 + 1) * 32, r1);
+        pass2(r0, cb + 2 * c2);
         tc::tmem_ld_wait();
-        if (c2 < 3) tc::tmem_ld32(taddr + (2 * c2 + 2) * 32, r0);
-        pass2(r1, 2 * c2 + 1);
+        if (c2 < 1) tc::tmem_ld32(taddr + (cb + 2 * c2 + 2) * 32, r0);
+        pass2(r1, cb + 2 * c2 + 1);
         tc::tmem_ld_wait();
     }
 }
@@ -146,7 +176,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), leader ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
-        tc::mbar_init(act_ready, 8); tc::mbar_init(acc_ready, 1);
+        tc::mbar_init(act_ready, 16); tc::mbar_init(acc_ready, 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 256);
@@ -164,14 +194,17 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                 const uint8_t* src = a.stages + a.unit_off[l] + (size_t)rank * a.half_kcores[l] * TF_KCORE_BYTES;
                 for (int j = 0; j < 2 * a.nk[l]; ++j, ++it) {
                     const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
-                    const uint32_t bytes = X3_GROUP_BYTES + (j == 0 ? blk_bytes : 0);
+                    const uint32_t front = j == 0 ? blk_bytes : 0;     // the unit's bias block precedes its first group in the image
                     tc::mbar_wait_spin(ring_empty(slot), ph ^ 1, a.wait_hint);
                     if (tc::elect_one()) {
-                        tc::mbar_arrive_expect_tx(ring_full(slot), bytes);
-                        tc::tma_load_1d(base + SM_RING + slot * TF_SLOT_BYTES, src, bytes, ring_full(slot));
+                        tc::mbar_arrive_expect_tx(ring_full(slot), X3_GROUP_BYTES + front);
+                        // One bias area for all units: bias blocks are >= 8 stages apart and the wait above covers the MMAs of
+                        // every stage up to it - TC_RING (a commit completes after all earlier MMAs), the last bias MMA included.
+                        if (front) tc::tma_load_1d(base + X3_SM_BIAS, src, front, ring_full(slot));
+                        tc::tma_load_1d(base + SM_RING + slot * X3_GROUP_BYTES, src + front, X3_GROUP_BYTES, ring_full(slot));
                     }
                     __syncwarp();
-                    src += bytes;
+                    src += X3_GROUP_BYTES + front;
                 }
             }
     } else if (warp == 1) {
@@ -182,6 +215,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
             constexpr uint32_t hi_b = (TF_B_SBO >> 4) | (1u << 14);                       // no-swizzle k-cores
             auto lo_a = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
             const uint32_t ring_lo = (((base + SM_RING) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
+            const uint32_t bias_lo = (((base + X3_SM_BIAS) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
             auto mma = [&](uint32_t alo, uint32_t blo, uint32_t acc) {
                 tc::umma_bf16_2cta(tmem_base, ((uint64_t)hi_a << 32) | alo, ((uint64_t)hi_b << 32) | blo, idesc, acc);
             };
@@ -190,8 +224,11 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
             uint32_t it = 0, act_it = 0;
             for (int q = 0; q < n_my; ++q)
                 for (int l = 0; l < 10; ++l) {
+                    const bool pfm = a.prof && blockIdx.x == 0 && q == 1 && lane == 0;
+                    if (pfm) a.prof[l * 8 + 0] = clock64();
                     tc::mbar_wait_spin(act_ready, act_it & 1, a.wait_hint); ++act_it;
                     tc::tcgen05_fence_after();
+                    if (pfm) a.prof[l * 8 + 1] = clock64();
                     const bool blk = tc_unit_has_bias_block(l);
                     const int ng = 2 * a.nk[l];
                     for (int j = 0; j < ng; ++j, ++it) {
@@ -200,13 +237,12 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                         const bool enc = (l == 0 || slab >= 4);
                         const uint32_t a_hi = (enc ? pe_lo : act_lo + slab * (TC_SLAB_BYTES >> 4)) + (j & 1) * 4;   // 32 columns = 64 B = 4 units
                         const uint32_t a_lo = a_hi + (enc ? PE_LO_PART : ACT_LO_PART);
-                        uint32_t blo = ring_lo + slot * (TF_SLOT_BYTES >> 4);
+                        const uint32_t blo = ring_lo + slot * (X3_GROUP_BYTES >> 4);
                         tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
                         if (tc::elect_one()) {
                             uint32_t acc = (j != 0) ? 1u : 0u;
                             if (blk && j == 0) {                   // acc = b': hi slab columns 48..63 (ones at 60..62) x bias block
-                                mma(pe_lo + 3 * 2, blo, 0); acc = 1u;
-                                blo += (TF_BIAS_KCORES * TF_KCORE_BYTES) >> 4;
+                                mma(pe_lo + 3 * 2, bias_lo, 0); acc = 1u;
                             }
 #pragma unroll
                             for (int kk = 0; kk < 2; ++kk) {
@@ -221,6 +257,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                         }
                         __syncwarp();
                     }
+                    if (pfm) a.prof[l * 8 + 2] = clock64();
                 }
         } else if (lane == 0) {
             // ===================== peer relay: "my weight half has landed" -> leader's full barrier =====================
@@ -235,9 +272,11 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
         }
     } else {
         // ===================== encoder + epilogue =====================
-        const uint32_t row = (warp & 3) * 32 + lane;                 // TMEM lane quarter = warp % 4
+        const uint32_t row = (warp & 3) * 32 + lane;                 // TMEM lane quarter = warp % 4: warps w and w + 4 share rows
+        const int half = (warp - 2) >> 2;                            // which 128 columns of the row this thread takes
+        const uint32_t et = threadIdx.x - 64;                        // 0..255 within the group
         const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16);
-        const uint32_t act_addr = base + SM_ACT, pe_addr = base + SM_PE;
+        const uint32_t act_addr = base + SM_ACT, pe_addr = base + SM_PE, xch_addr = base + X3_SM_XCH;
         const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
         auto signal_act = [&]() {
             tc::fence_proxy_async_smem();
@@ -246,52 +285,61 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
             if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
         };
         uint32_t acc_it = 0;
-        // TRAIN: row 0 bulk-stores the slab images (hi and lo) the backward needs.  A store must have been READ OUT of shared
-        // memory before the slabs are written again: `stores_read_out` (wait_group.read by the issuing thread + the group's
-        // barrier) precedes every writer of a slab; the MMAs only read the slabs, so stores and MMAs overlap freely.
-        auto stores_read_out = [&]() { if (row == 0) tc::tma_store_wait_read0(); tc::named_bar_sync(1, 128); };
-        auto slabs_complete = [&]() { tc::fence_proxy_async_smem(); tc::named_bar_sync(1, 128); };
+        // TRAIN: the slab images (hi and lo) the backward needs, shared memory -> HBM, 16 bytes per thread and step, four in
+        // flight.  Issued after the slabs are complete (`slabs_complete`) and the MMAs have been released; the MMAs only read
+        // the slabs.  The next writer of a slab is a pass 2 or an encoder at least one exchange barrier later, and a thread
+        // reaches that barrier only after its own copies have been read out (the loads feed its stores).
+        auto slabs_complete = [&]() { tc::fence_proxy_async_smem(); tc::named_bar_sync(1, 256); };
+        auto copy_out = [&](uint8_t* dst, uint32_t src, uint32_t bytes) {
+#pragma unroll 1
+            for (uint32_t o = et * 16u; o < bytes; o += 4u * 4096u) {
+                uint4 v[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v[k] = lds128v(src + o + k * 4096u);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(dst + o + k * 4096u) = v[k];
+            }
+        };
         for (int q = 0; q < n_my; ++q) {
             const int unit = me + q * G;
             const int tile = 2 * unit + (int)rank;
             RowState st;
-            if (TRAIN) stores_read_out();
-            encode_row<true>(a, tile, row, pe_addr, st);
+            if (half == 0) encode_row<true>(a, tile, row, pe_addr, st);
+            else { st.p = (int64_t)tile * 128 + row; st.valid = false; st.d[0] = st.d[1] = st.d[2] = 0.f; }
             if (TRAIN) {
                 st.p = (int64_t)tile * 128 + row;                      // rows beyond P still own a row of the padded images
                 slabs_complete();
-                if (row == 0) {
-                    tc::tma_store_1d(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
-                    tc::tma_store_1d(a.tr_pex_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
-                    tc::tma_store_commit();
-                }
             }
             signal_act();
+            if (TRAIN) {
+                copy_out(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
+                copy_out(a.tr_pex_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
+            }
             for (int l = 0; l < 10; ++l) {
+                const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1 && half == 0;
+                if (pfe) a.prof[l * 8 + 3] = clock64();
                 tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
-                if (TRAIN) stores_read_out();
-                if (l == 7) epilogue_unit_x3<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                else if (l == 9) epilogue_unit_x3<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                else epilogue_unit_x3<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st);
-                if (l == 4) encode_dir_row<true>(a, row, pe_addr, st);     // unit 4 was the last reader of the position slabs
+                if (pfe) a.prof[l * 8 + 4] = clock64();
+                if (l == 7) epilogue_unit_x3<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
+                else if (l == 9) epilogue_unit_x3<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
+                else epilogue_unit_x3<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
+                if (l == 4 && half == 0) encode_dir_row<true>(a, row, pe_addr, st);     // unit 4 was the last reader of the position slabs
+                if (pfe) a.prof[l * 8 + 5] = clock64();
+                if (TRAIN) slabs_complete();
+                if (l < 9) signal_act();
+                if (pfe) a.prof[l * 8 + 6] = clock64();
                 if (TRAIN) {
-                    slabs_complete();
-                    if (row == 0) {
-                        const size_t img = ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
-                        tc::tma_store_1d(a.tr_act + img, act_addr, 4 * TC_SLAB_BYTES);
-                        tc::tma_store_1d(a.tr_act_lo + img, act_addr + 65536, 4 * TC_SLAB_BYTES);
-                        if (l == 4) {
-                            tc::tma_store_1d(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
-                            tc::tma_store_1d(a.tr_ped_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
-                        }
-                        tc::tma_store_commit();
+                    const size_t img = ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
+                    copy_out(a.tr_act + img, act_addr, 4 * TC_SLAB_BYTES);
+                    copy_out(a.tr_act_lo + img, act_addr + 65536, 4 * TC_SLAB_BYTES);
+                    if (l == 4) {
+                        copy_out(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
+                        copy_out(a.tr_ped_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
                     }
                 }
-                if (l < 9) signal_act();
             }
         }
-        if (TRAIN && row == 0) tc::tma_store_wait_all0();
     }
     tc::tcgen05_fence_before();
     tc::cluster_sync_all();
@@ -306,6 +354,8 @@ int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool trai
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed + X.weight_bytes);
     static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
     a.wait_hint = wait_hint; a.prof = nullptr; a.ray_bias = nullptr;
+    static const bool want_prof = nerf_env_set("NERF_X3_PROF");   // debug timeline of CTA 0's second tile: allocates and synchronises, never on by default
+    if (want_prof) { NERF_CUDA(cudaMalloc(&a.prof, 80 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 80 * sizeof(long long))); }
     NERF_CUDA(train ? nerf_smem_opt_in<g1_fused_x3_kernel<true>>(TC_SMEM_BYTES) : nerf_smem_opt_in<g1_fused_x3_kernel<false>>(TC_SMEM_BYTES));
     const int sms = nerf_num_sms();
     const int pairs = (a.n_tiles + 1) / 2, clusters = pairs < sms / 2 ? pairs : sms / 2;
@@ -317,5 +367,17 @@ int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool trai
     if (train) NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel<true>, a));
     else NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_fused_x3_kernel<false>, a));
     NERF_CUDA_CHECK_LAUNCH();
+    if (a.prof) {
+        long long h[80];
+        NERF_CUDA(cudaStreamSynchronize(st));
+        NERF_CUDA(cudaMemcpy(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost));
+        const long long t0 = h[3];
+        for (int l = 0; l < 10; ++l) {
+            const long long* r = h + l * 8;
+            fprintf(stderr, "x3 fwd%s unit %d: mma wait act %lld..%lld issued %lld | epi: start %lld acc_ready %lld math done %lld signalled %lld\n",
+                    train ? " (train)" : "", l, r[0] - t0, r[1] - t0, r[2] - t0, r[3] - t0, r[4] - t0, r[5] - t0, r[6] - t0);
+        }
+        cudaFree(a.prof); a.prof = nullptr;
+    }
     return NERF_OK;
 }

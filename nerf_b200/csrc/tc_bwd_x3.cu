@@ -8,7 +8,10 @@
 // the second tile slot's shared memory of the bf16 kernel holds the lo parts here.
 //   warp 0     TMA producer of the transposed weight stages: per K-slab the hi stage, then the lo stage
 //   warp 1     MMA issuer (leader CTA) / weight-arrival relay (peer CTA)
-//   warps 2-5  LayerNorm + ReLU backward (thread = point row = TMEM lane), in fp32:
+//   warps 2-9  LayerNorm + ReLU backward in fp32, TWO threads per point row (warps w and w + 4 share a TMEM lane quarter;
+//              each takes 128 of the row's 256 columns, the two row sums are exchanged through shared memory): with one
+//              tile slot there is one such warp pair per SMSP, and a single warp per SMSP left every dependent
+//              instruction's latency exposed (ncu: 1.5 warps per SMSP, issue slots 20 % busy).
 //                  dz = mask * rstd * (g - mean(g) - n * mean(g n)),   n = n_hi + n_lo (forward's slab images),
 //              the mask is the forward's exact bitmask (8 words per row and unit, fused_tc_x3.cu);
 //              dz overwrites n in place as (hi, lo) = the A operands of the next MMAs and is bulk-stored for the
@@ -17,14 +20,16 @@
 // lo parts in 227 KB.  n_{l-1} is prefetched into L2 while the MMAs of unit l run.
 #include "tc_bwd_kernel.cuh"
 #include "tc_bwd_x3.cuh"
+#include <stdio.h>
 
-#define BX_THREADS 192
+#define BX_THREADS 320
 #define BX_RING 4
 #define BX_SM_HI 0                                    // 4 slabs: n_l hi -> dz_l hi
 #define BX_SM_LO 65536                                // 4 slabs: n_l lo -> dz_l lo
 #define BX_SM_RING (2 * 65536)                        // BX_RING x 16 KB weight stages
 #define BX_SM_VEC (BX_SM_RING + BX_RING * TC_STAGE_BYTES)      // head weights [4][256] fp32
-#define BX_SM_BAR (BX_SM_VEC + 4 * 256 * 4)
+#define BX_SM_XCH (BX_SM_VEC + 4 * 256 * 4)            // [128 rows][2 halves] float2: partial (sum g, sum g n)
+#define BX_SM_BAR (BX_SM_XCH + 128 * 2 * 8)
 #define BX_SM_TOTAL (BX_SM_BAR + 256)
 #define BX_SMEM_BYTES (BX_SM_TOTAL + 1024)
 
@@ -32,6 +37,20 @@
 __device__ __forceinline__ void sts128u(uint32_t addr, uint4 v) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+// The tile images move on the LSU path (LDGSTS in, st.global out), not through TMA: the SM's one TMA queue drains at
+// ~32 B/cycle, and with n in, dz out and the L2 prefetch on it (384 KB a unit) the 128 KB of weight stages queued behind
+// them and the MMAs ran at half rate (clock64 timeline, NERF_X3_PROF).
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(__cvta_generic_to_global(src)) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2_line(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(__cvta_generic_to_global(p))); }
+__device__ __forceinline__ uint4 lds128v(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
 // (hi, lo) bf16 pair of two fp32 values: hi = bf16(x), lo = bf16(x - hi)
 __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(x, y);
@@ -42,11 +61,12 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 
 // LayerNorm + ReLU backward of one unit for one row, fp32 throughout; dz replaces n in place as (hi, lo).
 // SRC: 0 = g from TMEM, 1 = g from TMEM + d_sigma * w'_sigma (unit 7), 2 = g = W'_c^T d_rgb (unit 9).
-// Two passes over the row (sums, then dz); TMEM is read in both.  Written for clarity, not for the last cycle: the
-// kernel's time goes to the three-product MMAs and the 256 KB of slab traffic per tile and unit.
+// Two passes over this thread's HALF of the row (columns 128 * half .. + 127): sums, exchanged with the other half's
+// thread, then dz; TMEM is read in both.
 template <int SRC>
 __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_addr, uint32_t lo_addr, uint32_t row, uint32_t hw_addr,
-                                                  const uint32_t (&mw)[8], float rstd, float ds, float dr, float dg, float db) {
+                                                  const uint32_t (&mw)[8], float rstd, float ds, float dr, float dg, float db,
+                                                  int half, uint32_t xch_addr) {
     uint32_t r[32];
     // g of the 8 columns ch*32 + i*8 .. +7 (rc = the chunk's 32 TMEM columns)
     auto grad8 = [&](const uint32_t (&rc)[32], int ch, int i, float (&g)[8]) {
@@ -82,7 +102,7 @@ __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_ad
     // ---- pass 1: sum g, sum g n   (two chains each)
     float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
 #pragma unroll 1
-    for (int ch = 0; ch < 8; ++ch) {
+    for (int ch = 4 * half; ch < 4 * half + 4; ++ch) {
         if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -95,11 +115,20 @@ __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_ad
             }
         }
     }
-    const float m1 = (s1a + s1b) * (1.0f / 256.f), m2 = (s2a + s2b) * (1.0f / 256.f);
+    // the other half's sums (named barrier 2: the 256 epilogue threads)
+    float p1 = s1a + s1b, p2 = s2a + s2b;
+    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(xch_addr + (row * 2 + half) * 8), "f"(p1), "f"(p2) : "memory");
+    tc::named_bar_sync(2, 256);
+    {
+        float o1, o2;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(o1), "=f"(o2) : "r"(xch_addr + (row * 2 + (half ^ 1)) * 8) : "memory");
+        p1 += o1; p2 += o2;
+    }
+    const float m1 = p1 * (1.0f / 256.f), m2 = p2 * (1.0f / 256.f);
     const float c0 = -rstd * m1, c1 = -rstd * m2;
     // ---- pass 2: dz = mask * (rstd g - rstd m1 - n rstd m2), (hi, lo) in place over (n_hi, n_lo)
 #pragma unroll 1
-    for (int ch = 0; ch < 8; ++ch) {
+    for (int ch = 4 * half; ch < 4 * half + 4; ++ch) {
         if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -127,7 +156,7 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
     const uint32_t bar0 = base + BX_SM_BAR;
     auto ring_full = [&](int s) { return bar0 + 8u * s; };
     auto ring_empty = [&](int s) { return bar0 + 8u * (BX_RING + s); };
-    const uint32_t act_ready = bar0 + 8u * (2 * BX_RING), acc_ready = bar0 + 8u * (2 * BX_RING + 1), n_full = bar0 + 8u * (2 * BX_RING + 2);
+    const uint32_t act_ready = bar0 + 8u * (2 * BX_RING), acc_ready = bar0 + 8u * (2 * BX_RING + 1);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + BX_SM_BAR + 8 * (2 * BX_RING + 3));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -140,7 +169,7 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
     for (int i = threadIdx.x; i < 4 * 256; i += BX_THREADS) hw_s[i] = a.vec[TC_VEC_HEADW + i];
     if (threadIdx.x == 0) {
         for (int s = 0; s < BX_RING; ++s) { tc::mbar_init(ring_full(s), leader ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
-        tc::mbar_init(act_ready, 8); tc::mbar_init(acc_ready, 1); tc::mbar_init(n_full, 1);
+        tc::mbar_init(act_ready, 16); tc::mbar_init(acc_ready, 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 256);
@@ -179,14 +208,18 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
             uint32_t it = 0, act_it = 0;
             for (int q = 0; q < n_my; ++q)
                 for (int l = 9; l >= 1; --l) {
+                    const bool pfm = a.prof && blockIdx.x == 0 && q == 1 && lane == 0;
+                    if (pfm) a.prof[l * 8 + 0] = clock64();
                     tc::mbar_wait_spin(act_ready, act_it & 1, a.wait_hint); ++act_it;
                     tc::tcgen05_fence_after();
+                    if (pfm) a.prof[l * 8 + 1] = clock64();
                     for (int ks = 0; ks < 4; ++ks)
                         for (int part = 0; part < 2; ++part, ++it) {
                             const int slot = it % BX_RING; const uint32_t ph = (it / BX_RING) & 1;
                             const uint32_t blo = ring_lo + slot * (TC_STAGE_BYTES >> 4);
                             const uint32_t ah = dzh_lo + ks * (TC_SLAB_BYTES >> 4), al = dzl_lo + ks * (TC_SLAB_BYTES >> 4);
                             tc::mbar_wait_spin(ring_full(slot), ph, a.wait_hint);
+                            if (pfm && l == 5) a.prof[80 + ks * 2 + part] = clock64();
                             if (tc::elect_one()) {
                                 if (part == 0) {                       // W_hi: with dz_hi, then with dz_lo
 #pragma unroll
@@ -202,6 +235,7 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
                             }
                             __syncwarp();
                         }
+                    if (pfm) a.prof[l * 8 + 2] = clock64();
                 }
         } else if (lane == 0) {
             // ===================== peer relay of weight arrivals =====================
@@ -216,28 +250,61 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
         }
     } else {
         // ===================== LayerNorm-backward epilogue group =====================
-        const uint32_t row = (warp & 3) * 32 + lane;
+        const uint32_t row = (warp & 3) * 32 + lane;                     // TMEM lane quarter = warp % 4: warps w and w + 4 share rows
+        const int half = (warp - 2) >> 2;                                // which 128 columns of the row this thread takes
         const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16);
-        const uint32_t hi_addr = base + BX_SM_HI, lo_addr = base + BX_SM_LO, hw_addr = base + BX_SM_VEC;
-        const bool io = row == 0;                                        // the group's bulk-copy thread
+        const uint32_t hi_addr = base + BX_SM_HI, lo_addr = base + BX_SM_LO, hw_addr = base + BX_SM_VEC, xch_addr = base + BX_SM_XCH;
+        const uint32_t et = threadIdx.x - 64;                            // 0..255 within the group: owner of the 16-byte chunks et + 256 j
         const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
         const size_t img = 4 * (size_t)TC_SLAB_BYTES;
-        uint32_t acc_it = 0, nf_it = 0;
+        uint32_t acc_it = 0;
         float hs0 = 0.f, hs1 = 0.f, hs2 = 0.f, hs3 = 0.f;
-        auto load_unit = [&](int l, int tile) {                          // n_l (hi, lo) of this tile -> the two buffers
-            tc::mbar_arrive_expect_tx(n_full, 2 * (uint32_t)img);
-            tc::tma_load_1d(hi_addr, a.act_hi + ((size_t)l * a.tr_tiles + tile) * img, (uint32_t)img, n_full);
-            tc::tma_load_1d(lo_addr, a.act_lo + ((size_t)l * a.tr_tiles + tile) * img, (uint32_t)img, n_full);
+        // n_l (hi, lo) of this tile -> the two buffers.  A thread writes only the chunks it read out in store_unit, so the
+        // refill needs no wait for the other threads' copies.
+        auto load_unit = [&](int l, int tile) {
+            const uint8_t* sh = a.act_hi + ((size_t)l * a.tr_tiles + tile) * img;
+            const uint8_t* sl = a.act_lo + ((size_t)l * a.tr_tiles + tile) * img;
+#pragma unroll 4
+            for (int j = 0; j < 16; ++j) {
+                const uint32_t o = ((uint32_t)j * 256u + et) * 16u;
+                cp_async16(hi_addr + o, sh + o); cp_async16(lo_addr + o, sl + o);
+            }
+            cp_async_wait_all();
+            tc::named_bar_sync(3, 256);
+        };
+        // dz_l -> HBM for the weight-gradient GEMM (while the MMAs read the same shared memory); n_{l-1} -> L2
+        auto store_unit = [&](int l, int tile) {
+            uint8_t* dh = a.dz_hi + ((size_t)l * a.tr_tiles + tile) * img;
+            uint8_t* dl = a.dz_lo + ((size_t)l * a.tr_tiles + tile) * img;
+#pragma unroll 1
+            for (int j0 = 0; j0 < 16; j0 += 4) {
+                uint4 vh[4], vl[4];
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const uint32_t o = ((uint32_t)(j0 + jj) * 256u + et) * 16u;
+                    vh[jj] = lds128v(hi_addr + o); vl[jj] = lds128v(lo_addr + o);
+                }
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj) {
+                    const uint32_t o = ((uint32_t)(j0 + jj) * 256u + et) * 16u;
+                    *reinterpret_cast<uint4*>(dh + o) = vh[jj]; *reinterpret_cast<uint4*>(dl + o) = vl[jj];
+                }
+            }
+            if (l > 0) {
+                const uint8_t* sh = a.act_hi + ((size_t)(l - 1) * a.tr_tiles + tile) * img;
+                const uint8_t* sl = a.act_lo + ((size_t)(l - 1) * a.tr_tiles + tile) * img;
+                prefetch_l2_line(sh + et * 128u); prefetch_l2_line(sh + (et + 256u) * 128u);
+                prefetch_l2_line(sl + et * 128u); prefetch_l2_line(sl + (et + 256u) * 128u);
+            }
         };
         for (int q = 0; q < n_my; ++q) {
             const int unit = me + q * G;
             const int tile = 2 * unit + (int)rank;
             const int64_t p = (int64_t)tile * 128 + row;
-            if (io) { tc::tma_store_wait_read0(); load_unit(9, tile); } // (dz_0 of the previous tile has been read out)
             float ds = 0.f, dr = 0.f, dg = 0.f, db = 0.f;
             if (p < a.P) { ds = a.d_sigma[p]; dr = a.d_rgb[p * 3]; dg = a.d_rgb[p * 3 + 1]; db = a.d_rgb[p * 3 + 2]; }
-            hs0 += ds; hs1 += dr; hs2 += dg; hs3 += db;
-            {   // small-operand images of (d_sigma, d_rgb), hi and lo: [16 point groups][2 column halves][8 points][8 columns] bf16
+            if (half == 0) { hs0 += ds; hs1 += dr; hs2 += dg; hs3 += db; }
+            if (half == 0) {   // small-operand images of (d_sigma, d_rgb), hi and lo: [16 point groups][2 column halves][8 points][8 columns] bf16
                 uint32_t h0, l0, h1, l1;
                 split2(ds, dr, h0, l0); split2(dg, db, h1, l1);
                 const size_t o = (size_t)tile * 4096 + (row >> 3) * 256 + (row & 7) * 16;
@@ -254,34 +321,30 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
                     const uint4 m0 = mp[0], m1 = mp[1];
                     mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
                 }
+                const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1 && half == 0;
+                if (pfe) a.prof[l * 8 + 3] = clock64();
                 if (l < 9) {
                     tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;     // g_l is in TMEM, the MMAs have consumed dz_{l+1}
                     tc::tcgen05_fence_after();
-                    if (io) { tc::tma_store_wait_read0(); load_unit(l, tile); }      // its store has been read out too: refill with n_l
                 }
-                tc::mbar_wait(n_full, nf_it & 1, a.wait_hint); ++nf_it;
-                if (l == 9) bwd_x3_epilogue_unit<2>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
-                else if (l == 7) bwd_x3_epilogue_unit<1>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
-                else bwd_x3_epilogue_unit<0>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db);
+                if (pfe) a.prof[l * 8 + 4] = clock64();
+                load_unit(l, tile);
+                if (pfe) a.prof[l * 8 + 5] = clock64();
+                if (l == 9) bwd_x3_epilogue_unit<2>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db, half, xch_addr);
+                else if (l == 7) bwd_x3_epilogue_unit<1>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db, half, xch_addr);
+                else bwd_x3_epilogue_unit<0>(taddr, hi_addr, lo_addr, row, hw_addr, mw, stt.x, ds, dr, dg, db, half, xch_addr);
+                if (pfe) a.prof[l * 8 + 6] = clock64();
                 tc::fence_proxy_async_smem();
-                tc::named_bar_sync(1, 128);                                       // dz_l complete in shared memory
+                tc::named_bar_sync(1, 256);                                       // dz_l complete in shared memory
+                if (pfe) a.prof[l * 8 + 7] = clock64();
                 if (l > 0) {
                     tc::tcgen05_fence_before();
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
                 }
-                if (io) {                                                         // dz_l -> HBM for the weight-gradient GEMM
-                    tc::tma_store_1d(a.dz_hi + ((size_t)l * a.tr_tiles + tile) * img, hi_addr, (uint32_t)img);
-                    tc::tma_store_1d(a.dz_lo + ((size_t)l * a.tr_tiles + tile) * img, lo_addr, (uint32_t)img);
-                    tc::tma_store_commit();
-                    if (l > 0) {                                                  // n_{l-1}: into L2 while the MMAs run
-                        tc::tma_prefetch_l2(a.act_hi + ((size_t)(l - 1) * a.tr_tiles + tile) * img, (uint32_t)img);
-                        tc::tma_prefetch_l2(a.act_lo + ((size_t)(l - 1) * a.tr_tiles + tile) * img, (uint32_t)img);
-                    }
-                }
+                store_unit(l, tile);
             }
         }
-        if (io) tc::tma_store_wait_all0();
         hs0 = warp_sum(hs0); hs1 = warp_sum(hs1); hs2 = warp_sum(hs2); hs3 = warp_sum(hs3);
         if (lane == 0 && n_my > 0) { atomicAdd(a.hsum, hs0); atomicAdd(a.hsum + 1, hs1); atomicAdd(a.hsum + 2, hs2); atomicAdd(a.hsum + 3, hs3); }
     }
@@ -301,7 +364,25 @@ int launch_bwd_x3(BwdX3Args& a, cudaStream_t st) {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
+    static const bool want_prof = nerf_env_set("NERF_X3_PROF");   // debug timeline: allocates and synchronises, never on by default
+    a.prof = nullptr;
+    if (want_prof) { NERF_CUDA(cudaMalloc(&a.prof, 96 * sizeof(long long))); NERF_CUDA(cudaMemset(a.prof, 0, 96 * sizeof(long long))); }
     NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_bwd_x3_kernel, a));
     NERF_CUDA_CHECK_LAUNCH();
+    if (a.prof) {
+        long long h[96];
+        NERF_CUDA(cudaStreamSynchronize(st));
+        NERF_CUDA(cudaMemcpy(h, a.prof, sizeof(h), cudaMemcpyDeviceToHost));
+        const long long t0 = h[9 * 8 + 3];
+        for (int l = 9; l >= 0; --l) {
+            const long long* r = h + l * 8;
+            fprintf(stderr, "x3 bwd unit %d: mma wait act %lld..%lld issued %lld | epi: start %lld acc_ready %lld n_full %lld math done %lld synced %lld\n",
+                    l, r[0] - t0, r[1] - t0, r[2] - t0, r[3] - t0, r[4] - t0, r[5] - t0, r[6] - t0, r[7] - t0);
+        }
+        fprintf(stderr, "x3 bwd unit 5 stage waits passed at:");
+        for (int j = 0; j < 8; ++j) fprintf(stderr, " %lld", h[80 + j] - t0);
+        fprintf(stderr, "\n");
+        cudaFree(a.prof);
+    }
     return NERF_OK;
 }

@@ -14,6 +14,7 @@ struct BwdX3Args {
     float* hsum;                                          // [4] += sums of (d_sigma, d_rgb)
     int64_t P, P_pad; int n_tiles, tr_tiles;
     uint32_t wait_hint;
+    long long* prof;                                      // NERF_X3_PROF: clock64 stamps of CTA 0, its second tile: [unit][8]
 };
 
 int launch_bwd_x3(BwdX3Args& a, cudaStream_t st);

@@ -113,8 +113,11 @@ def test_unmodified_reference_train_script_reaches_tcgen05(tmp_path, nerf_pth_st
     assert imgs.shape == (4, 1, h, w, 3) and json.load(open(logdir / "params.json"))["batch_size"] == batch
 
 
-def test_unmodified_notebook_cells_reach_tcgen05(tmp_path, monkeypatch, nerf_pth_state_dict):
+@pytest.mark.parametrize("precision", ["bf16", "bf16x3"])
+def test_unmodified_notebook_cells_reach_tcgen05(tmp_path, monkeypatch, nerf_pth_state_dict, precision):
+    """example.ipynb cells 0-9 as they are, on the bf16 tensor-core step and on the fp32-grade one (bf16x3)"""
     cells = _reference_cells()
+    fam = "tc" if precision == "bf16" else "x3"
     for i, sha in CELL_SHA.items():
         assert hashlib.sha256(cells[i].encode()).hexdigest() == sha, f"cell {i} is not the reference's"
     from nerf_b200 import ops
@@ -130,7 +133,7 @@ def test_unmodified_notebook_cells_reach_tcgen05(tmp_path, monkeypatch, nerf_pth
         images = teacher.render_image(poses[:, :3, 3].cuda(), poses[:, :3, :3].cuda(), h, w, focal, 2.0, 6.0, 64).cpu().numpy()
     np.savez(tmp_path / "tiny_nerf_data.npz", images=images, poses=poses.numpy(), focal=np.float64(focal))
     monkeypatch.chdir(tmp_path)
-    monkeypatch.setenv("NERF_B200_PRECISION", "bf16")
+    monkeypatch.setenv("NERF_B200_PRECISION", precision)
     plt = types.ModuleType("matplotlib.pyplot")                     # matplotlib is not installed: the plotting calls become no-ops
     for name in ("figure", "subplot", "title", "imshow", "plot", "show", "close"):
         setattr(plt, name, lambda *a, **k: None)
@@ -141,17 +144,17 @@ def test_unmodified_notebook_cells_reach_tcgen05(tmp_path, monkeypatch, nerf_pth
     ns = {"__name__": "__notebook__"}
     for i in range(10):                                             # cells 0-9: imports, data, dataset, model, optimiser, the loop, the save
         exec(compile(cells[i], f"<example.ipynb cell {i}>", "exec"), ns)
-    fwd = ops.COUNTERS["g1_train_fwd_tc"] - before.get("g1_train_fwd_tc", 0)
-    bwd = ops.COUNTERS["g1_train_bwd_tc"] - before.get("g1_train_bwd_tc", 0)
+    fwd = ops.COUNTERS[f"g1_train_fwd_{fam}"] - before.get(f"g1_train_fwd_{fam}", 0)
+    bwd = ops.COUNTERS[f"g1_train_bwd_{fam}"] - before.get(f"g1_train_bwd_{fam}", 0)
     assert fwd == bwd == 100, (fwd, bwd)                            # 100 epochs x 1 batch of (n-1)*144 = 576 pixels
     assert ops.COUNTERS["g1_mlp_fwd_fp32"] == before.get("g1_mlp_fwd_fp32", 0)     # nothing fell to the FFMA path
     nerf = ns["nerf"]
-    assert nerf.precision == "bf16" and ns["iteration"] == 99
+    assert nerf.precision == precision and ns["iteration"] == 99
     with torch.no_grad():
         out = nerf.render_image(ns["test_pose"][..., :3, 3], ns["test_pose"][..., :3, :3], h, w, focal, 2.0, 6.0, 64)
         psnr_end = (-10.0 * torch.log(((out - ns["test_image"]) ** 2).mean()) / 2.30258509299).item()
     psnr_0 = float(ns["psnrs"][0])
-    print(f"notebook loop on tcgen05: held-out PSNR {psnr_0:.2f} dB after 1 step -> {psnr_end:.2f} dB after 100")
+    print(f"notebook loop on tcgen05 ({precision}): held-out PSNR {psnr_0:.2f} dB after 1 step -> {psnr_end:.2f} dB after 100")
     assert psnr_end > psnr_0 + 0.3
     sd = torch.load(tmp_path / "nerf.pth", map_location="cpu")      # cell 9
     assert list(sd.keys()) == list(nerf_pth_state_dict.keys())
