@@ -290,14 +290,26 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
         // the slabs.  The next writer of a slab is a pass 2 or an encoder at least one exchange barrier later, and a thread
         // reaches that barrier only after its own copies have been read out (the loads feed its stores).
         auto slabs_complete = [&]() { tc::fence_proxy_async_smem(); tc::named_bar_sync(1, 256); };
-        auto copy_out = [&](uint8_t* dst, uint32_t src, uint32_t bytes) {
+        // (the HBM images interleave hi and lo in 4 KB pieces of 32 points: tc_layout.cuh, "slab images of the bf16x3 step")
+        auto copy_hidden = [&](uint8_t* img) {                     // the 4 activation slabs, both parts
 #pragma unroll 1
-            for (uint32_t o = et * 16u; o < bytes; o += 4u * 4096u) {
+            for (uint32_t g = 0; g < 8; ++g) {
+                const uint32_t part = g >> 2, o = (g & 3u) * 4u * 4096u + et * 16u;
                 uint4 v[4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v[k] = lds128v(src + o + k * 4096u);
+                for (uint32_t k = 0; k < 4; ++k) v[k] = lds128v(act_addr + part * 65536u + o + k * 4096u);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(dst + o + k * 4096u) = v[k];
+                for (uint32_t k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(img + x3_img_offset(o + k * 4096u, part)) = v[k];
+            }
+        };
+        auto copy_enc = [&](uint8_t* img) {                        // the encoding slab, both parts
+#pragma unroll
+            for (uint32_t part = 0; part < 2; ++part) {
+                uint4 v[4];
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) v[k] = lds128v(pe_addr + part * TC_SLAB_BYTES + et * 16u + k * 4096u);
+#pragma unroll
+                for (uint32_t k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(img + x3_enc_img_offset(et * 16u + k * 4096u, part)) = v[k];
             }
         };
         for (int q = 0; q < n_my; ++q) {
@@ -311,10 +323,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                 slabs_complete();
             }
             signal_act();
-            if (TRAIN) {
-                copy_out(a.tr_pex + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
-                copy_out(a.tr_pex_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
-            }
+            if (TRAIN) copy_enc(a.tr_pex + (size_t)tile * X3_ENC_IMG_BYTES);
             for (int l = 0; l < 10; ++l) {
                 const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1 && half == 0;
                 if (pfe) a.prof[l * 8 + 3] = clock64();
@@ -330,13 +339,8 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                 if (l < 9) signal_act();
                 if (pfe) a.prof[l * 8 + 6] = clock64();
                 if (TRAIN) {
-                    const size_t img = ((size_t)l * a.tr_tiles + tile) * (4 * TC_SLAB_BYTES);
-                    copy_out(a.tr_act + img, act_addr, 4 * TC_SLAB_BYTES);
-                    copy_out(a.tr_act_lo + img, act_addr + 65536, 4 * TC_SLAB_BYTES);
-                    if (l == 4) {
-                        copy_out(a.tr_ped + (size_t)tile * TC_SLAB_BYTES, pe_addr, TC_SLAB_BYTES);
-                        copy_out(a.tr_ped_lo + (size_t)tile * TC_SLAB_BYTES, pe_addr + TC_SLAB_BYTES, TC_SLAB_BYTES);
-                    }
+                    copy_hidden(a.tr_act + ((size_t)l * a.tr_tiles + tile) * X3_IMG_BYTES);
+                    if (l == 4) copy_enc(a.tr_ped + (size_t)tile * X3_ENC_IMG_BYTES);
                 }
             }
         }

@@ -256,26 +256,24 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
         const uint32_t hi_addr = base + BX_SM_HI, lo_addr = base + BX_SM_LO, hw_addr = base + BX_SM_VEC, xch_addr = base + BX_SM_XCH;
         const uint32_t et = threadIdx.x - 64;                            // 0..255 within the group: owner of the 16-byte chunks et + 256 j
         const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
-        const size_t img = 4 * (size_t)TC_SLAB_BYTES;
         uint32_t acc_it = 0;
         float hs0 = 0.f, hs1 = 0.f, hs2 = 0.f, hs3 = 0.f;
         // n_l (hi, lo) of this tile -> the two buffers.  A thread writes only the chunks it read out in store_unit, so the
         // refill needs no wait for the other threads' copies.
+        // (HBM images: hi and lo interleaved in 4 KB pieces of 32 points, tc_layout.cuh)
         auto load_unit = [&](int l, int tile) {
-            const uint8_t* sh = a.act_hi + ((size_t)l * a.tr_tiles + tile) * img;
-            const uint8_t* sl = a.act_lo + ((size_t)l * a.tr_tiles + tile) * img;
+            const uint8_t* img = a.act + ((size_t)l * a.tr_tiles + tile) * X3_IMG_BYTES;
 #pragma unroll 4
             for (int j = 0; j < 16; ++j) {
                 const uint32_t o = ((uint32_t)j * 256u + et) * 16u;
-                cp_async16(hi_addr + o, sh + o); cp_async16(lo_addr + o, sl + o);
+                cp_async16(hi_addr + o, img + x3_img_offset(o, 0)); cp_async16(lo_addr + o, img + x3_img_offset(o, 1));
             }
             cp_async_wait_all();
             tc::named_bar_sync(3, 256);
         };
         // dz_l -> HBM for the weight-gradient GEMM (while the MMAs read the same shared memory); n_{l-1} -> L2
         auto store_unit = [&](int l, int tile) {
-            uint8_t* dh = a.dz_hi + ((size_t)l * a.tr_tiles + tile) * img;
-            uint8_t* dl = a.dz_lo + ((size_t)l * a.tr_tiles + tile) * img;
+            uint8_t* img = a.dz + ((size_t)l * a.tr_tiles + tile) * X3_IMG_BYTES;
 #pragma unroll 1
             for (int j0 = 0; j0 < 16; j0 += 4) {
                 uint4 vh[4], vl[4];
@@ -287,14 +285,13 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
 #pragma unroll
                 for (int jj = 0; jj < 4; ++jj) {
                     const uint32_t o = ((uint32_t)(j0 + jj) * 256u + et) * 16u;
-                    *reinterpret_cast<uint4*>(dh + o) = vh[jj]; *reinterpret_cast<uint4*>(dl + o) = vl[jj];
+                    *reinterpret_cast<uint4*>(img + x3_img_offset(o, 0)) = vh[jj]; *reinterpret_cast<uint4*>(img + x3_img_offset(o, 1)) = vl[jj];
                 }
             }
             if (l > 0) {
-                const uint8_t* sh = a.act_hi + ((size_t)(l - 1) * a.tr_tiles + tile) * img;
-                const uint8_t* sl = a.act_lo + ((size_t)(l - 1) * a.tr_tiles + tile) * img;
-                prefetch_l2_line(sh + et * 128u); prefetch_l2_line(sh + (et + 256u) * 128u);
-                prefetch_l2_line(sl + et * 128u); prefetch_l2_line(sl + (et + 256u) * 128u);
+                const uint8_t* nx = a.act + ((size_t)(l - 1) * a.tr_tiles + tile) * X3_IMG_BYTES;
+                prefetch_l2_line(nx + et * 128u); prefetch_l2_line(nx + (et + 256u) * 128u);
+                prefetch_l2_line(nx + (et + 512u) * 128u); prefetch_l2_line(nx + (et + 768u) * 128u);
             }
         };
         for (int q = 0; q < n_my; ++q) {
@@ -307,11 +304,11 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
             if (half == 0) {   // small-operand images of (d_sigma, d_rgb), hi and lo: [16 point groups][2 column halves][8 points][8 columns] bf16
                 uint32_t h0, l0, h1, l1;
                 split2(ds, dr, h0, l0); split2(dg, db, h1, l1);
-                const size_t o = (size_t)tile * 4096 + (row >> 3) * 256 + (row & 7) * 16;
-                *reinterpret_cast<uint4*>(a.dh_hi + o) = make_uint4(h0, h1, 0u, 0u);
-                *reinterpret_cast<uint4*>(a.dh_hi + o + 128) = make_uint4(0u, 0u, 0u, 0u);
-                *reinterpret_cast<uint4*>(a.dh_lo + o) = make_uint4(l0, l1, 0u, 0u);
-                *reinterpret_cast<uint4*>(a.dh_lo + o + 128) = make_uint4(0u, 0u, 0u, 0u);
+                uint8_t* dh = a.dh + (size_t)tile * X3_DH_IMG_BYTES;
+                *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 0, 0)) = make_uint4(h0, h1, 0u, 0u);
+                *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 1, 0)) = make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 0, 1)) = make_uint4(l0, l1, 0u, 0u);
+                *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 1, 1)) = make_uint4(0u, 0u, 0u, 0u);
             }
             for (int l = 9; l >= 0; --l) {
                 const float2 stt = a.stats[(int64_t)l * a.P_pad + p];

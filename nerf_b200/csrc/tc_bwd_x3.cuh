@@ -5,12 +5,12 @@
 struct BwdX3Args {
     const uint8_t* stages_hi; const uint8_t* stages_lo;   // transposed weight stages, unit l in 1..9 -> 8 stages at (l-1)*8 (tc_train.cu layout)
     const float* vec;                                     // forward epilogue vectors (head weights with gamma folded)
-    const uint8_t* act_hi; const uint8_t* act_lo;         // [10][tr_tiles][4 slabs]
+    const uint8_t* act;                                   // [10][tr_tiles] hidden images (hi and lo interleaved, tc_layout.cuh)
     const uint32_t* mask;                                 // [10][P_pad][8] words: ReLU mask, bit = column active
     const float2* stats;                                  // [10][P_pad] (rstd, -mean*rstd)
     const float* d_sigma; const float* d_rgb;
-    uint8_t* dz_hi; uint8_t* dz_lo;                       // [10][tr_tiles][4 slabs] out
-    uint8_t* dh_hi; uint8_t* dh_lo;                       // [tr_tiles][4 KB] out: (d_sigma, d_rgb) small-operand images
+    uint8_t* dz;                                          // [10][tr_tiles] hidden images out
+    uint8_t* dh;                                          // [tr_tiles] small-operand images out: (d_sigma, d_rgb)
     float* hsum;                                          // [4] += sums of (d_sigma, d_rgb)
     int64_t P, P_pad; int n_tiles, tr_tiles;
     uint32_t wait_hint;

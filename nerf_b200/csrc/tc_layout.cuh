@@ -131,20 +131,45 @@ static inline void make_train_layout(int64_t B, int S, TrainLayout& T, int Dx = 
 
 // ---- workspace of the fp32-grade ("bf16x3") training step (tc_train_x3.cu): the bf16 step's layout holds the hi parts,
 // a second set of images behind it the lo parts (activations, dz, the two encodings, the (d_sigma, d_rgb) image)
+// The (hi, lo) slab images of the bf16x3 step in HBM.  In shared memory a tile's image is 4 slabs (hidden) or 1 slab (encoding)
+// of [128 points x 128 B], hi and lo in separate buffers; in HBM the two parts are interleaved in 4 KB pieces of 32 points:
+//     hidden    [unit][tile][quarter q = point / 32][slab s][part hi|lo][4096 B]        128 KB per (unit, tile)
+//     encoding        [tile][quarter q][part][4096 B]                                    32 KB per tile
+//     small operand   [tile][quarter q][part][1024 B]    ((d_sigma, d_rgb) rows: 8 points x 2 column halves x 16 B)
+// so that the weight-gradient GEMM, whose contraction runs over the points, fetches a 32-point stage of one CTA (2 slabs x
+// 2 parts) as ONE 16 KB bulk copy.  The forward and data-gradient kernels move the images as 16-byte thread chunks and apply
+// the permutation for free.
+#define X3_IMG_BYTES (8 * TC_SLAB_BYTES)      // hidden image of one (unit, tile), both parts
+#define X3_ENC_IMG_BYTES (2 * TC_SLAB_BYTES)
+#define X3_DH_IMG_BYTES 8192
+// byte offset inside a hidden image of the 16-byte chunk at offset o (o < 65536) of the shared-memory part `part`
+__host__ __device__ static inline uint32_t x3_img_offset(uint32_t o, uint32_t part) {
+    return ((((o >> 12) & 3u) * 4u + (o >> 14)) * 2u + part) * 4096u + (o & 4095u);
+}
+// ... inside an encoding image (o < 16384)
+__host__ __device__ static inline uint32_t x3_enc_img_offset(uint32_t o, uint32_t part) { return ((o >> 12) * 2u + part) * 4096u + (o & 4095u); }
+// ... of point row `row`'s 16-byte entry (column half `ch`) inside a small-operand image
+__host__ __device__ static inline uint32_t x3_dh_img_offset(uint32_t row, uint32_t ch, uint32_t part) {
+    return ((row >> 5) * 2u + part) * 1024u + ((row >> 3) & 3u) * 256u + ch * 128u + (row & 7u) * 16u;
+}
+
 struct X3TrainLayout {
-    TrainLayout T;
-    int64_t off_act_lo, off_dz_lo, off_pex_lo, off_ped_lo, off_dh_lo, total;
+    TrainLayout T;       // the fp32 outputs, statistics and flags of the bf16 step; its slab-image regions are re-cut below
+    int64_t off_act3, off_dz3;     // [10][tr_tiles] hidden images
+    int64_t off_pex3, off_ped3;    // [tr_tiles] encoding images
+    int64_t off_dh3;               // [tr_tiles] small-operand images
     int64_t off_mask;    // [10][P_pad][8] uint32: the ReLU mask of every unit, one bit per column (bit c & 31 of word c >> 5)
+    int64_t total;
 };
 static inline void make_x3_train_layout(int64_t B, int S, X3TrainLayout& X) {
     make_train_layout(B, S, X.T, 3);
     int64_t o = X.T.total;
-    const int64_t unit_images = 10ll * X.T.tr_tiles * 4 * TC_SLAB_BYTES;
-    X.off_act_lo = o; o += unit_images;
-    X.off_dz_lo = o; o += unit_images;
-    X.off_pex_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
-    X.off_ped_lo = o; o += (int64_t)X.T.tr_tiles * TC_SLAB_BYTES;
-    X.off_dh_lo = o; o += (int64_t)X.T.tr_tiles * 4096;
+    const int64_t unit_images = 10ll * X.T.tr_tiles * X3_IMG_BYTES;
+    X.off_act3 = X.T.off_act;                       // T's act and dz regions are adjacent: together one x3 region
+    X.off_dz3 = o; o += unit_images;
+    X.off_pex3 = X.T.off_pex;                       // likewise T's pex and ped
+    X.off_ped3 = o; o += (int64_t)X.T.tr_tiles * X3_ENC_IMG_BYTES;
+    X.off_dh3 = o; o += (int64_t)X.T.tr_tiles * X3_DH_IMG_BYTES;
     X.off_mask = o; o += 10ll * X.T.P_pad * 32;
     X.total = o;
 }

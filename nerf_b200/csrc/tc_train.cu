@@ -400,8 +400,7 @@ extern "C" int nerf_g1_train_fwd_x3(const void* packed_x3, const float* rays_o, 
     a.t_in = t_in; a.t_base = t_base; a.u = u; a.jitter = (jitter || u) ? 1 : 0; a.seed = seed; a.ray_id_base = ray_id_base;
     a.near_plane = near_plane; a.far_plane = far_plane; a.norm = normalize_position; a.normalize_dir = normalize_direction;
     a.out_t = out_t; a.out_sigma = out_sigma; a.out_rgb = out_rgb; a.dbg = nullptr; a.dbg_layer = -1;
-    a.tr_act = ws + T.off_act; a.tr_pex = ws + T.off_pex; a.tr_ped = ws + T.off_ped;
-    a.tr_act_lo = ws + X.off_act_lo; a.tr_pex_lo = ws + X.off_pex_lo; a.tr_ped_lo = ws + X.off_ped_lo;
+    a.tr_act = ws + X.off_act3; a.tr_pex = ws + X.off_pex3; a.tr_ped = ws + X.off_ped3;     // interleaved (hi, lo) images
     a.tr_mask = reinterpret_cast<uint32_t*>(ws + X.off_mask);
     a.tr_stats = reinterpret_cast<float2*>(ws + T.off_stats); a.P_pad = T.P_pad; a.tr_tiles = T.tr_tiles;
     return launch_fused_x3(packed_x3, a, (cudaStream_t)stream, true);
@@ -423,9 +422,9 @@ extern "C" int nerf_g1_train_bwd_x3(const void* packed_x3, const void* packed_bw
     BwdX3Args a{};
     a.stages_hi = (const uint8_t*)packed_bwd_x3; a.stages_lo = a.stages_hi + 72ll * TC_STAGE_BYTES;
     a.vec = reinterpret_cast<const float*>((const uint8_t*)packed_x3 + XL.weight_bytes);
-    a.act_hi = ws + T.off_act; a.act_lo = ws + X.off_act_lo; a.mask = reinterpret_cast<const uint32_t*>(ws + X.off_mask); a.stats = reinterpret_cast<const float2*>(ws + T.off_stats);
-    a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz_hi = ws + T.off_dz; a.dz_lo = ws + X.off_dz_lo;
-    a.dh_hi = ws + T.off_dh; a.dh_lo = ws + X.off_dh_lo; a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
+    a.act = ws + X.off_act3; a.mask = reinterpret_cast<const uint32_t*>(ws + X.off_mask); a.stats = reinterpret_cast<const float2*>(ws + T.off_stats);
+    a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dz = ws + X.off_dz3;
+    a.dh = ws + X.off_dh3; a.hsum = reinterpret_cast<float*>(ws + T.off_hsum);
     a.P = T.P; a.P_pad = T.P_pad; a.n_tiles = T.n_tiles; a.tr_tiles = T.tr_tiles;
     rc = launch_bwd_x3(a, st); if (rc) return rc;
     if (stage == 1) return NERF_OK;

@@ -354,35 +354,249 @@ int launch_wgrad_tc_units(const uint8_t* ws, const TrainLayout& T, cudaStream_t 
     return launch_wgrad_tc(a, st);
 }
 
-// fp32-grade weight gradients (bf16x3 training): dZ^T X ~= dZ_hi^T X_hi + dZ_lo^T X_hi + dZ_hi^T X_lo -- three launches of the
-// same GEMM over the hi / lo slab images, accumulating into the same fp32 outputs.  The column sums of dZ (bias gradients)
-// come from the "ones" columns: dZ_hi in the first launch, dZ_lo in the second, not flushed in the third.
+// ------------------------------------------------------------------------------------------------------------------
+// fp32-grade weight gradients (bf16x3 training):   dZ^T X  ~=  dZ_hi^T X_hi + dZ_lo^T X_hi + dZ_hi^T X_lo
+// in ONE pass over the interleaved (hi, lo) images (tc_layout.cuh): the four operand parts of a stage are fetched once and
+// feed three MMAs per K-step into the same accumulators.  (Three launches of the bf16 GEMM, one per product, read every
+// part twice -- 8.1 GB for 5.4 GB of images at 4096 x 64 -- and ran at the HBM roof.)
+// A stage covers 32 points: [A: 2 slabs x (hi | lo) x 4 KB] [B: the same of the hidden input, or the small operand (hi | lo)
+// x 1 KB] [E: encoding (hi | lo) x 4 KB, leader CTA; the peer's E_hi holds ones, its E_lo zeros] = 40 KB, two or three bulk
+// copies; five stages in flight.  Column sums of dZ (bias gradients): the ones see dZ_hi and dZ_lo.
+#define W3_STAGES 5
+#define W3_PIECE 4096
+#define W3_OFF_B (4 * W3_PIECE)
+#define W3_OFF_E (8 * W3_PIECE)
+#define W3_STAGE_BYTES (10 * W3_PIECE)
+#define W3_SM_ONES (W3_STAGES * W3_STAGE_BYTES)
+#define W3_SM_BAR (W3_SM_ONES + 1024)
+#define W3_SM_SEGS (W3_SM_BAR + 128)
+#define W3_SM_TOTAL (W3_SM_SEGS + WG_MAX_SEGS * 16)
+#define W3_SMEM_BYTES (W3_SM_TOTAL + 1024)
+
+struct WgradX3Args {
+    const uint8_t* dz[WG_NU];        // [n_tiles] hidden images: the M operand (null = absent)
+    const uint8_t* xmain[WG_NU];     // [n_tiles] hidden images: hidden input of unit l (null = none)
+    const uint8_t* xenc[WG_NU];      // [n_tiles] encoding images (null = none)
+    const uint8_t* xsmall[WG_NU];    // [n_tiles] small-operand images (null = none; excludes xmain)
+    float* out[WG_NU];
+    int ld[WG_NU];
+    int ones[WG_NU];
+    int n_tiles;
+    uint32_t wait_hint;
+};
+// relative time per tile: the pass is HBM-bound, so the bytes a pair fetches (in KB) plus ~4 KB worth of issue time per copy
+__host__ __device__ inline int w3_cost(const WgradX3Args& a, int l) {
+    return 64 + 8 + (a.xmain[l] ? 64 + 8 : 0) + (a.xenc[l] ? 16 + 4 : 0) + (a.xsmall[l] ? 4 + 8 : 0);
+}
+
+__global__ void __launch_bounds__(WG_THREADS, 1) g1_wgrad_x3_kernel(const WgradX3Args a) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = tc::smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* sm = smem_raw + (base - raw);
+    const uint32_t bar0 = base + W3_SM_BAR;
+    auto full = [&](int s) { return bar0 + 8u * s; };
+    auto empty = [&](int s) { return bar0 + 8u * (W3_STAGES + s); };
+    const uint32_t acc_done = bar0 + 8u * (2 * W3_STAGES), acc_free = bar0 + 8u * (2 * W3_STAGES + 1);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + W3_SM_BAR + 8 * (2 * W3_STAGES + 2));
+    volatile int* n_segs_s = reinterpret_cast<volatile int*>(sm + W3_SM_BAR + 8 * (2 * W3_STAGES + 2) + 4);
+    WgSeg* segs = reinterpret_cast<WgSeg*>(sm + W3_SM_SEGS);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const bool leader = rank == 0;
+    const int n_pairs = gridDim.x >> 1, pair = blockIdx.x >> 1;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < W3_STAGES; ++s) { tc::mbar_init(full(s), leader ? 2 : 1); tc::mbar_init(empty(s), 1); }
+        tc::mbar_init(acc_done, 1); tc::mbar_init(acc_free, 8);
+        tc::fence_barrier_init();
+        int64_t total = 0;                                          // equal-cost contiguous cut of the (unit, tile) list, as above
+        for (int l = 0; l < WG_NU; ++l) if (a.dz[l]) total += (int64_t)a.n_tiles * w3_cost(a, l);
+        const int64_t lo = total * pair / n_pairs, hi = total * (pair + 1) / n_pairs;
+        int n = 0; int64_t pre = 0;
+        for (int l = 0; l < WG_NU; ++l) {
+            if (!a.dz[l]) continue;
+            const int64_t c = w3_cost(a, l);
+            const int64_t end = pre + c * a.n_tiles;
+            const int64_t s0 = lo > pre ? lo : pre, s1 = hi < end ? hi : end;
+            if (s1 > s0) {
+                const int tb = (int)((s0 - pre + c - 1) / c), te = (int)((s1 - pre + c - 1) / c);
+                if (te > tb && n < WG_MAX_SEGS) { segs[n].l = l; segs[n].tb = tb; segs[n].te = te; ++n; }
+            }
+            pre = end;
+        }
+        *n_segs_s = n;
+    }
+    for (int i = threadIdx.x; i < 256; i += WG_THREADS) reinterpret_cast<uint32_t*>(sm + W3_SM_ONES)[i] = 0x3F803F80u;
+    if (!leader)                                                    // the peer's share of the [encoding | ones] operand: ones against hi, zeros against lo
+        for (int s = 0; s < W3_STAGES; ++s)
+            for (int i = threadIdx.x; i < 2 * W3_PIECE / 4; i += WG_THREADS)
+                reinterpret_cast<uint32_t*>(sm + s * W3_STAGE_BYTES + W3_OFF_E)[i] = i < W3_PIECE / 4 ? 0x3F803F80u : 0u;
+    tc::fence_proxy_async_smem();
+    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 512);
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    tc::tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_segs = *n_segs_s;
+
+    if (warp == 0) {
+        // ===================== TMA producer: this CTA's two slabs (hi, lo) of both operands, 32 points a stage =====================
+        uint32_t it = 0;
+        for (int si = 0; si < n_segs; ++si) {
+            const WgSeg sg = segs[si];
+            const uint8_t* xm = a.xmain[sg.l]; const uint8_t* xs = a.xsmall[sg.l];
+            const uint8_t* xe = leader ? a.xenc[sg.l] : nullptr;
+            const uint32_t bytes = 4 * W3_PIECE + (xm ? 4 * W3_PIECE : 0) + (xe ? 2 * W3_PIECE : 0) + (xs ? 2048 : 0);
+            const size_t mine = (size_t)rank * 4 * W3_PIECE;                    // slabs 2 rank, 2 rank + 1 inside a quarter
+            const uint8_t* pa = a.dz[sg.l] + (size_t)sg.tb * X3_IMG_BYTES + mine;
+            const uint8_t* pm = xm ? xm + (size_t)sg.tb * X3_IMG_BYTES + mine : nullptr;
+            const uint8_t* pe = xe ? xe + (size_t)sg.tb * X3_ENC_IMG_BYTES : nullptr;
+            const uint8_t* ps = xs ? xs + (size_t)sg.tb * X3_DH_IMG_BYTES : nullptr;
+            for (int n = 4 * (sg.te - sg.tb); n > 0; --n, ++it) {
+                const int slot = it % W3_STAGES; const uint32_t ph = (it / W3_STAGES) & 1;
+                tc::mbar_wait(empty(slot), ph ^ 1, a.wait_hint);
+                const uint32_t st = base + slot * W3_STAGE_BYTES, fb = full(slot);
+                if (tc::elect_one()) {
+                    tc::mbar_arrive_expect_tx(fb, bytes);
+                    tc::tma_load_1d(st, pa, 4 * W3_PIECE, fb);
+                    if (pm) tc::tma_load_1d(st + W3_OFF_B, pm, 4 * W3_PIECE, fb);
+                    if (pe) tc::tma_load_1d(st + W3_OFF_E, pe, 2 * W3_PIECE, fb);
+                    if (ps) tc::tma_load_1d(st + W3_OFF_B, ps, 2048, fb);
+                }
+                __syncwarp();
+                pa += 8 * W3_PIECE; if (pm) pm += 8 * W3_PIECE; if (pe) pe += 2 * W3_PIECE; if (ps) ps += 2048;   // next quarter (tiles are contiguous)
+            }
+        }
+    } else if (warp == 1) {
+        if (leader) {
+            // ===================== MMA issuer: per K-step (16 points) three products per accumulator =====================
+            constexpr uint32_t idesc_main = tc::umma_idesc_bf16_mn(256, 256), idesc_enc = tc::umma_idesc_bf16_mn(256, 128);
+            constexpr uint32_t idesc_32 = tc::umma_idesc_bf16_mn(256, 32);
+            constexpr uint32_t hi_sw = (1024u >> 4) | (1u << 14) | (2u << 29), hi_ns = (128u >> 4) | (1u << 14);
+            constexpr uint32_t lbo_slab = (uint32_t)(2 * W3_PIECE >> 4) << 16;     // next 64-feature atom = next slab of the stage: hi|lo pieces apart
+            constexpr uint32_t LO = W3_PIECE >> 4;                                  // hi -> lo piece, in descriptor units
+            const uint64_t ones_desc = wg_desc(hi_ns, (((base + W3_SM_ONES) & 0x3FFFFu) >> 4) | ((128u >> 4) << 16));
+            uint32_t it = 0;
+            for (int si = 0; si < n_segs; ++si) {
+                const WgSeg sg = segs[si];
+                const bool has_main = a.xmain[sg.l] != nullptr, has_enc = a.xenc[sg.l] != nullptr;
+                const bool has_small = a.xsmall[sg.l] != nullptr, has_ones = a.ones[sg.l] != 0;
+                if (si > 0) { tc::mbar_wait(acc_free, (si - 1) & 1, a.wait_hint); tc::tcgen05_fence_after(); }
+                uint32_t acc = 0;
+                for (int n = 4 * (sg.te - sg.tb); n > 0; --n, ++it) {
+                    const int slot = it % W3_STAGES; const uint32_t ph = (it / W3_STAGES) & 1;
+                    tc::mbar_wait(full(slot), ph, a.wait_hint);
+                    tc::tcgen05_fence_after();
+                    const uint32_t st = ((base + slot * W3_STAGE_BYTES) & 0x3FFFFu) >> 4;
+                    const uint32_t a_lo = st | lbo_slab, m_lo = (st + (W3_OFF_B >> 4)) | lbo_slab, e_lo = (st + (W3_OFF_E >> 4)) | lbo_slab;
+                    const uint32_t s_lo = (st + (W3_OFF_B >> 4)) | ((256u >> 4) << 16);
+                    if (tc::elect_one()) {
+#pragma unroll
+                        for (int kk = 0; kk < 2; ++kk) {
+                            const uint64_t ah = wg_desc(hi_sw, a_lo + kk * 128), al = wg_desc(hi_sw, a_lo + LO + kk * 128);
+                            const uint32_t ac = (kk == 0) ? acc : 1u;
+                            if (has_main) {
+                                const uint64_t bh = wg_desc(hi_sw, m_lo + kk * 128), bl = wg_desc(hi_sw, m_lo + LO + kk * 128);
+                                tc::umma_bf16_2cta(tmem_base, ah, bh, idesc_main, ac);
+                                tc::umma_bf16_2cta(tmem_base, al, bh, idesc_main, 1u);
+                                tc::umma_bf16_2cta(tmem_base, ah, bl, idesc_main, 1u);
+                            }
+                            if (has_enc) {
+                                const uint64_t eh = wg_desc(hi_sw, e_lo + kk * 128), el = wg_desc(hi_sw, e_lo + LO + kk * 128);
+                                tc::umma_bf16_2cta(tmem_base + 256, ah, eh, idesc_enc, ac);
+                                tc::umma_bf16_2cta(tmem_base + 256, al, eh, idesc_enc, 1u);
+                                tc::umma_bf16_2cta(tmem_base + 256, ah, el, idesc_enc, 1u);
+                            } else if (has_ones) {
+                                tc::umma_bf16_2cta(tmem_base + 320, ah, ones_desc, idesc_32, ac);
+                                tc::umma_bf16_2cta(tmem_base + 320, al, ones_desc, idesc_32, 1u);
+                            }
+                            if (has_small) {                             // 16 points = 2 groups of 256 B; the lo part 1 KB on
+                                const uint64_t sh = wg_desc(hi_ns, s_lo + kk * 32), sl = wg_desc(hi_ns, s_lo + (1024u >> 4) + kk * 32);
+                                tc::umma_bf16_2cta(tmem_base, ah, sh, idesc_32, ac);
+                                tc::umma_bf16_2cta(tmem_base, al, sh, idesc_32, 1u);
+                                tc::umma_bf16_2cta(tmem_base, ah, sl, idesc_32, 1u);
+                            }
+                        }
+                        tc::umma_commit_2cta(empty(slot));
+                    }
+                    __syncwarp();
+                    acc = 1;
+                }
+                if (tc::elect_one()) tc::umma_commit_2cta(acc_done);
+                __syncwarp();
+            }
+        } else if (lane == 0) {
+            // ===================== peer relay =====================
+            uint32_t it = 0;
+            for (int si = 0; si < n_segs; ++si)
+                for (int n = 4 * (segs[si].te - segs[si].tb); n > 0; --n, ++it) {
+                    const int slot = it % W3_STAGES; const uint32_t ph = (it / W3_STAGES) & 1;
+                    tc::mbar_wait(full(slot), ph, a.wait_hint);
+                    tc::mbar_arrive_cluster(tc::mapa(full(slot), 0));
+                }
+        }
+    } else {
+        // ===================== flush: this CTA's 128 output features =====================
+        const uint32_t q = warp & 3;
+        const uint32_t row = q * 32 + lane;
+        const uint32_t taddr = tmem_base + ((q * 32u) << 16);
+        const uint32_t free_remote = tc::mapa(acc_free, 0);
+        for (int si = 0; si < n_segs; ++si) {
+            const WgSeg sg = segs[si];
+            const bool has_main = a.xmain[sg.l] != nullptr, has_enc = a.xenc[sg.l] != nullptr;
+            float* o = a.out[sg.l] + (size_t)(rank * 128 + row) * a.ld[sg.l];
+            tc::mbar_wait(acc_done, si & 1, a.wait_hint);
+            tc::tcgen05_fence_after();
+            for (int c = 0; c < 336; c += 16) {
+                const bool live = c < 256 ? (has_main || (c == 0 && a.xsmall[sg.l])) : (c < 320 ? has_enc : a.ones[sg.l] != 0);
+                if (!live) continue;
+                uint32_t r[16];
+                tc::tmem_ld16(taddr + c, r); tc::tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; j += 4)
+                    tc::red_add_v4(o + c + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+            }
+            tc::tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive_cluster(free_remote);
+        }
+    }
+    tc::tcgen05_fence_before();
+    tc::cluster_sync_all();
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 512); }
+}
+
+// all weight gradients of one fp32-grade training step from the workspace the x3 forward / data-gradient kernels filled
 int launch_wgrad_tc_units_x3(const uint8_t* ws, const X3TrainLayout& X, cudaStream_t st) {
     const TrainLayout& T = X.T;
-    const size_t unit_bytes = (size_t)T.tr_tiles * 4 * TC_SLAB_BYTES;
+    const size_t unit_bytes = (size_t)T.tr_tiles * X3_IMG_BYTES;
     uint8_t* w = const_cast<uint8_t*>(ws);
-    for (int pass = 0; pass < 3; ++pass) {
-        const bool dz_lo = pass == 1, x_lo = pass == 2;
-        const uint8_t* dz = ws + (dz_lo ? X.off_dz_lo : T.off_dz);
-        const uint8_t* act = ws + (x_lo ? X.off_act_lo : T.off_act);
-        const uint8_t* pex = ws + (x_lo ? X.off_pex_lo : T.off_pex);
-        const uint8_t* ped = ws + (x_lo ? X.off_ped_lo : T.off_ped);
-        WgradArgs a{};
-        for (int l = 0; l < 10; ++l) {
-            a.dz[l] = dz + l * unit_bytes;
-            a.xmain[l] = (l == 0) ? nullptr : act + (l - 1) * unit_bytes;
-            a.xenc[l] = (l == 0 || l == 4) ? pex : (l == 8 ? ped : nullptr);
-            a.out[l] = reinterpret_cast<float*>(w + T.off_gw) + (size_t)l * 256 * TC_GW_LD; a.ld[l] = TC_GW_LD; a.ones[l] = pass < 2;
-        }
-        // head pseudo-units: n_7 / n_9 (hi, lo) against the (d_sigma, d_rgb) images (hi, lo)
-        const uint8_t* nact = ws + (dz_lo ? X.off_act_lo : T.off_act);
-        for (int hd = 0; hd < 2; ++hd) {
-            a.dz[10 + hd] = nact + (hd == 0 ? 7 : 9) * unit_bytes;
-            a.xsmall[10 + hd] = ws + (x_lo ? X.off_dh_lo : T.off_dh);
-            a.out[10 + hd] = reinterpret_cast<float*>(w + T.off_gh) + (size_t)hd * 256 * 16; a.ld[10 + hd] = 16;
-        }
-        a.n_tiles = T.n_tiles;
-        int rc = launch_wgrad_tc(a, st); if (rc) return rc;
+    WgradX3Args a{};
+    for (int l = 0; l < 10; ++l) {
+        a.dz[l] = ws + X.off_dz3 + l * unit_bytes;
+        a.xmain[l] = (l == 0) ? nullptr : ws + X.off_act3 + (l - 1) * unit_bytes;
+        a.xenc[l] = (l == 0 || l == 4) ? ws + X.off_pex3 : (l == 8 ? ws + X.off_ped3 : nullptr);
+        a.out[l] = reinterpret_cast<float*>(w + T.off_gw) + (size_t)l * 256 * TC_GW_LD; a.ld[l] = TC_GW_LD; a.ones[l] = 1;
     }
+    for (int hd = 0; hd < 2; ++hd) {                 // head pseudo-units: n_7 / n_9 against the (d_sigma, d_rgb) images
+        a.dz[10 + hd] = ws + X.off_act3 + (hd == 0 ? 7 : 9) * unit_bytes;
+        a.xsmall[10 + hd] = ws + X.off_dh3;
+        a.out[10 + hd] = reinterpret_cast<float*>(w + T.off_gh) + (size_t)hd * 256 * 16; a.ld[10 + hd] = 16;
+    }
+    a.n_tiles = T.n_tiles;
+    NERF_CUDA(nerf_smem_opt_in<g1_wgrad_x3_kernel>(W3_SMEM_BYTES));
+    static const uint32_t wait_hint = nerf_env_u32("NERF_TC_WAIT_HINT", 0x989680u);
+    a.wait_hint = wait_hint;
+    int pairs = nerf_num_sms() / 2;
+    const int64_t work = 12ll * a.n_tiles;
+    if (work < pairs) pairs = (int)(work > 0 ? work : 1);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * pairs); cfg.blockDim = dim3(WG_THREADS); cfg.dynamicSmemBytes = W3_SMEM_BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension; attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    NERF_CUDA(cudaLaunchKernelEx(&cfg, g1_wgrad_x3_kernel, a));
+    NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
