@@ -423,9 +423,10 @@ def run_ours(args):
         ms_dw = float(np.mean(timed_steps(k_bwd(2), 5, flush)))
         return {"value": RAYS * n / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms / n, "steps": n, "precision": "bf16x3", "per_gpu": True,
                 "contraction": "tcgen05 kind::f16 with hi/lo operands (3 products per term) in the forward, the data-gradient chain and the "
-                               "weight-gradient GEMMs; LayerNorm/ReLU forward and backward, heads, unfold, Adam in fp32",
+                               "weight-gradient GEMM (one pass over interleaved hi/lo images); LayerNorm/ReLU forward and backward, heads, "
+                               "unfold, Adam in fp32",
                 "mlp_tflops": RAYS * SAMPLES * FLOP_PER_POINT_FWD_BWD * n / (ms * 1e-3) / 1e12,
-                "kernels_ms": {"g1_fused_x3_kernel<train>": ms_f, "g1_bwd_x3_kernel": ms_d, "g1_wgrad_tc_kernel x 3": ms_dw - ms_d},
+                "kernels_ms": {"g1_fused_x3_kernel<train>": ms_f, "g1_bwd_x3_kernel": ms_d, "g1_wgrad_x3_kernel": ms_dw - ms_d},
                 "workspace_bytes": int(z4["n"]),
                 "parity": "gradient vs the fp32 path: 7e-4 .. 2e-3 whole-gradient rel-L2 = the exact gradient's own sensitivity to a 1e-5 "
                           "relative change of the forward (profiles/r02_grad_conditioning.txt); bf16: 5e-2 .. 6e-2"}
@@ -585,7 +586,7 @@ def run_ours(args):
         out["max_abs_pixel_diff_100x100"] = float((a_ - b_).abs().max().item())
         out["speedup"] = out["bf16x3"]["value"] / out["fp32_ffma"]["value"]
         out["note"] = ("fp32-mode accuracy (<= 1e-3 pixels, north star) on tcgen05: every GEMM operand split into two bf16 parts, "
-                       "hi*hi + lo*hi + hi*lo with fp32 accumulation (csrc/fused_tc_x3.cu); forward / render only")
+                       "hi*hi + lo*hi + hi*lo with fp32 accumulation (csrc/fused_tc_x3.cu); the training step in this mode: fp32_grade_train")
         return out
     render_fp32_grade = safe("render_fp32_grade", _render_fp32_grade) if (world == 1 or args.all_sections) else None
 

@@ -11,9 +11,10 @@
 //   SM_PE   [hi slab | lo slab]
 //   ring    3 x 16 KB [4 k-cores hi | 4 k-cores lo], then ONE 4 KB bias block (of the unit in flight; units without an
 //           encoding slab) and the 8 KB exchange buffer of the epilogue's thread pairs -- the bf16 kernel's 3 x 20 KB
-// so a ring stage covers K = 32 (two K-steps, six MMAs).  One accumulator (256 TMEM columns): the MMAs of unit l+1
-// depend on the whole epilogue of unit l of the same tile, so tensor pipe and epilogue alternate; the price of
-// fp32-grade operands here is ~3x the MMAs and no tile ping-pong.
+// so a ring stage covers K = 32 (two K-steps, six MMAs).  One tile per CTA (the price of fp32-grade operands in 227 KB is
+// ~3x the MMAs and no tile ping-pong), but TWO accumulators (units alternate between TMEM columns 0 and 256): pass 2 of the
+// epilogue of unit l writes the activation slabs in K order and releases the MMAs of unit l+1 slab by slab, so they run
+// under the rest of the pass instead of after it.
 //   warp 0    TMA producer      warp 1    MMA issuer (leader) / weight-arrival relay (peer)
 //   warps 2-9 encoder + epilogue, TWO threads per point row (warps w and w + 4 share a TMEM lane quarter; each takes 128
 //             of the row's 256 columns and the row sums are exchanged through shared memory).  With one tile slot and one
@@ -46,7 +47,8 @@ __device__ __forceinline__ uint4 lds128v(uint32_t addr) {
 // (a + b = b + a in fp32), half 0 writes the row's outputs.
 template <int MODE, bool TRAIN>
 __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_t taddr, uint32_t act_addr, uint32_t row,
-                                              uint32_t vec_addr, const RowState& st, int half, uint32_t xch_addr) {
+                                              uint32_t vec_addr, const RowState& st, int half, uint32_t xch_addr,
+                                              uint32_t slab_bar_remote, bool signal) {
     const uint32_t hsum_addr = vec_addr + (SM_HSUM - SM_VEC);
     uint32_t r0[32], r1[32];
     float2 s2 = make_float2(0.f, 0.f), q2 = s2, s3 = s2, q3 = s2;
@@ -71,15 +73,16 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
             }
         }
     };
-    const int cb = 4 * half;                                       // this thread's first 32-column chunk
-    tc::tmem_ld32(taddr + cb * 32, r0); tc::tmem_ld_wait();
+    // this thread's chunks: 2k + half, k = 0..3 -- one 32-column chunk of every 64-column slab, so that slab k is complete
+    // when both threads of the row have done their k-th chunk of pass 2 and the next unit's MMAs over it can start
+    tc::tmem_ld32(taddr + half * 32, r0); tc::tmem_ld_wait();
 #pragma unroll 1
     for (int c2 = 0; c2 < 2; ++c2) {
-        tc::tmem_ld32(taddr + (cb + 2 * c2 + 1) * 32, r1);
-        pass1(r0, cb + 2 * c2);
+        tc::tmem_ld32(taddr + (4 * c2 + 2 + half) * 32, r1);
+        pass1(r0, 4 * c2 + half);
         tc::tmem_ld_wait();
-        if (c2 < 1) tc::tmem_ld32(taddr + (cb + 2 * c2 + 2) * 32, r0);
-        pass1(r1, cb + 2 * c2 + 1);
+        if (c2 < 1) tc::tmem_ld32(taddr + (4 * c2 + 4 + half) * 32, r0);
+        pass1(r1, 4 * c2 + 2 + half);
         tc::tmem_ld_wait();
     }
     s2 = __fadd2_rn(s2, s3); q2 = __fadd2_rn(q2, q3);
@@ -135,15 +138,26 @@ __device__ __noinline__ void epilogue_unit_x3(const FusedArgs& a, int l, uint32_
         }
         if (TRAIN) a.tr_mask[((size_t)l * a.P_pad + st.p) * 8 + ch] = mask;
     };
-    tc::tmem_ld32(taddr + cb * 32, r0); tc::tmem_ld_wait();
+    // slab k of the activations is written: release the next unit's MMAs over it (one arrival per warp and slab; the leader's
+    // barrier k counts the 16 epilogue warps of the pair)
+    auto slab_done = [&](int k) {
+        if (!signal) return;
+        tc::fence_proxy_async_smem();
+        tc::tcgen05_fence_before();
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) tc::mbar_arrive_cluster(slab_bar_remote + 8u * k);
+    };
+    tc::tmem_ld32(taddr + half * 32, r0); tc::tmem_ld_wait();
 #pragma unroll 1
     for (int c2 = 0; c2 < 2; ++c2) {
-        tc::tmem_ld32(taddr + (cb + 2 * c2 + 1) * 32, r1);
-        pass2(r0, cb + 2 * c2);
+        tc::tmem_ld32(taddr + (4 * c2 + 2 + half) * 32, r1);
+        pass2(r0, 4 * c2 + half);
         tc::tmem_ld_wait();
-        if (c2 < 1) tc::tmem_ld32(taddr + (cb + 2 * c2 + 2) * 32, r0);
-        pass2(r1, cb + 2 * c2 + 1);
+        slab_done(2 * c2);
+        if (c2 < 1) tc::tmem_ld32(taddr + (4 * c2 + 4 + half) * 32, r0);
+        pass2(r1, 4 * c2 + 2 + half);
         tc::tmem_ld_wait();
+        slab_done(2 * c2 + 1);
     }
 }
 
@@ -157,8 +171,11 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
     const uint32_t bar0 = base + SM_BAR;
     auto ring_full = [&](int s) { return bar0 + 8u * s; };
     auto ring_empty = [&](int s) { return bar0 + 8u * (TC_RING + s); };
-    const uint32_t act_ready = bar0 + 8u * (2 * TC_RING), acc_ready = bar0 + 8u * (2 * TC_RING + 1);
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 2));
+    // pe_ready: the tile's encoding slab is written (unit 0's MMAs); slab_ready[k]: activation slab k of the unit in the epilogue
+    // is written (the next unit's MMAs over K-slab k); acc_ready: a unit's MMAs are complete
+    const uint32_t pe_ready = bar0 + 8u * (2 * TC_RING), acc_ready = bar0 + 8u * (2 * TC_RING + 1);
+    auto slab_ready = [&](int k) { return bar0 + 8u * (2 * TC_RING + 2 + k); };
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + SM_BAR + 8 * (2 * TC_RING + 6));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = tc::cluster_ctarank();
@@ -176,10 +193,11 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < TC_RING; ++s) { tc::mbar_init(ring_full(s), leader ? 2 : 1); tc::mbar_init(ring_empty(s), 1); }
-        tc::mbar_init(act_ready, 16); tc::mbar_init(acc_ready, 1);
+        tc::mbar_init(pe_ready, 16); tc::mbar_init(acc_ready, 1);
+        for (int k = 0; k < 4; ++k) tc::mbar_init(slab_ready(k), 16);
         tc::fence_barrier_init();
     }
-    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 256);
+    if (warp == 1) tc::tmem_alloc2(tc::smem_u32((const void*)tmem_slot), 512);   // two accumulators: units alternate
     tc::tcgen05_fence_before();
     tc::cluster_sync_all();
     tc::tcgen05_fence_after();
@@ -216,25 +234,31 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
             auto lo_a = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | (1u << 16); };
             const uint32_t ring_lo = (((base + SM_RING) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
             const uint32_t bias_lo = (((base + X3_SM_BIAS) & 0x3FFFFu) >> 4) | ((TF_B_LBO >> 4) << 16);
-            auto mma = [&](uint32_t alo, uint32_t blo, uint32_t acc) {
-                tc::umma_bf16_2cta(tmem_base, ((uint64_t)hi_a << 32) | alo, ((uint64_t)hi_b << 32) | blo, idesc, acc);
+            auto mma = [&](uint32_t d, uint32_t alo, uint32_t blo, uint32_t acc) {
+                tc::umma_bf16_2cta(d, ((uint64_t)hi_a << 32) | alo, ((uint64_t)hi_b << 32) | blo, idesc, acc);
             };
             const uint32_t act_lo = lo_a(base + SM_ACT), pe_lo = lo_a(base + SM_PE);
             constexpr uint32_t ACT_LO_PART = 65536u >> 4, PE_LO_PART = TC_SLAB_BYTES >> 4;   // hi -> lo distance, in descriptor units
-            uint32_t it = 0, act_it = 0;
+            // Unit l accumulates into TMEM columns (l & 1) * 256: the epilogue of unit l-1 is still reading the other accumulator when
+            // these MMAs start on the first slabs it has written.
+            uint32_t it = 0, pe_it = 0, slab_it = 0;
             for (int q = 0; q < n_my; ++q)
                 for (int l = 0; l < 10; ++l) {
                     const bool pfm = a.prof && blockIdx.x == 0 && q == 1 && lane == 0;
                     if (pfm) a.prof[l * 8 + 0] = clock64();
-                    tc::mbar_wait_spin(act_ready, act_it & 1, a.wait_hint); ++act_it;
-                    tc::tcgen05_fence_after();
-                    if (pfm) a.prof[l * 8 + 1] = clock64();
+                    if (l == 0) { tc::mbar_wait_spin(pe_ready, pe_it & 1, a.wait_hint); ++pe_it; tc::tcgen05_fence_after(); }
+                    const uint32_t d_tmem = tmem_base + (uint32_t)(l & 1) * 256u;
                     const bool blk = tc_unit_has_bias_block(l);
                     const int ng = 2 * a.nk[l];
                     for (int j = 0; j < ng; ++j, ++it) {
                         const int slot = it % TC_RING; const uint32_t ph = (it / TC_RING) & 1;
                         const int slab = j >> 1;
                         const bool enc = (l == 0 || slab >= 4);
+                        if (!enc && (j & 1) == 0) {                    // K-slab `slab` of n_{l-1}
+                            tc::mbar_wait_spin(slab_ready(slab), slab_it & 1, a.wait_hint);
+                            tc::tcgen05_fence_after();
+                            if (pfm && slab == 0) a.prof[l * 8 + 1] = clock64();
+                        }
                         const uint32_t a_hi = (enc ? pe_lo : act_lo + slab * (TC_SLAB_BYTES >> 4)) + (j & 1) * 4;   // 32 columns = 64 B = 4 units
                         const uint32_t a_lo = a_hi + (enc ? PE_LO_PART : ACT_LO_PART);
                         const uint32_t blo = ring_lo + slot * (X3_GROUP_BYTES >> 4);
@@ -242,14 +266,14 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                         if (tc::elect_one()) {
                             uint32_t acc = (j != 0) ? 1u : 0u;
                             if (blk && j == 0) {                   // acc = b': hi slab columns 48..63 (ones at 60..62) x bias block
-                                mma(pe_lo + 3 * 2, bias_lo, 0); acc = 1u;
+                                mma(d_tmem, pe_lo + 3 * 2, bias_lo, 0); acc = 1u;
                             }
 #pragma unroll
                             for (int kk = 0; kk < 2; ++kk) {
                                 const uint32_t bh = blo + kk * (2 * TF_KCORE_BYTES >> 4), bl = bh + (4 * TF_KCORE_BYTES >> 4);
-                                mma(a_hi + kk * 2, bh, acc);
-                                mma(a_lo + kk * 2, bh, 1u);
-                                mma(a_hi + kk * 2, bl, 1u);
+                                mma(d_tmem, a_hi + kk * 2, bh, acc);
+                                mma(d_tmem, a_lo + kk * 2, bh, 1u);
+                                mma(d_tmem, a_hi + kk * 2, bl, 1u);
                                 acc = 1u;
                             }
                             tc::umma_commit_2cta(ring_empty(slot));
@@ -257,6 +281,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                         }
                         __syncwarp();
                     }
+                    if (l >= 1) ++slab_it;
                     if (pfm) a.prof[l * 8 + 2] = clock64();
                 }
         } else if (lane == 0) {
@@ -277,12 +302,12 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
         const uint32_t et = threadIdx.x - 64;                        // 0..255 within the group
         const uint32_t taddr = tmem_base + (((warp & 3) * 32u) << 16);
         const uint32_t act_addr = base + SM_ACT, pe_addr = base + SM_PE, xch_addr = base + X3_SM_XCH;
-        const uint32_t act_bar_remote = tc::mapa(act_ready, 0);
-        auto signal_act = [&]() {
+        const uint32_t pe_bar_remote = tc::mapa(pe_ready, 0), slab_bar_remote = tc::mapa(slab_ready(0), 0);
+        auto signal_pe = [&]() {
             tc::fence_proxy_async_smem();
             tc::tcgen05_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
+            if (lane == 0) tc::mbar_arrive_cluster(pe_bar_remote);
         };
         uint32_t acc_it = 0;
         // TRAIN: the slab images (hi and lo) the backward needs, shared memory -> HBM, 16 bytes per thread and step, four in
@@ -322,7 +347,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                 st.p = (int64_t)tile * 128 + row;                      // rows beyond P still own a row of the padded images
                 slabs_complete();
             }
-            signal_act();
+            signal_pe();
             if (TRAIN) copy_enc(a.tr_pex + (size_t)tile * X3_ENC_IMG_BYTES);
             for (int l = 0; l < 10; ++l) {
                 const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1 && half == 0;
@@ -330,13 +355,15 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
                 tc::mbar_wait(acc_ready, acc_it & 1, a.wait_hint); ++acc_it;
                 tc::tcgen05_fence_after();
                 if (pfe) a.prof[l * 8 + 4] = clock64();
-                if (l == 7) epilogue_unit_x3<1, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
-                else if (l == 9) epilogue_unit_x3<2, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
-                else epilogue_unit_x3<0, TRAIN>(a, l, taddr, act_addr, row, base + SM_VEC, st, half, xch_addr);
-                if (l == 4 && half == 0) encode_dir_row<true>(a, row, pe_addr, st);     // unit 4 was the last reader of the position slabs
+                // unit 4 was the last reader of the position slabs: the direction encoding goes in before this unit's slab signals,
+                // which release MMAs that read the slab's ones columns (the bias product of unit 5)
+                if (l == 4 && half == 0) encode_dir_row<true>(a, row, pe_addr, st);
+                const uint32_t tacc = taddr + (uint32_t)(l & 1) * 256u;
+                if (l == 7) epilogue_unit_x3<1, TRAIN>(a, l, tacc, act_addr, row, base + SM_VEC, st, half, xch_addr, slab_bar_remote, true);
+                else if (l == 9) epilogue_unit_x3<2, TRAIN>(a, l, tacc, act_addr, row, base + SM_VEC, st, half, xch_addr, slab_bar_remote, false);
+                else epilogue_unit_x3<0, TRAIN>(a, l, tacc, act_addr, row, base + SM_VEC, st, half, xch_addr, slab_bar_remote, true);
                 if (pfe) a.prof[l * 8 + 5] = clock64();
                 if (TRAIN) slabs_complete();
-                if (l < 9) signal_act();
                 if (pfe) a.prof[l * 8 + 6] = clock64();
                 if (TRAIN) {
                     copy_hidden(a.tr_act + ((size_t)l * a.tr_tiles + tile) * X3_IMG_BYTES);
@@ -347,7 +374,7 @@ __global__ void __launch_bounds__(X3_THREADS, 1) g1_fused_x3_kernel(const FusedA
     }
     tc::tcgen05_fence_before();
     tc::cluster_sync_all();
-    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 256); }
+    if (warp == 1) { tc::tcgen05_fence_after(); tc::tmem_dealloc2(tmem_base, 512); }
 }
 
 // launches the x3 kernel on a.n_tiles tiles; `packed` = the image of nerf_g1_pack_weights_x3

@@ -14,10 +14,13 @@
 //              instruction's latency exposed (ncu: 1.5 warps per SMSP, issue slots 20 % busy).
 //                  dz = mask * rstd * (g - mean(g) - n * mean(g n)),   n = n_hi + n_lo (forward's slab images),
 //              the mask is the forward's exact bitmask (8 words per row and unit, fused_tc_x3.cu);
-//              dz overwrites n in place as (hi, lo) = the A operands of the next MMAs and is bulk-stored for the
-//              weight-gradient GEMM; row 0 of the group issues the tile's bulk loads and stores.
-// Per unit the steps are serial (epilogue -> MMAs -> refill): the bf16 kernel's two-slot overlap does not fit next to the
-// lo parts in 227 KB.  n_{l-1} is prefetched into L2 while the MMAs of unit l run.
+//              dz overwrites n in place as (hi, lo) = the A operands of the next MMAs; the same 256 threads bring n in
+//              (cp.async) and copy dz out (st.global) for the weight-gradient GEMM -- see the note at cp_async16.
+// Per unit the steps are serial (MMAs -> refill -> epilogue): the bf16 kernel's two-slot overlap does not fit next to the
+// lo parts in 227 KB.  n_{l-1} is prefetched into L2 while the MMAs of unit l run.  (Releasing the next MMAs slab by slab
+// from inside pass 2, into a second accumulator -- what the forward does -- was measured here and is not kept: pass 2 reads
+// and writes both parts of the image, ~73 B/cycle of shared-memory traffic, the MMAs need ~64 of the same 128, and the two
+// only slow each other down: 1.36 ms against 1.30.)
 #include "tc_bwd_kernel.cuh"
 #include "tc_bwd_x3.cuh"
 #include <stdio.h>
@@ -67,9 +70,10 @@ template <int SRC>
 __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_addr, uint32_t lo_addr, uint32_t row, uint32_t hw_addr,
                                                   const uint32_t (&mw)[8], float rstd, float ds, float dr, float dg, float db,
                                                   int half, uint32_t xch_addr) {
-    uint32_t r[32];
-    // g of the 8 columns ch*32 + i*8 .. +7 (rc = the chunk's 32 TMEM columns)
-    auto grad8 = [&](const uint32_t (&rc)[32], int ch, int i, float (&g)[8]) {
+    uint32_t r0[32], r1[32];
+    const float2 ds2 = make_float2(ds, ds), dr2 = make_float2(dr, dr), dg2 = make_float2(dg, dg), db2 = make_float2(db, db);
+    // g of the 8 columns ch*32 + i*8 .. +7 as four column pairs (rc = the chunk's 32 TMEM columns); packed f32x2 arithmetic
+    auto grad8 = [&](const uint32_t (&rc)[32], int ch, int i, float2 (&g)[4]) {
         const int c0 = ch * 32 + i * 8;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -77,46 +81,93 @@ __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_ad
                 const float4 w0 = tc::lds128(hw_addr + (256 + c0 + 4 * h) * 4);
                 const float4 w1 = tc::lds128(hw_addr + (512 + c0 + 4 * h) * 4);
                 const float4 w2 = tc::lds128(hw_addr + (768 + c0 + 4 * h) * 4);
-                g[4 * h + 0] = fmaf(dr, w0.x, fmaf(dg, w1.x, db * w2.x)); g[4 * h + 1] = fmaf(dr, w0.y, fmaf(dg, w1.y, db * w2.y));
-                g[4 * h + 2] = fmaf(dr, w0.z, fmaf(dg, w1.z, db * w2.z)); g[4 * h + 3] = fmaf(dr, w0.w, fmaf(dg, w1.w, db * w2.w));
+                g[2 * h] = __ffma2_rn(dr2, make_float2(w0.x, w0.y), __ffma2_rn(dg2, make_float2(w1.x, w1.y), __fmul2_rn(db2, make_float2(w2.x, w2.y))));
+                g[2 * h + 1] = __ffma2_rn(dr2, make_float2(w0.z, w0.w), __ffma2_rn(dg2, make_float2(w1.z, w1.w), __fmul2_rn(db2, make_float2(w2.z, w2.w))));
             } else {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) g[4 * h + q] = __uint_as_float(rc[i * 8 + 4 * h + q]);
+                g[2 * h] = make_float2(__uint_as_float(rc[i * 8 + 4 * h]), __uint_as_float(rc[i * 8 + 4 * h + 1]));
+                g[2 * h + 1] = make_float2(__uint_as_float(rc[i * 8 + 4 * h + 2]), __uint_as_float(rc[i * 8 + 4 * h + 3]));
                 if (SRC == 1) {
                     const float4 w = tc::lds128(hw_addr + (c0 + 4 * h) * 4);
-                    g[4 * h + 0] = fmaf(ds, w.x, g[4 * h + 0]); g[4 * h + 1] = fmaf(ds, w.y, g[4 * h + 1]);
-                    g[4 * h + 2] = fmaf(ds, w.z, g[4 * h + 2]); g[4 * h + 3] = fmaf(ds, w.w, g[4 * h + 3]);
+                    g[2 * h] = __ffma2_rn(ds2, make_float2(w.x, w.y), g[2 * h]);
+                    g[2 * h + 1] = __ffma2_rn(ds2, make_float2(w.z, w.w), g[2 * h + 1]);
                 }
             }
         }
     };
-    // n = hi + lo and the ReLU mask (bit q = column q active) of the same 8 columns; off = their byte offset in both parts
-    auto load_n = [&](int ch, int i, float (&n)[8], uint32_t& mask, uint32_t& off) {
-        off = (uint32_t)(ch >> 1) * TC_SLAB_BYTES + tc::sw128_offset(row, (ch & 1) * 4 + i);
-        const uint4 h = lds128u(hi_addr + off), l = lds128u(lo_addr + off);
+    // n = hi + lo of the same 8 columns (four pairs) from the two 16-byte row pieces
+    auto sum_n = [&](const uint4& h, const uint4& l, float2 (&n)[4]) {
         const uint32_t hv[4] = {h.x, h.y, h.z, h.w}, lv[4] = {l.x, l.y, l.z, l.w};
-        mask = (mw[ch] >> (i * 8)) & 0xFFu;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) { n[2 * q] = bf_lo(hv[q]) + bf_lo(lv[q]); n[2 * q + 1] = bf_hi(hv[q]) + bf_hi(lv[q]); }
+        for (int q = 0; q < 4; ++q) n[q] = __fadd2_rn(make_float2(bf_lo(hv[q]), bf_hi(hv[q])), make_float2(bf_lo(lv[q]), bf_hi(lv[q])));
     };
-    // ---- pass 1: sum g, sum g n   (two chains each)
-    float s1a = 0.f, s1b = 0.f, s2a = 0.f, s2b = 0.f;
-#pragma unroll 1
-    for (int ch = 4 * half; ch < 4 * half + 4; ++ch) {
-        if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
+    auto piece = [&](int ch, int i) { return (uint32_t)(ch >> 1) * TC_SLAB_BYTES + tc::sw128_offset(row, (ch & 1) * 4 + i); };
+    // ---- pass 1: sum g, sum g n   (two chains each); the chunk's eight row pieces are requested back to back
+    float2 s1a = make_float2(0.f, 0.f), s1b = s1a, s2a = s1a, s2b = s1a;
+    auto pass1 = [&](const uint32_t (&rc)[32], int ch) {
+        uint4 nh[4], nl[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const uint32_t off = piece(ch, i); nh[i] = lds128u(hi_addr + off); nl[i] = lds128u(lo_addr + off); }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            float g[8], n[8]; uint32_t mask, off;
-            grad8(r, ch, i, g); load_n(ch, i, n, mask, off);
+            float2 g[4], n[4];
+            grad8(rc, ch, i, g); sum_n(nh[i], nl[i], n);
+            s1a = __fadd2_rn(s1a, g[0]); s1b = __fadd2_rn(s1b, g[1]); s1a = __fadd2_rn(s1a, g[2]); s1b = __fadd2_rn(s1b, g[3]);
+            s2a = __ffma2_rn(g[0], n[0], s2a); s2b = __ffma2_rn(g[1], n[1], s2b);
+            s2a = __ffma2_rn(g[2], n[2], s2a); s2b = __ffma2_rn(g[3], n[3], s2b);
+        }
+    };
+    // ---- pass 2: dz = mask * (rstd g - rstd m1 - n rstd m2), (hi, lo) in place over (n_hi, n_lo)
+    float2 c0, c1;
+    const float2 rs2 = make_float2(rstd, rstd);
+    auto pass2 = [&](const uint32_t (&rc)[32], int ch) {
+        uint4 nh[4], nl[4];
 #pragma unroll
-            for (int q = 0; q < 8; q += 2) {
-                s1a += g[q]; s1b += g[q + 1];
-                s2a = fmaf(g[q], n[q], s2a); s2b = fmaf(g[q + 1], n[q + 1], s2b);
+        for (int i = 0; i < 4; ++i) { const uint32_t off = piece(ch, i); nh[i] = lds128u(hi_addr + off); nl[i] = lds128u(lo_addr + off); }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float2 g[4], n[4];
+            grad8(rc, ch, i, g); sum_n(nh[i], nl[i], n);
+            const uint32_t mask = mw[ch] >> (i * 8);
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float2 d = __ffma2_rn(n[q], c1, __ffma2_rn(g[q], rs2, c0));
+                d.x = (mask & (1u << (2 * q))) ? d.x : 0.f;
+                d.y = (mask & (2u << (2 * q))) ? d.y : 0.f;
+                const __nv_bfloat162 h = __float22bfloat162_rn(d);
+                const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h);
+                const float2 res = __fadd2_rn(d, make_float2(-bf_lo(hb), -bf_hi(hb)));
+                const __nv_bfloat162 l = __float22bfloat162_rn(res);
+                hi[q] = hb; lo[q] = *reinterpret_cast<const uint32_t*>(&l);
+            }
+            const uint32_t off = piece(ch, i);
+            sts128u(hi_addr + off, make_uint4(hi[0], hi[1], hi[2], hi[3]));
+            sts128u(lo_addr + off, make_uint4(lo[0], lo[1], lo[2], lo[3]));
+        }
+    };
+    // both passes walk this thread's four chunks with the next chunk's TMEM load in flight (static register double buffer)
+    const int cb = 4 * half;
+    auto walk = [&](auto&& pass) {
+        if (SRC == 2) {
+#pragma unroll 1
+            for (int ch = cb; ch < cb + 4; ++ch) pass(r0, ch);
+        } else {
+            tc::tmem_ld32(taddr + cb * 32, r0); tc::tmem_ld_wait();
+#pragma unroll 1
+            for (int c2 = 0; c2 < 2; ++c2) {
+                tc::tmem_ld32(taddr + (cb + 2 * c2 + 1) * 32, r1);
+                pass(r0, cb + 2 * c2);
+                tc::tmem_ld_wait();
+                if (c2 < 1) tc::tmem_ld32(taddr + (cb + 2 * c2 + 2) * 32, r0);
+                pass(r1, cb + 2 * c2 + 1);
+                tc::tmem_ld_wait();
             }
         }
-    }
+    };
+    walk(pass1);
     // the other half's sums (named barrier 2: the 256 epilogue threads)
-    float p1 = s1a + s1b, p2 = s2a + s2b;
+    const float2 s1 = __fadd2_rn(s1a, s1b), s2 = __fadd2_rn(s2a, s2b);
+    float p1 = s1.x + s1.y, p2 = s2.x + s2.y;
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(xch_addr + (row * 2 + half) * 8), "f"(p1), "f"(p2) : "memory");
     tc::named_bar_sync(2, 256);
     {
@@ -125,26 +176,8 @@ __device__ __noinline__ void bwd_x3_epilogue_unit(uint32_t taddr, uint32_t hi_ad
         p1 += o1; p2 += o2;
     }
     const float m1 = p1 * (1.0f / 256.f), m2 = p2 * (1.0f / 256.f);
-    const float c0 = -rstd * m1, c1 = -rstd * m2;
-    // ---- pass 2: dz = mask * (rstd g - rstd m1 - n rstd m2), (hi, lo) in place over (n_hi, n_lo)
-#pragma unroll 1
-    for (int ch = 4 * half; ch < 4 * half + 4; ++ch) {
-        if (SRC != 2) { tc::tmem_ld32(taddr + ch * 32, r); tc::tmem_ld_wait(); }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            float g[8], n[8]; uint32_t mask, off;
-            grad8(r, ch, i, g); load_n(ch, i, n, mask, off);
-            uint32_t hi[4], lo[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const float d0 = ((mask >> (2 * q)) & 1u) ? fmaf(n[2 * q], c1, fmaf(g[2 * q], rstd, c0)) : 0.f;
-                const float d1 = ((mask >> (2 * q + 1)) & 1u) ? fmaf(n[2 * q + 1], c1, fmaf(g[2 * q + 1], rstd, c0)) : 0.f;
-                split2(d0, d1, hi[q], lo[q]);
-            }
-            sts128u(hi_addr + off, make_uint4(hi[0], hi[1], hi[2], hi[3]));
-            sts128u(lo_addr + off, make_uint4(lo[0], lo[1], lo[2], lo[3]));
-        }
-    }
+    c0 = make_float2(-rstd * m1, -rstd * m1); c1 = make_float2(-rstd * m2, -rstd * m2);
+    walk(pass2);
 }
 
 __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Args a) {
@@ -288,11 +321,13 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
                     *reinterpret_cast<uint4*>(img + x3_img_offset(o, 0)) = vh[jj]; *reinterpret_cast<uint4*>(img + x3_img_offset(o, 1)) = vl[jj];
                 }
             }
+            if (a.prof && blockIdx.x == 0 && et == 1 && l == 5 && tile == (int)gridDim.x) a.prof[88] = clock64();
             if (l > 0) {
                 const uint8_t* nx = a.act + ((size_t)(l - 1) * a.tr_tiles + tile) * X3_IMG_BYTES;
                 prefetch_l2_line(nx + et * 128u); prefetch_l2_line(nx + (et + 256u) * 128u);
                 prefetch_l2_line(nx + (et + 512u) * 128u); prefetch_l2_line(nx + (et + 768u) * 128u);
             }
+            if (a.prof && blockIdx.x == 0 && et == 1 && l == 5 && tile == (int)gridDim.x) a.prof[89] = clock64();
         };
         for (int q = 0; q < n_my; ++q) {
             const int unit = me + q * G;
@@ -310,14 +345,19 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
                 *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 0, 1)) = make_uint4(l0, l1, 0u, 0u);
                 *reinterpret_cast<uint4*>(dh + x3_dh_img_offset(row, 1, 1)) = make_uint4(0u, 0u, 0u, 0u);
             }
+            // (rstd, shift) and the ReLU mask of this row for unit l: requested a whole copy-out ahead of their use and held in
+            // registers -- asked for after store_unit they waited ~4 k cycles on a memory system busy with that copy
+            float2 stt_n; uint4 m0_n, m1_n;
+            auto fetch_row = [&](int l) {
+                stt_n = a.stats[(int64_t)l * a.P_pad + p];
+                const uint4* mp = reinterpret_cast<const uint4*>(a.mask + ((size_t)l * a.P_pad + p) * 8);
+                m0_n = mp[0]; m1_n = mp[1];
+            };
+            fetch_row(9);
             for (int l = 9; l >= 0; --l) {
-                const float2 stt = a.stats[(int64_t)l * a.P_pad + p];
-                uint32_t mw[8];                                                   // the unit's ReLU mask of this row (requested before the waits)
-                {
-                    const uint4* mp = reinterpret_cast<const uint4*>(a.mask + ((size_t)l * a.P_pad + p) * 8);
-                    const uint4 m0 = mp[0], m1 = mp[1];
-                    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
-                }
+                const float2 stt = stt_n;
+                uint32_t mw[8];
+                mw[0] = m0_n.x; mw[1] = m0_n.y; mw[2] = m0_n.z; mw[3] = m0_n.w; mw[4] = m1_n.x; mw[5] = m1_n.y; mw[6] = m1_n.z; mw[7] = m1_n.w;
                 const bool pfe = a.prof && blockIdx.x == 0 && q == 1 && row == 1 && half == 0;
                 if (pfe) a.prof[l * 8 + 3] = clock64();
                 if (l < 9) {
@@ -339,6 +379,7 @@ __global__ void __launch_bounds__(BX_THREADS, 1) g1_bwd_x3_kernel(const BwdX3Arg
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive_cluster(act_bar_remote);
                 }
+                if (l > 0) fetch_row(l - 1);
                 store_unit(l, tile);
             }
         }
@@ -378,7 +419,7 @@ int launch_bwd_x3(BwdX3Args& a, cudaStream_t st) {
         }
         fprintf(stderr, "x3 bwd unit 5 stage waits passed at:");
         for (int j = 0; j < 8; ++j) fprintf(stderr, " %lld", h[80 + j] - t0);
-        fprintf(stderr, "\n");
+        fprintf(stderr, "; store_unit(5): copy done %lld, prefetch issued %lld\n", h[88] - t0, h[89] - t0);
         cudaFree(a.prof);
     }
     return NERF_OK;
