@@ -40,3 +40,24 @@ for _ in range(50):
     tr.step(o, d, tgt)
 e1.record(); torch.cuda.synchronize()
 print(f"step {e0.elapsed_time(e1) / 50:.3f} ms | fwd {t_f:.3f}  dgrad {t_d:.3f}  wgrad {t_w:.3f}")
+
+if os.environ.get("PERF_BF16_MODES"):
+    # how the bracket is taken matters at the 5 % level: a 256 MiB write right before the kernel leaves L2 full of dirty lines
+    def async_flush(f, n=10):
+        evs = []
+        for _ in range(n):
+            flush.zero_()
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); f(); b_.record(); evs.append((a, b_))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b_) for a, b_ in evs) / n
+
+    def no_flush(f, n=10):
+        evs = []
+        for _ in range(n):
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); f(); b_.record(); evs.append((a, b_))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b_) for a, b_ in evs) / n
+    for name, f in (("fwd", fwd), ("dgrad", bwd(1)), ("wgrad", bwd(3))):
+        print(f"{name}: flushed+sync {timed(f):.4f}  flushed async {async_flush(f):.4f}  no flush {no_flush(f):.4f}")
