@@ -281,7 +281,8 @@ def run_ours(args):
         if i + 1 < e2e_state["n"]:
             pipe.submit(pool_h[(i + 1) % n_pool])
         o, d, tgt = pipe.get()                                     # rays_o, rays_d, target pixels: views of one [3, RAYS, 3] buffer
-        pipe.done(trainer.step(o, d, tgt))
+        loss = trainer.step(o, d, tgt)
+        pipe.done(loss, ring=trainer.loss_ring)
 
     # ------------------------------------------------------------------ kernels timed alone through the C ABI ----
     # Taken TWICE: here, after three steps of warm-up and before any long region (boost clocks: the state the BURST peak of

@@ -23,8 +23,13 @@ class HostBatchPipeline:
             if i + 1 < n: pipe.submit(host_batches[i + 1])     # copy of the next batch runs under this step
             o, d, target = pipe.get()                          # current stream waits for this batch's copy only
             loss = trainer.step(o, d, target)
-            pipe.done(loss)                                    # frees the buffer; schedules the loss read-back
+            pipe.done(loss, ring=trainer.loss_ring)            # frees the buffer; schedules the loss read-back
         pipe.losses()                                          # pinned host tensor with the losses read back so far
+
+    `ring` tells the pipeline when the producer overwrites the storage of `loss`: `ring` steps later (default 1: the very next
+    step, e.g. a single device scalar).  The step that overwrites it is made to wait for its read-back; with ring = 1 that is
+    an event round trip and a 4-byte copy between EVERY two steps (~55 us of a 1.5 ms step, measured), with the Trainer's ring
+    of 4 slots the read-back waited for is three steps old and long complete.
     """
 
     def __init__(self, device, like, depth=2, max_losses=1 << 16):
@@ -34,6 +39,8 @@ class HostBatchPipeline:
         self.h2d, self.d2h = torch.cuda.Stream(device), torch.cuda.Stream(device)
         self.host_losses = torch.zeros(max_losses).pin_memory()
         self.stepped, self.loss_read = torch.cuda.Event(), torch.cuda.Event()
+        self.read_events = [torch.cuda.Event() for _ in range(8)]
+        self.reads = []                                            # (step at which the loss storage is overwritten, read-back event)
         self.head = self.tail = self.n_losses = 0
         self.pending = [False] * depth
 
@@ -55,11 +62,18 @@ class HostBatchPipeline:
             raise RuntimeError("HostBatchPipeline: get() without a submitted batch")
         cur = torch.cuda.current_stream()
         cur.wait_event(self.copied[k])
-        if self.n_losses:
-            cur.wait_event(self.loss_read)                     # the trainer reuses ONE device loss buffer: the previous read-back
-        return tuple(self.bufs[k])                             # (long finished by now) precedes the step that overwrites it
+        keep = []
+        for reuse, ev in self.reads:                           # read-backs whose source the coming step overwrites precede it
+            if reuse <= self.n_losses:
+                cur.wait_event(ev)
+            else:
+                keep.append((reuse, ev))
+        self.reads = keep
+        return tuple(self.bufs[k])
 
-    def done(self, loss=None):
+    def done(self, loss=None, ring=1):
+        if not 1 <= ring < len(self.read_events):
+            raise ValueError("HostBatchPipeline.done: ring must be in 1..7")
         k = self.tail % len(self.bufs)
         cur = torch.cuda.current_stream()
         self.freed[k].record(cur)
@@ -70,7 +84,9 @@ class HostBatchPipeline:
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(self.stepped)
                 self.host_losses[self.n_losses % self.host_losses.numel():][:1].copy_(loss.detach().reshape(1), non_blocking=True)
+                self.loss_read = self.read_events[self.n_losses % len(self.read_events)]
                 self.loss_read.record(self.d2h)
+            self.reads.append((self.n_losses + ring, self.loss_read))
             self.n_losses += 1
 
     def losses(self):
@@ -79,6 +95,8 @@ class HostBatchPipeline:
 
 
 class Trainer:
+    LOSS_RING = 4      # loss slots of the tensor-core step, used in turn: step i's loss is overwritten by step i + 4
+
     def __init__(self, model, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, near=2.0, far=6.0,
                  num_samples=64, density_noise_std=1.0, randomly_sample=True, seed=0,
                  precision=None, process_group=None, fused_exchange=True):
@@ -105,6 +123,10 @@ class Trainer:
         self.exp_avg_sq = torch.zeros_like(flat)
         self.step_count = 0
         self.rays_seen = 0
+        # how many steps later the storage of the loss the LAST step returned is overwritten (HostBatchPipeline.done(loss,
+        # ring=...)): the fp32 step returns a fresh tensor whose block the allocator may hand out again at once
+        self.loss_ring = 1
+        self._loss_k = 0
         self._ws = None
         self._tc = None                 # bf16 path: buffers keyed by (B, S)
         self.kernel_launches = 0        # kernels launched by the last step() (our .so only)
@@ -130,7 +152,7 @@ class Trainer:
                 "packed_bwd": torch.empty(L.nerf_g1_packed_bwd_x3_bytes() if x3 else L.nerf_g1_packed_bwd_bytes(dx, 3),
                                           dtype=torch.uint8, device=dev),
                 "t": e(b, s), "sigma": e(b, s), "rgb": e(b, s, 3), "d_sigma": e(b, s), "d_rgb": e(b, s, 3),
-                "pixels": e(b, 3), "g_pixels": e(b, 3), "loss": e(1),
+                "pixels": e(b, 3), "g_pixels": e(b, 3), "loss": e(self.LOSS_RING),
             }
         return self._tc
 
@@ -144,6 +166,9 @@ class Trainer:
         dev = flat.device
         L = lib()
         z = self._tc_buffers(b, s, dev)
+        loss = z["loss"][self._loss_k:self._loss_k + 1]
+        self._loss_k = (self._loss_k + 1) % self.LOSS_RING
+        self.loss_ring = self.LOSS_RING
         st = stream()
         ray_base = self.rays_seen * self.world + self.rank * b
         dx = m.density_inputs
@@ -172,7 +197,7 @@ class Trainer:
             z["sigma"] += noise.view(b, s); std = 0.0
         if s <= 256:                            # noise + composite + MSE + composite backward: one launch
             check(L.nerf_composite_mse_train(ptr(z["sigma"]), ptr(z["rgb"]), ptr(rays_o), ptr(rays_d), ptr(z["t"]), ptr(target),
-                                             b, s, std, self.seed, ray_base, ptr(z["pixels"]), ptr(z["loss"]),
+                                             b, s, std, self.seed, ray_base, ptr(z["pixels"]), ptr(loss),
                                              ptr(z["d_sigma"]), ptr(z["d_rgb"]), st), "nerf_composite_mse_train")
             launches += 1
         else:
@@ -180,7 +205,7 @@ class Trainer:
                 ops.add_density_noise_(z["sigma"], std, self.seed, ray_base); launches += 1
             check(L.nerf_composite_fwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
                                        ptr(z["pixels"]), None, None, None, st), "nerf_composite_fwd")
-            check(L.nerf_mse_loss(ptr(z["pixels"]), ptr(target), b * 3, ptr(z["loss"]), ptr(z["g_pixels"]), st), "nerf_mse_loss")
+            check(L.nerf_mse_loss(ptr(z["pixels"]), ptr(target), b * 3, ptr(loss), ptr(z["g_pixels"]), st), "nerf_mse_loss")
             check(L.nerf_composite_bwd(ptr(z["sigma"]), ptr(z["rgb"]), None, ptr(rays_o), ptr(rays_d), ptr(z["t"]), b, s,
                                        ptr(z["g_pixels"]), None, None, None, ptr(z["pixels"]), None, None,
                                        ptr(z["d_sigma"]), ptr(z["d_rgb"]), st),
@@ -199,7 +224,7 @@ class Trainer:
         self.rays_seen += b
         self.kernel_launches = launches
         self.last_pixels = z["pixels"]
-        return z["loss"]
+        return loss
 
     def _exchange_and_update(self, flat, apply_update):
         """[all-reduce of the flat gradient] + Adam.  Returns the number of OUR kernels launched.  With the fused
@@ -229,6 +254,7 @@ class Trainer:
                 and (m.density_inputs == 3 or (states_x is not None and self.precision == ops.PREC_BF16))):
             return self._step_bf16(rays_o.contiguous(), rays_d.contiguous(), target.contiguous(), u, noise, apply_update,
                                    states_x=states_x)
+        self.loss_ring = 1
         flat = m.flat_parameters()
         b, s = rays_o.shape[0], self.num_samples
         dx, dd = m.density_inputs, m.color_inputs

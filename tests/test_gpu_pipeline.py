@@ -30,7 +30,8 @@ def _run(nerf_pth_state_dict, batches, piped):
             if i + 1 < len(batches):
                 pipe.submit(batches[i + 1])
             o, d, t = pipe.get()
-            pipe.done(tr.step(o, d, t))
+            loss = tr.step(o, d, t)
+            pipe.done(loss, ring=tr.loss_ring)
         losses = pipe.losses().tolist()
     torch.cuda.synchronize()
     return m.flat_parameters().clone(), losses
@@ -53,6 +54,33 @@ def test_pipeline_steps_equal_direct_steps(nerf_pth_state_dict):
     assert len(l_piped) == 6 and l_piped[0] == pytest.approx(l_direct[0], rel=1e-6)    # (the loss is an atomicAdd of block sums)
     assert l_piped == pytest.approx(l_direct, rel=1e-3)
     assert diff <= max(4.0 * noise, 6 * 2.5e-4)                                  # six Adam steps of lr 1e-4: a sign flip of a ~zero gradient moves 2e-4
+    # the trainer rotates LOSS_RING loss slots and the pipeline waits only for the read-back of the slot about to be
+    # overwritten: every loss read back is still the loss of ITS step (12 steps = three trips around the ring)
+    from nerf_b200.model import NeRF
+    from nerf_b200.train import Trainer
+    m = NeRF(normalize_position=6.0, precision="bf16").cuda(); m.load_state_dict(nerf_pth_state_dict)
+    tr = Trainer(m, num_samples=64, density_noise_std=0.0, randomly_sample=False, seed=3, precision="bf16")
+    assert tr.LOSS_RING == 4
+    pipe = HostBatchPipeline(torch.device("cuda"), like=batches[0])
+    pipe.submit(batches[0])
+    direct = []
+    for i in range(12):
+        if i + 1 < 12:
+            pipe.submit(batches[(i + 1) % 6])
+        o, d, t = pipe.get()
+        loss = tr.step(o, d, t, apply_update=False)           # no update: the loss depends on the batch only
+        assert tr.loss_ring == 4
+        pipe.done(loss, ring=tr.loss_ring)
+        direct.append(loss)                                    # a view of the slot: read AFTER the loop it shows a later step's loss
+    got = pipe.losses().tolist()
+    torch.cuda.synchronize()
+    assert len(got) == 12
+    for i in range(6):
+        assert got[i] == pytest.approx(got[i + 6], rel=1e-6), (i, got)       # same batch, same parameters
+    assert len({round(x, 7) for x in got[:6]}) == 6                          # and six different batches gave six different losses
+    assert direct[0].data_ptr() == direct[4].data_ptr() != direct[1].data_ptr()
+    with pytest.raises(ValueError):
+        pipe.done(None, ring=9)
     # misuse is an error, not a silent overwrite of a buffer a step still reads
     pipe = HostBatchPipeline(torch.device("cuda"), like=batches[0], depth=2)
     pipe.submit(batches[0]); pipe.submit(batches[1])
