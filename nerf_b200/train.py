@@ -65,7 +65,8 @@ class HostBatchPipeline:
         keep = []
         for reuse, ev in self.reads:                           # read-backs whose source the coming step overwrites precede it
             if reuse <= self.n_losses:
-                cur.wait_event(ev)
+                if not ev.query():                             # (a wait on a finished event is still a stream operation between
+                    cur.wait_event(ev)                         #  two kernels; an old read-back has long finished)
             else:
                 keep.append((reuse, ev))
         self.reads = keep
@@ -76,11 +77,11 @@ class HostBatchPipeline:
             raise ValueError("HostBatchPipeline.done: ring must be in 1..7")
         k = self.tail % len(self.bufs)
         cur = torch.cuda.current_stream()
-        self.freed[k].record(cur)
+        self.freed[k].record(cur)                              # one record per step: "the buffer is free" = "the loss is written"
+        self.stepped = self.freed[k]
         self.pending[k] = False
         self.tail += 1
         if loss is not None:
-            self.stepped.record(cur)
             with torch.cuda.stream(self.d2h):
                 self.d2h.wait_event(self.stepped)
                 self.host_losses[self.n_losses % self.host_losses.numel():][:1].copy_(loss.detach().reshape(1), non_blocking=True)
