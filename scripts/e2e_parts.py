@@ -2,7 +2,7 @@
 time (CUDA events over the region + the host time spent issuing it).  The GPU power-caps over the first seconds of load, so
 compare a line with its neighbours, not with the first one."""
 import os, sys, time, torch
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bench import nerf_pth_state_dict, synthetic_batch
 from nerf_b200.model import NeRF
 from nerf_b200.train import Trainer, HostBatchPipeline
