@@ -137,7 +137,7 @@ def test_x3_train_step_gradients_vs_oracle_fixture(model_x3, g1_ref):
     assert worst <= 3e-4
 
 
-@pytest.mark.parametrize("b,s", [(1024, 64), (3, 40), (129, 33), (300, 64)])
+@pytest.mark.parametrize("b,s", [(1024, 64), (3, 40), (129, 33), (300, 64), (5, 64), (33, 64)])    # 5 x 64: 3 tiles, 33 x 64: 17 tiles (odd: the last pair is half empty)
 def test_x3_train_step_vs_fp32_step(nerf_pth_state_dict, b, s):
     """the same step by the fp32 FFMA kernels (1e-6 from the oracle's autograd) and by the bf16x3 tensor-core kernels, same
     draws; sizes with one tile (its pair partner empty), rays straddling tiles, a partial last tile.
