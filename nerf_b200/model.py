@@ -303,6 +303,43 @@ class NeRF(nn.Module):
             t_all = ops.sample_pdf_merge(coarse["t"], coarse["weights"], num_fine)
         return self.render_rays_full(rays_o, rays_d, near, far, num_coarse + num_fine, states_x, states_d, t=t_all)
 
+    @staticmethod
+    def _launch_pieces(ray_begin, ray_end, total, chunk):
+        """How render_image cuts the ray ids [ray_begin, ray_end) of a frame of `total` rays into launches of about `chunk`
+        rays: yields (lo, hi, i, j) = launch the rays [lo, hi), keep [i, j).
+
+        A ray's pixel does not depend on the other rays of its launch, with one exception: the composite picks its kernel by
+        the launch's ray count (warp-per-ray below ops.COMPOSITE_WARP_BELOW, thread-per-ray from it on; they sum in different
+        orders).  A shard is bit-identical to the slice of the frame, at any world size, if each of its rays sees the kernel
+        it sees in the frame.  The frame is cut into `chunk`-ray launches; when chunk >= threshold all of them take the
+        thread-per-ray kernel except, possibly, a short last one (the frame's tail).  So outside the tail any launch of at
+        least `threshold` rays will do: the shard is cut into equal pieces of its own, none below the threshold (a shard
+        shorter than the threshold is widened to it and sliced); the tail is launched as it is.  (Aligning the shard's
+        launches to the frame's chunks, as this did at first, made a rank with two short edge pieces render 131 072 rays
+        for its 80 000 at N = 8.)"""
+        thr = ops.COMPOSITE_WARP_BELOW
+        ray_end = min(ray_end, total)
+        if chunk < thr:                                      # every launch of the frame is below the threshold: so is every piece
+            for i in range(ray_begin, ray_end, chunk):
+                j = min(i + chunk, ray_end)
+                yield i, j, i, j
+            return
+        last = total % chunk
+        tail0 = total - last if 0 < last < thr else total    # rays from tail0 on see the warp-per-ray kernel in the frame
+        a, b = ray_begin, min(ray_end, tail0)
+        n = b - a
+        if 0 < n < thr:                                      # (tail0 >= chunk >= thr here: there is room to widen)
+            lo = max(0, min(a, tail0 - thr))
+            yield lo, lo + thr, a, b
+        elif n > 0:
+            k = max(1, min(-(-n // chunk), n // thr))
+            for q in range(k):
+                i, j = a + n * q // k, a + n * (q + 1) // k
+                yield i, j, i, j
+        a = max(ray_begin, tail0)
+        if a < ray_end:
+            yield a, ray_end, a, ray_end
+
     def render_image(self, camera_o, camera_r, image_h, image_w, focal_length, near, far, num_samples,
                      states_x=None, states_d=None, max_chunk_size=None, num_fine=0,
                      ray_begin=0, ray_end=None):
@@ -321,20 +358,7 @@ class NeRF(nn.Module):
             if states_x is not None:                        # one state row per camera (train_conditional_nerf.py:141-153)
                 states_x = states_x.float().reshape(-1, states_x.shape[-1]).expand(bc, -1).contiguous()
             big = 1 << 20                                   # rays per launch (bounds the t/sigma/rgb workspace)
-            # Launches are cut on multiples of `big` in the FRAME's ray ids, whatever the shard.  The composite inside the fused
-            # call picks its kernel by the launch's ray count (warp-per-ray below ops.COMPOSITE_WARP_BELOW, thread-per-ray
-            # from it on; they sum in different orders), so a shard piece shorter than that inside a frame piece that is not
-            # is widened to the threshold (rays are independent of their neighbours in both kernels) and sliced: a shard is
-            # bit-identical to the slice of the frame at any world size.
-            thr = ops.COMPOSITE_WARP_BELOW
-            i = ray_begin
-            while i < ray_end:
-                c0 = (i // big) * big
-                c1 = min(c0 + big, total)
-                j = min(c1, ray_end)
-                lo, hi = i, j
-                if hi - lo < thr <= c1 - c0:
-                    lo = max(c0, min(lo, c1 - thr)); hi = lo + thr
+            for lo, hi, i, j in self._launch_pieces(ray_begin, ray_end, total, big):
                 r = ops.g1_render_fused(packed, num_samples, near, far, self.normalize_position,
                                         self.normalize_direction,
                                         camera=(camera_o, camera_r, image_h, image_w, focal_length),
@@ -342,22 +366,11 @@ class NeRF(nn.Module):
                                         t_base=self._ladder(near, far, num_samples, camera_o.device), want=("pixels",),
                                         states_x=states_x, rays_per_state=image_h * image_w, x3=x3)
                 outs.append(r["pixels"][i - lo:j - lo])
-                i = j
             if not outs:                                    # an empty shard (more ranks than rays)
                 return torch.empty(0, 3, device=camera_o.device)
             img = torch.cat(outs, dim=0)
             return img.reshape(bc, image_h, image_w, 3) if full else img
-        # Chunks are cut on multiples of `chunk` in the FRAME's ray ids, whatever the shard: a shard then runs the frame's own chunks.
-        # The coarse composite of the hierarchical path picks its kernel by the chunk's ray count (ops.COMPOSITE_WARP_BELOW), so an
-        # edge piece shorter than that is rendered as the frame's whole chunk and sliced: shards stay bit-identical to the frame.
-        i = ray_begin
-        while i < ray_end:
-            c0 = (i // chunk) * chunk
-            c1 = min(c0 + chunk, total)
-            j = min(c1, ray_end)
-            lo, hi = i, j
-            if num_fine > 0 and hi - lo < ops.COMPOSITE_WARP_BELOW <= c1 - c0:
-                lo, hi = c0, c1
+        for lo, hi, i, j in self._launch_pieces(ray_begin, ray_end, total, chunk):
             o, d = ops.generate_rays(camera_o, camera_r, image_h, image_w, focal_length, lo, hi)
             sx = sd = None
             if states_x is not None or states_d is not None:
@@ -369,6 +382,7 @@ class NeRF(nn.Module):
             else:
                 r = self.render_rays_full(o, d, near, far, num_samples, sx, sd)
             outs.append(r["pixels"][i - lo:j - lo])
-            i = j
+        if not outs:
+            return torch.empty(0, 3, device=camera_o.device)
         img = torch.cat(outs, dim=0)
         return img.reshape(bc, image_h, image_w, 3) if full else img

@@ -218,3 +218,31 @@ def test_image_ray_dataset_matches_reference_items():
                 assert np.array_equal(item[k].numpy(), want), k
             else:
                 np.testing.assert_allclose(item[k].numpy(), want, rtol=0, atol=1e-6, err_msg=k)
+
+
+def test_render_image_launch_pieces_cover_and_keep_the_kernel_choice():
+    """NeRF._launch_pieces: a shard's launches cover it exactly, in order; outside the frame's short tail chunk every launch
+    has at least COMPOSITE_WARP_BELOW rays (the thread-per-ray composite, as in the frame) and stays outside the tail;
+    the tail's launches stay below it (the warp-per-ray composite, as in the frame)."""
+    from nerf_b200 import ops
+    from nerf_b200.model import NeRF
+    thr = ops.COMPOSITE_WARP_BELOW
+    for total, chunk in ((640000, 32768), (640000, 1 << 20), (40000, 32768), (10000, 32768), (10000, 1024), (70000, 32768),
+                         (65536, 32768), (82020, 32768), (16384, 16384), (16385, 16384), (3 * 32768 + 5, 32768), (2 * 640000, 1 << 20)):
+        last = total % chunk
+        tail0 = total - last if (chunk >= thr and 0 < last < thr) else total
+        for world in (1, 2, 3, 8, 64):
+            for r in range(world):
+                rb, re = total * r // world, total * (r + 1) // world
+                x = rb
+                for lo, hi, i, j in NeRF._launch_pieces(rb, re, total, chunk):
+                    assert 0 <= lo <= i < j <= hi <= total and i == x
+                    x = j
+                    if chunk < thr:
+                        assert hi - lo <= chunk
+                    elif i < tail0:
+                        assert hi - lo >= thr and hi <= tail0
+                    else:
+                        assert lo >= tail0 and hi - lo < thr
+                assert x == re
+    assert list(NeRF._launch_pieces(5, 5, 100, 32768)) == []                     # an empty shard
