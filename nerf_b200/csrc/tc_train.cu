@@ -18,25 +18,22 @@ int launch_fused_train(const void* packed, int Dx, int Dd, const float* rays_o, 
 
 // ---- transposed weight stages for g_{l-1} = dz_l W'_l: stage (l-1)*8 + ks*2 + nh holds
 //      [128 rows r = input feature nh*128 + r] x [64 cols c = output feature ks*64 + c], K-major SW128
-//      One block per stage: the 64 x 128 tile of W is read row by row (512 contiguous bytes a row), transposed through shared
-//      memory, and the 16 KB image is written out in order.  (A thread per 16-byte image piece, reading its 8 weights with a
-//      stride of a whole row, took 19 us of every step.)
-__global__ void __launch_bounds__(256) pack_bwd_stage_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
-    __shared__ __align__(16) uint8_t img[TC_STAGE_BYTES];
-    const int stage = blockIdx.x;
+__global__ void pack_bwd_stage_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 72ll * 128 * 8) return;
+    const int c16 = (int)(i & 7), r = (int)((i >> 3) & 127), stage = (int)(i >> 10);
     const int l = 1 + stage / 8, rel = stage % 8, ks = rel >> 1, nh = rel & 1;
-    const float* W = params + L.off_W[l] + (size_t)(ks * 64) * L.Kt[l] + nh * 128;      // rows n = ks*64 + c, columns kin = nh*128 + r
+    const int kin = nh * 128 + r;
+    const float* W = params + L.off_W[l];
+    const float g = params[L.off_gamma[l - 1] + kin];
     const int Kt = L.Kt[l];
-    const int r = threadIdx.x & 127, chalf = threadIdx.x >> 7;                         // a warp reads 32 consecutive kin of one row
-    const float g = params[L.off_gamma[l - 1] + nh * 128 + r];
-    __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(img);
-#pragma unroll 4
-    for (int c = chalf; c < 64; c += 2)
-        out[(tc::sw128_offset(r, c >> 3) >> 1) + (c & 7)] = __float2bfloat16_rn(W[(size_t)c * Kt + r] * g);
-    __syncthreads();
-    uint4* dst = reinterpret_cast<uint4*>(packed + (size_t)stage * TC_STAGE_BYTES);
-    const uint4* src = reinterpret_cast<const uint4*>(img);
-    for (int i = threadIdx.x; i < TC_STAGE_BYTES / 16; i += 256) dst[i] = src[i];
+    uint32_t out[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int n0 = ks * 64 + c16 * 8 + q * 2;
+        out[q] = tc::pack_bf16x2(W[(size_t)n0 * Kt + kin] * g, W[(size_t)(n0 + 1) * Kt + kin] * g);
+    }
+    *reinterpret_cast<uint4*>(packed + (size_t)stage * TC_STAGE_BYTES + tc::sw128_offset(r, c16)) = make_uint4(out[0], out[1], out[2], out[3]);
 }
 
 extern "C" int64_t nerf_g1_packed_bwd_bytes(int Dx, int Dd) {
@@ -48,7 +45,8 @@ extern "C" int64_t nerf_g1_packed_bwd_bytes(int Dx, int Dd) {
 extern "C" int nerf_g1_pack_weights_bwd(const float* params, int Dx, int Dd, void* packed_bwd, void* stream) {
     if (!params || !packed_bwd) return NERF_ERR_BAD_ARG;
     PackLayout L; int rc = make_pack_layout(Dx, Dd, L); if (rc) return rc;
-    pack_bwd_stage_kernel<<<72, 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
+    const int64_t n = 72ll * 128 * 8;
+    pack_bwd_stage_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
@@ -348,30 +346,26 @@ int launch_fused_x3(const void* packed, FusedArgs& a, cudaStream_t st, bool trai
 int launch_wgrad_tc_units_x3(const uint8_t* ws, const X3TrainLayout& X, cudaStream_t st);      // tc_wgrad.cu
 
 // transposed stages as pack_bwd_stage_kernel, split: part 0 = bf16(w'), part 1 = bf16(w' - part 0)
-// (one block per stage, rows of W read contiguously and transposed through shared memory, like pack_bwd_stage_kernel)
-__global__ void __launch_bounds__(256) pack_bwd_stage_x3_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
-    __shared__ __align__(16) uint8_t img[2][TC_STAGE_BYTES];
-    const int stage = blockIdx.x;
+__global__ void pack_bwd_stage_x3_kernel(const float* __restrict__ params, PackLayout L, uint8_t* __restrict__ packed) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 72ll * 128 * 8) return;
+    const int c16 = (int)(i & 7), r = (int)((i >> 3) & 127), stage = (int)(i >> 10);
     const int l = 1 + stage / 8, rel = stage % 8, ks = rel >> 1, nh = rel & 1;
-    const float* W = params + L.off_W[l] + (size_t)(ks * 64) * L.Kt[l] + nh * 128;
+    const int kin = nh * 128 + r;
+    const float* W = params + L.off_W[l];
+    const float g = params[L.off_gamma[l - 1] + kin];
     const int Kt = L.Kt[l];
-    const int r = threadIdx.x & 127, chalf = threadIdx.x >> 7;
-    const float g = params[L.off_gamma[l - 1] + nh * 128 + r];
-    __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(img[0]);
-    __nv_bfloat16* lo = reinterpret_cast<__nv_bfloat16*>(img[1]);
-#pragma unroll 4
-    for (int c = chalf; c < 64; c += 2) {
-        const float w = W[(size_t)c * Kt + r] * g;
-        const __nv_bfloat16 h = __float2bfloat16_rn(w);
-        const int e = (tc::sw128_offset(r, c >> 3) >> 1) + (c & 7);
-        hi[e] = h; lo[e] = __float2bfloat16_rn(w - __bfloat162float(h));
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int n0 = ks * 64 + c16 * 8 + q * 2;
+        const float w0 = W[(size_t)n0 * Kt + kin] * g, w1 = W[(size_t)(n0 + 1) * Kt + kin] * g;
+        hi[q] = tc::pack_bf16x2(w0, w1);
+        lo[q] = tc::pack_bf16x2(w0 - bf_lo(hi[q]), w1 - bf_hi(hi[q]));
     }
-    __syncthreads();
-    for (int part = 0; part < 2; ++part) {
-        uint4* dst = reinterpret_cast<uint4*>(packed + (size_t)part * 72 * TC_STAGE_BYTES + (size_t)stage * TC_STAGE_BYTES);
-        const uint4* src = reinterpret_cast<const uint4*>(img[part]);
-        for (int i = threadIdx.x; i < TC_STAGE_BYTES / 16; i += 256) dst[i] = src[i];
-    }
+    const size_t off = (size_t)stage * TC_STAGE_BYTES + tc::sw128_offset(r, c16);
+    *reinterpret_cast<uint4*>(packed + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(packed + 72ll * TC_STAGE_BYTES + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
 }
 
 extern "C" int64_t nerf_g1_packed_bwd_x3_bytes(void) { return 2 * 72ll * TC_STAGE_BYTES; }
@@ -379,7 +373,8 @@ extern "C" int64_t nerf_g1_packed_bwd_x3_bytes(void) { return 2 * 72ll * TC_STAG
 extern "C" int nerf_g1_pack_weights_bwd_x3(const float* params, void* packed_bwd, void* stream) {
     if (!params || !packed_bwd) return NERF_ERR_BAD_ARG;
     PackLayout L; int rc = make_pack_layout(3, 3, L); if (rc) return rc;
-    pack_bwd_stage_x3_kernel<<<72, 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
+    const int64_t n = 72ll * 128 * 8;
+    pack_bwd_stage_x3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(params, L, (uint8_t*)packed_bwd);
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
 }
