@@ -68,17 +68,28 @@ __global__ void pe_states_kernel(const float* __restrict__ states, int64_t B, in
     float* o = pes + ray * (2 * NERF_PE_X_OCTAVES * Sx) + c * 2 * NERF_PE_X_OCTAVES;
     o[j] = s; o[NERF_PE_X_OCTAVES + j] = co;
 }
-// rb[u][ray][n] = sum_k sw[u][k][n] pes[ray][k]   (block = ray, thread = n)
+// rb[u][ray][n] = sum_k sw[u][k][n] pes[ray][k]   (block = RB_RAYS rays, thread = n: a weight is loaded once for the block's
+// rays -- a block per ray re-read the 80 KB weight block 8192 times, 34 us per step; the sum over k keeps its order)
+#define RB_RAYS 16
 __global__ void __launch_bounds__(256) ray_bias_kernel(const float* __restrict__ sw, const float* __restrict__ pes, int64_t B, int EXs,
                                                       float* __restrict__ rb) {
-    __shared__ float pe_s[2 * NERF_PE_X_OCTAVES * 13];
-    const int64_t ray = blockIdx.x; const int u = blockIdx.y, n = threadIdx.x;
-    for (int k = threadIdx.x; k < EXs; k += 256) pe_s[k] = pes[ray * EXs + k];
+    extern __shared__ float pe_s[];                                  // [RB_RAYS][EXs]
+    const int64_t r0 = (int64_t)blockIdx.x * RB_RAYS; const int u = blockIdx.y, n = threadIdx.x;
+    const int nr = (int)(B - r0 < RB_RAYS ? B - r0 : RB_RAYS);
+    for (int i = threadIdx.x; i < RB_RAYS * EXs; i += 256) pe_s[i] = (i / EXs) < nr ? pes[r0 * EXs + i] : 0.f;
     __syncthreads();
     const float* w = sw + (size_t)u * EXs * 256 + n;
-    float acc = 0.f;
-    for (int k = 0; k < EXs; ++k) acc = fmaf(w[(size_t)k * 256], pe_s[k], acc);
-    rb[((size_t)u * B + ray) * 256 + n] = acc;
+    float acc[RB_RAYS];
+#pragma unroll
+    for (int r = 0; r < RB_RAYS; ++r) acc[r] = 0.f;
+#pragma unroll 4
+    for (int k = 0; k < EXs; ++k) {
+        const float wk = w[(size_t)k * 256];
+#pragma unroll
+        for (int r = 0; r < RB_RAYS; ++r) acc[r] = fmaf(wk, pe_s[r * EXs + k], acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < RB_RAYS; ++r) if (r < nr) rb[((size_t)u * B + r0 + r) * 256 + n] = acc[r];
 }
 // rsum[u][ray][n] = sum over the ray's S points of dz_l[p][n], l = 0 (u = 0) or 4 (u = 1), read from the slab image.
 // Block = ray; thread = (point group pg of 8, 16-byte chunk c of the row's 32): 128-byte segments per warp-load.
@@ -105,23 +116,34 @@ __global__ void __launch_bounds__(256) dz_ray_sum_kernel(const uint8_t* __restri
     for (int g = 0; g < 8; ++g) t += part[g][n];
     rsum[((size_t)u * B + ray) * 256 + n] = t;
 }
-// gs[u][n][k] += sum_ray rsum[u][ray][n] pes[ray][k]: block = (chunk of 64 rays, u), thread = n holding the EXs
-// partial sums of its output feature in registers (one coalesced load + EXs FMAs per ray), EXs <= 20 * 13
+// gs[u][n][k] += sum_ray rsum[u][ray][n] pes[ray][k]: block = (chunk of SG_RAYS rays, u, chunk of KC columns), thread = n holding
+// its KC partial sums in registers (one coalesced load + KC FMAs per ray, eight loads in flight), EXs <= 20 * 13.  One atomic
+// per output element and block: with 64 rays a block the 2.6 M contended atomics were most of the kernel's 48 us.
+#define SG_RAYS 128
 template <int KC>
 __global__ void __launch_bounds__(256) state_grad_kernel(const float* __restrict__ rsum, const float* __restrict__ pes, int64_t B, int EXs,
                                                         float* __restrict__ gs) {
     __shared__ float pe_s[64][KC];
     const int u = blockIdx.y, n = threadIdx.x, k0 = blockIdx.z * KC;
-    const int64_t r0 = (int64_t)blockIdx.x * 64; const int nr = (int)(B - r0 < 64 ? B - r0 : 64);
-    for (int i = threadIdx.x; i < nr * KC; i += 256) { const int r = i / KC, k = i % KC; pe_s[r][k] = k0 + k < EXs ? pes[(r0 + r) * EXs + k0 + k] : 0.f; }
-    __syncthreads();
     float acc[KC];
 #pragma unroll
     for (int k = 0; k < KC; ++k) acc[k] = 0.f;
-    for (int r = 0; r < nr; ++r) {
-        const float v = rsum[((size_t)u * B + r0 + r) * 256 + n];
+    const int64_t b0 = (int64_t)blockIdx.x * SG_RAYS, b1 = b0 + SG_RAYS < B ? b0 + SG_RAYS : B;
+    for (int64_t r0 = b0; r0 < b1; r0 += 64) {
+        const int nr = (int)(b1 - r0 < 64 ? b1 - r0 : 64);
+        __syncthreads();
+        for (int i = threadIdx.x; i < 64 * KC; i += 256) { const int r = i / KC, k = i % KC; pe_s[r][k] = (r < nr && k0 + k < EXs) ? pes[(r0 + r) * EXs + k0 + k] : 0.f; }
+        __syncthreads();
+        const float* src = rsum + ((size_t)u * B + r0) * 256 + n;
+        for (int r = 0; r < 64; r += 8) {
+            float v[8];
 #pragma unroll
-        for (int k = 0; k < KC; ++k) acc[k] = fmaf(v, pe_s[r][k], acc[k]);
+            for (int q = 0; q < 8; ++q) v[q] = r + q < nr ? src[(size_t)(r + q) * 256] : 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+                for (int k = 0; k < KC; ++k) acc[k] = fmaf(v[q], pe_s[r + q][k], acc[k]);
+        }
     }
 #pragma unroll
     for (int k = 0; k < KC; ++k) if (k0 + k < EXs) atomicAdd(gs + ((size_t)u * 256 + n) * EXs + k0 + k, acc[k]);
@@ -263,7 +285,7 @@ int launch_state_bias(const void* packed, int Dx, int Dd, const float* states, i
     const int64_t n = n_states * Sx * NERF_PE_X_OCTAVES;
     pe_states_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(states, n_states, Sx, pes);
     NERF_CUDA_CHECK_LAUNCH();
-    ray_bias_kernel<<<dim3((unsigned)n_states, 2), 256, 0, st>>>(
+    ray_bias_kernel<<<dim3((unsigned)((n_states + RB_RAYS - 1) / RB_RAYS), 2), 256, (size_t)RB_RAYS * L.EXs * sizeof(float), st>>>(
         reinterpret_cast<const float*>((const uint8_t*)packed + tc_packed_state_w_offset(L)), pes, n_states, L.EXs, rb);
     NERF_CUDA_CHECK_LAUNCH();
     return NERF_OK;
@@ -328,7 +350,7 @@ extern "C" int nerf_g1_train_bwd_tc(const void* packed, const void* packed_bwd, 
         float* rsum = reinterpret_cast<float*>(ws + T.off_rsum);
         dz_ray_sum_kernel<<<dim3((unsigned)B, 2), 256, 0, st>>>(ws + T.off_dz, T.tr_tiles, B, S, rsum);
         NERF_CUDA_CHECK_LAUNCH();
-        state_grad_kernel<40><<<dim3((unsigned)((B + 63) / 64), 2, (T.EXs + 39) / 40), 256, 0, st>>>(
+        state_grad_kernel<40><<<dim3((unsigned)((B + SG_RAYS - 1) / SG_RAYS), 2, (T.EXs + 39) / 40), 256, 0, st>>>(
             rsum, reinterpret_cast<const float*>(ws + T.off_pes), B, T.EXs, reinterpret_cast<float*>(ws + T.off_gs));
         NERF_CUDA_CHECK_LAUNCH();
     }
