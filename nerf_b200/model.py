@@ -110,6 +110,12 @@ class NeRF(nn.Module):
             self._flatten()
         return self._flat
 
+    def _param_list(self):
+        """list(self.parameters()) without the walk over the module tree (0.15-0.19 ms per call): the 44 slots recorded at
+        flatten time, read afresh (a replaced Parameter object is seen)"""
+        self.flat_parameters()
+        return [mod._parameters[name] for mod, name in self._slots]
+
     def _apply(self, fn, *args, **kwargs):
         out = super()._apply(fn, *args, **kwargs)
         self._flatten()
@@ -190,7 +196,7 @@ class NeRF(nn.Module):
         b, s = samples.shape
         flat = self.flat_parameters()
         sigma, rgb = ops.g1_mlp(ex.view(b * s, ex.shape[-1]), ed, s, self.density_inputs, self.color_inputs,
-                                ops.PREC_FP32, flat, list(self.parameters()))
+                                ops.PREC_FP32, flat, self._param_list())
         return pts, sigma.view(b, s, 1), rgb.view(b, s, 3)
 
     def _render_chunk(self, rays_o, rays_d, near, far, num_samples, states_x, states_d, u, noise, t=None):
@@ -212,7 +218,7 @@ class NeRF(nn.Module):
         if self._train_tc_ok(num_samples, states_x, states_d) and b > 0:
             # tcgen05 training path under autograd: `loss.backward()` of the reference loop runs the tensor-core
             # data-/weight-gradient kernels (ops._G1TrainTC); the composite is its own differentiable node
-            t, sigma, rgb = ops.g1_train_tc(self.flat_parameters(), list(self.parameters()), rays_o, rays_d, num_samples,
+            t, sigma, rgb = ops.g1_train_tc(self.flat_parameters(), self._param_list(), rays_o, rays_d, num_samples,
                                             near, far, self.normalize_position, self.normalize_direction,
                                             t_base=self._ladder(near, far, num_samples, rays_o.device), t_in=t, u=u,
                                             states_x=states_x, x3=self.precision == "bf16x3")
@@ -269,7 +275,7 @@ class NeRF(nn.Module):
         return self._tc_shape_ok(num_samples, states_x, states_d) and not self._wants_grad()
 
     def _wants_grad(self):
-        return torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        return torch.is_grad_enabled() and any(p.requires_grad for p in self._param_list())
 
     def _train_tc_ok(self, num_samples, states_x, states_d):
         """tcgen05 path with a graph (bf16, or fp32-grade bf16x3 for the unconditional model): when a gradient can be asked for."""
