@@ -249,7 +249,9 @@ class Trainer:
     def step(self, rays_o, rays_d, target, states_x=None, states_d=None, u=None, noise=None,
              apply_update=True):
         """One optimisation step on a ray batch resident on the device.  Returns the loss
-        (1-element device tensor; reading it is the caller's device->host sync)."""
+        (1-element device tensor; reading it is the caller's device->host sync).  On the tensor-core paths the tensor is a
+        view of one of LOSS_RING slots and is overwritten `self.loss_ring` steps later: `.item()` / `.clone()` it, or hand it
+        to HostBatchPipeline.done(loss, ring=self.loss_ring), before then."""
         m = self.model
         if (self.precision in (ops.PREC_BF16, ops.PREC_BF16X3) and states_d is None and m.color_inputs == 3 and self.num_samples >= 32
                 and (m.density_inputs == 3 or (states_x is not None and self.precision == ops.PREC_BF16))):
