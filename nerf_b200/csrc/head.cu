@@ -153,8 +153,9 @@ __global__ void __launch_bounds__(256) head_composite_kernel(
             }
             if (seg_out) {
                 const int nv = (S - s0 < 32) ? S - s0 : 32;
+                const float lw_lane = logf(__fadd_rn(w, 1e-10f));       // once per lane (= sample) here, not once per sample by every lane
                 for (int kk = 0; kk < nv; ++kk) {
-                    const float lw = logf(__fadd_rn(__shfl_sync(0xffffffffu, w, kk), 1e-10f));
+                    const float lw = __shfl_sync(0xffffffffu, lw_lane, kk);
                     const float* row = out + (base + s0 + kk) * n_out + 4;
                     const float x0 = lane < n_seg ? row[lane] : -INFINITY;
                     const float x1 = lane + 32 < n_seg ? row[lane + 32] : -INFINITY;
