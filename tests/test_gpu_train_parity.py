@@ -109,8 +109,9 @@ def _d2_inputs(b, s, seed=0):
 
 
 def test_d2_full_size_all_44_gradients_vs_oracle_autograd(nerf_pth_state_dict, g1_oracle):
-    """D2 at its full size: loss and every one of the 44 gradient tensors of the fp32 step (rel-L2) and
-    of the bf16 tensor-core step (cosine) against autograd of the ORACLE on the host (one 4096 x 64 fwd+bwd)."""
+    """D2 at its full size: loss and every one of the 44 gradient tensors of the fp32 step (rel-L2), of the
+    bf16 tensor-core step (cosine) and of the fp32-grade bf16x3 tensor-core step (both) against autograd of the ORACLE on
+    the host (one 4096 x 64 fwd+bwd)."""
     from nerf_b200.model import NeRF
     from nerf_b200.train import Trainer
     b, s = 4096, 64
@@ -123,11 +124,11 @@ def test_d2_full_size_all_44_gradients_vs_oracle_autograd(nerf_pth_state_dict, g
     g1_oracle.zero_grad()
     og_, dg, tg, ug, ng = (x.cuda().contiguous() for x in (o, d, tgt, u, noise))
     report = {}
-    for prec in ("fp32", "bf16"):
+    for prec in ("fp32", "bf16", "bf16x3"):
         m = NeRF(normalize_position=6.0, precision=prec).cuda(); m.load_state_dict(nerf_pth_state_dict)
         tr = Trainer(m, num_samples=s, precision=prec)
         loss = tr.step(og_, dg, tg, u=ug, noise=ng, apply_update=False).item()
-        assert abs(loss - lo.item()) <= (1e-5 if prec == "fp32" else 2e-3) * abs(lo.item()), (prec, loss, lo.item())
+        assert abs(loss - lo.item()) <= {"fp32": 1e-5, "bf16": 2e-3, "bf16x3": 2e-5}[prec] * abs(lo.item()), (prec, loss, lo.item())
         off = m._offsets
         rows = []
         for (k, p), o_ in zip(m.named_parameters(), off):
@@ -147,6 +148,10 @@ def test_d2_full_size_all_44_gradients_vs_oracle_autograd(nerf_pth_state_dict, g
     for k, cos, rel in report["bf16"]:
         floor = D2_COSINE_EXCEPTIONS.get(k, D2_COSINE_FLOOR)
         assert cos >= floor, ("bf16", k, cos, floor)
+    # fp32-grade mode: every tensor at the gradient's own conditioning (scripts/grad_conditioning.py: a 1e-5 relative change of
+    # the forward moves the exact gradient by ~2e-3 at this size), i.e. where the fp32 FFMA path itself sits against the oracle
+    for k, cos, rel in report["bf16x3"]:
+        assert rel <= 8e-3 and cos >= 0.99998, ("bf16x3", k, cos, rel)   # measured: rel-L2 <= 3.8e-3, cosine >= 0.999993 on all 44
 
 
 def test_conditional_fp32_gradients_vs_oracle_autograd():
